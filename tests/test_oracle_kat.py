@@ -1,0 +1,254 @@
+"""Pins the CPU oracle (oracle/*.hpp, C++) before anything is compared against it:
+reference golden vectors (secp256k1 unit tests, BLS12-381 generator), RFC 9496 vectors,
+SURVEY KAT set 2 (main.rs proof as discrete logs), an independent pure-Python arithmetic
+(tests/pyref.py), libsodium (PyNaCl) and OpenSSL (`cryptography`). CPU only."""
+import random
+
+import pytest
+
+from oracle import exponent_checker as ec
+from tests import pyref
+from tests.golden import reference_vectors as gv
+
+R, S, B = 0, 1, 2
+
+
+def secp_enc(xh, yh):
+    return int(xh, 16).to_bytes(32, "little") + int(yh, 16).to_bytes(32, "little")
+
+
+def bls_enc(xh, yh):
+    return int(xh, 16).to_bytes(48, "little") + int(yh, 16).to_bytes(48, "little")
+
+
+# ------------------------------------------------------------------ secp256k1: reference unit-test vectors
+def test_secp_small_multiples(oracle):  # secp256k1.rs:151-160, scalar_mul_smaller_nums :175-187
+    for k, (x, y) in enumerate(gv.SECP_G_MULTIPLES, start=1):
+        assert oracle.scalar_mul(S, k) == secp_enc(x, y)
+
+
+def test_secp_2g_decimal(oracle):  # secp256k1.rs:62-70
+    x, y = gv.SECP_2G_DEC
+    g = oracle.scalar_mul(S, 1)
+    assert oracle.point_add(S, g, g) == x.to_bytes(32, "little") + y.to_bytes(32, "little")
+
+
+def test_secp_large_scalar_mul(oracle):  # secp256k1.rs:190-235
+    for k, x, y in gv.SECP_SCALAR_MUL:
+        assert oracle.scalar_mul(S, int(k, 16)) == secp_enc(x, y)
+
+
+def test_secp_additions(oracle):  # secp256k1.rs:237-283
+    pts = [None] + [secp_enc(x, y) for x, y in gv.SECP_G_MULTIPLES]
+    for a, b, c in gv.SECP_ADD_CASES:
+        assert oracle.point_add(S, pts[a], pts[b]) == pts[c]
+    l1, l2, l3 = (secp_enc(x, y) for x, y in gv.SECP_LARGE_ADD)
+    assert oracle.point_add(S, l1, l2) == l3
+
+
+def test_secp_infinity_cases(oracle):  # secp256k1.rs:77-112
+    g = oracle.scalar_mul(S, 1)
+    inf = bytes(64)
+    assert oracle.point_add(S, g, oracle.point_neg(S, g)) == inf
+    assert oracle.point_add(S, g, inf) == g
+    assert oracle.point_add(S, inf, g) == g
+    assert oracle.point_add(S, inf, inf) == inf
+
+
+def test_secp_field_vectors(oracle):  # field/prime_field_elem.rs:642-663, :855-865
+    a, b, c = gv.SECP_FN_MUL
+    assert oracle.sc_op(S, 2, a, b) == c
+    x, xi = gv.SECP_FP_INV
+    assert oracle.fq_op(S, 3, x) == xi
+
+
+def test_secp_vs_openssl(oracle):
+    from cryptography.hazmat.primitives.asymmetric import ec as cec
+    rng = random.Random(7)
+    for _ in range(5):
+        k = rng.randrange(1, pyref.SECP_N)
+        nums = cec.derive_private_key(k, cec.SECP256K1()).public_key().public_numbers()
+        assert oracle.scalar_mul(S, k) == nums.x.to_bytes(32, "little") + nums.y.to_bytes(32, "little")
+
+
+# ------------------------------------------------------------------ BLS12-381 G1
+def test_bls_generator_and_multiples(oracle):  # point.rs:16 + SURVEY KAT set 1
+    gx, gy = gv.BLS_G_DECIMAL
+    assert oracle.scalar_mul(B, 1) == gx.to_bytes(48, "little") + gy.to_bytes(48, "little")
+    for k, (x, y) in gv.BLS_G_MULTIPLES.items():
+        assert oracle.scalar_mul(B, k) == bls_enc(x, y)
+    assert oracle.scalar_mul(B, pyref.BLS_R - 1) == oracle.point_neg(B, oracle.scalar_mul(B, 1))
+    assert oracle.scalar_mul(B, 0) == bytes(96)
+
+
+def test_bls_point_identities(oracle):  # point.rs:124-185
+    g = oracle.scalar_mul(B, 1)
+    g2 = oracle.point_add(B, g, g)
+    assert oracle.scalar_mul(B, 2) == g2
+    assert oracle.scalar_mul(B, 3) == oracle.point_add(B, g2, g)
+    assert oracle.point_add(B, g, oracle.point_neg(B, g)) == bytes(96)
+
+
+def test_bls_fr_small_kats(oracle):  # prime_field_elem.rs:256-347
+    assert oracle.sc_op(B, 1, 9, 2) == 7
+    assert oracle.sc_op(B, 2, 2, 5) == 10
+    assert oracle.sc_op(B, 2, 10, oracle.sc_op(B, 3, 2)) == 5
+    assert oracle.sc_op(B, 2, 5, oracle.sc_op(B, 3, 5)) == 1
+    assert oracle.sc_op(B, 0, oracle.sc_op(B, 4, 5), 5) == 0
+    assert oracle.sc_op(B, 4, 5) == pyref.BLS_R - 5  # set_int(-5) semantics, prime_field_elem.rs:191-195
+
+
+# ------------------------------------------------------------------ Ristretto255
+def test_ristretto_rfc9496_multiples(oracle):
+    for k, h in gv.RISTRETTO_MULTIPLES.items():
+        assert oracle.scalar_mul(R, k).hex() == h
+    assert pyref.SQRT_M1 == gv.RISTRETTO_SQRT_M1
+    assert pyref.INVSQRT_A_MINUS_D == gv.RISTRETTO_INVSQRT_A_MINUS_D
+
+
+def test_ristretto_bad_encodings(oracle):
+    p = pyref.P25519
+    bad = [p.to_bytes(32, "little"), (p + 1).to_bytes(32, "little"), (2**256 - 1).to_bytes(32, "little"),  # non-canonical
+           (1).to_bytes(32, "little"), (p - 2).to_bytes(32, "little")]  # negative s
+    for b in bad:
+        assert not oracle.point_decode_ok(R, b)
+    # every s the Python decoder rejects, the oracle rejects too (and vice versa)
+    rng = random.Random(3)
+    n_ok = 0
+    for _ in range(64):
+        b = (rng.randrange(0, p) & ~1).to_bytes(32, "little")
+        ok = pyref.ristretto_decode(b) is not None
+        assert oracle.point_decode_ok(R, b) == ok
+        n_ok += ok
+    assert 0 < n_ok < 64
+
+
+def test_ristretto_vs_python_and_libsodium(oracle):
+    import nacl.bindings as nb
+    rng = random.Random(11)
+    base = pyref.ed_base()
+    for _ in range(6):
+        k = rng.randrange(1, pyref.ELL)
+        P = pyref.ed_mul(k, base)
+        # pyref's Edwards arithmetic agrees with libsodium ...
+        assert pyref.ed25519_encode(P) == nb.crypto_scalarmult_ed25519_base_noclamp(k.to_bytes(32, "little"))
+        # ... and the oracle's Ristretto encoding of k*B agrees with pyref's
+        enc = pyref.ristretto_encode(P)
+        assert oracle.scalar_mul(R, k) == enc
+        # decode -> encode round trip, and torsion-coset invariance of the encoding
+        assert oracle.point_add(R, enc, bytes(32)) == enc
+    # scalar field vs libsodium
+    a, b = rng.randrange(pyref.ELL), rng.randrange(pyref.ELL)
+    assert oracle.sc_op(R, 2, a, b) == int.from_bytes(
+        nb.crypto_core_ed25519_scalar_mul(a.to_bytes(32, "little"), b.to_bytes(32, "little")), "little")
+    assert oracle.sc_op(R, 3, a) == int.from_bytes(nb.crypto_core_ed25519_scalar_invert(a.to_bytes(32, "little")), "little")
+
+
+# ------------------------------------------------------------------ group law vs pyref on all curves
+@pytest.mark.parametrize("curve", [R, S, B])
+def test_group_law_random(oracle, curve):
+    rng = random.Random(100 + curve)
+    q = pyref.CURVES[curve]["order"]
+    for _ in range(4):
+        a, b = rng.randrange(q), rng.randrange(q)
+        pa, pb_ = oracle.scalar_mul(curve, a), oracle.scalar_mul(curve, b)
+        assert pa == pyref.base_mul_encoded(curve, a)
+        assert oracle.point_add(curve, pa, pb_) == pyref.base_mul_encoded(curve, a + b)
+        assert oracle.scalar_mul(curve, b, pa) == pyref.base_mul_encoded(curve, a * b)
+        assert oracle.point_add(curve, pa, pa) == pyref.base_mul_encoded(curve, 2 * a)
+
+
+# ------------------------------------------------------------------ generators & commitments (publickey.rs, prover.rs)
+@pytest.mark.parametrize("curve", [R, S, B])
+def test_public_key_rule(oracle, curve):
+    pb = pyref.CURVES[curve]["pb"]
+    g, h, G, H = oracle.pk_new(curve, 8)
+    assert g == pyref.base_mul_encoded(curve, 1) and h == pyref.base_mul_encoded(curve, 2)
+    for i in range(8):
+        assert G[i * pb:(i + 1) * pb] == pyref.base_mul_encoded(curve, 3 * (i + 1))
+        assert H[i * pb:(i + 1) * pb] == pyref.base_mul_encoded(curve, 5 * (i + 1))
+    assert G[4 * pb:5 * pb] == H[2 * pb:3 * pb]  # 15*g, SURVEY §7.3 item 1
+
+
+@pytest.mark.parametrize("curve", [R, S, B])
+def test_commit_i32_quirk(oracle, curve):  # prover.rs:37 `v as i32`
+    q = pyref.CURVES[curve]["order"]
+    pb = pyref.CURVES[curve]["pb"]
+    vs = [2, 5, 2**31 - 1, 2**31, 2**32 + 9, 2**64 - 1]
+    gam = [3, 7, 11, 13, 17, q - 1]
+    out = oracle.commit(curve, vs, gam)
+    ck = ec.Checker(q)
+    for i, (v, gm) in enumerate(zip(vs, gam)):
+        assert out[i * pb:(i + 1) * pb] == pyref.base_mul_encoded(curve, ck.commit(v, gm))
+
+
+# ------------------------------------------------------------------ KAT set 2: the src/main.rs proof
+def _split_proof(proof, pb, rounds):
+    pts = [proof[i * pb:(i + 1) * pb] for i in range(2 * rounds + 3)]
+    sc = proof[(2 * rounds + 3) * pb:]
+    scal = [int.from_bytes(sc[i * 32:(i + 1) * 32], "little") for i in range(3)]
+    return dict(A=pts[0], L=pts[1:1 + rounds], R=pts[1 + rounds:1 + 2 * rounds], wipA=pts[1 + 2 * rounds],
+                wipB=pts[2 + 2 * rounds], r_prime=scal[0], s_prime=scal[1], d_prime=scal[2])
+
+
+@pytest.mark.parametrize("curve", [R, S, B])
+def test_main_rs_kat(oracle, curve):
+    q = pyref.CURVES[curve]["order"]
+    pb = pyref.CURVES[curve]["pb"]
+    exp = ec.main_rs_kat(curve)
+    # the independent checker reproduces the surveyor's digest and field values
+    assert exp.kat_digest() == gv.MAIN_RS_DIGEST[curve]
+    f = gv.MAIN_RS_FIELDS[curve]
+    assert (exp.A, exp.L[0], exp.R[0], exp.L[6], exp.R[6]) == tuple(int(f[k], 16) for k in ("A", "L0", "R0", "L6", "R6"))
+    assert (exp.wipA, exp.r_prime, exp.s_prime, exp.d_prime) == tuple(int(f[k], 16) for k in ("wipA", "r_prime", "s_prime", "d_prime"))
+    assert exp.wipB == gv.MAIN_RS_WIPB_DLOG
+    # the C++ restatement produces exactly those group elements and scalars
+    proof = oracle.range_prove(curve, 64, 2, [2, 5], [3, 7])
+    got = _split_proof(proof, pb, 7)
+    mul = lambda k: oracle.scalar_mul(curve, k % q)
+    assert got["A"] == mul(exp.A)
+    for k in range(7):
+        assert got["L"][k] == mul(exp.L[k]) and got["R"][k] == mul(exp.R[k])
+    assert got["wipA"] == mul(exp.wipA) and got["wipB"] == mul(exp.wipB)
+    assert (got["r_prime"], got["s_prime"], got["d_prime"]) == (exp.r_prime, exp.s_prime, exp.d_prime)
+    # main.rs:56 — verify == Ok(())
+    V = oracle.commit(curve, [2, 5], [3, 7])
+    assert V == mul(8) + mul(19)
+    assert oracle.range_verify(curve, 64, 2, V, proof) == 0
+
+
+@pytest.mark.parametrize("curve", [R, S, B])
+@pytest.mark.parametrize("n,m", [(8, 1), (8, 4), (32, 1)])
+def test_oracle_vs_checker_grid(oracle, curve, n, m):
+    """(n, m) grid of the commented-out reference test (range/mod.rs:520-566), small sizes."""
+    q = pyref.CURVES[curve]["order"]
+    pb = pyref.CURVES[curve]["pb"]
+    rng = random.Random(n * 100 + m + curve)
+    vs = [rng.randrange(0, 2**min(n, 31)) for _ in range(m)]
+    gam = [rng.randrange(q) for _ in range(m)]
+    rounds = (n * m).bit_length() - 1
+    exp = ec.Checker(q).range_prove(n, m, vs, gam)
+    proof = oracle.range_prove(curve, n, m, vs, gam)
+    got = _split_proof(proof, pb, rounds)
+    mul = lambda k: oracle.scalar_mul(curve, k % q)
+    assert got["A"] == mul(exp.A)
+    assert got["L"] == [mul(x) for x in exp.L] and got["R"] == [mul(x) for x in exp.R]
+    assert got["wipA"] == mul(exp.wipA) and got["wipB"] == mul(exp.wipB)
+    assert (got["r_prime"], got["s_prime"], got["d_prime"]) == (exp.r_prime, exp.s_prime, exp.d_prime)
+    V = oracle.commit(curve, vs, gam)
+    assert oracle.range_verify(curve, n, m, V, proof) == 0
+    # tampered proofs and an out-of-range value are rejected
+    bad = bytearray(proof)
+    bad[-1 - 64] ^= 1 if bad[-1 - 64] != 0 else 0  # r' high byte: keep canonical by flipping low byte instead
+    bad = bytearray(proof)
+    off = (2 * rounds + 3) * pb
+    bad[off] ^= 1  # r' + or - 1
+    assert oracle.range_verify(curve, n, m, V, bytes(bad)) == 1
+    A_plus_g = oracle.point_add(curve, proof[:pb], mul(1))
+    assert oracle.range_verify(curve, n, m, V, A_plus_g + proof[pb:]) == 1
+    V_bad = oracle.commit(curve, [vs[0] + 1] + vs[1:], gam)
+    assert oracle.range_verify(curve, n, m, V_bad, proof) == 1
+    if n < 31:
+        vs2 = [2**n] + vs[1:]
+        proof2 = oracle.range_prove(curve, n, m, vs2, gam)
+        assert oracle.range_verify(curve, n, m, oracle.commit(curve, vs2, gam), proof2) == 1
