@@ -1,0 +1,361 @@
+"""Host-side mirror of the reference crate's public API over the C ABI (include/bpp.h).
+
+Names, argument meaning and error behaviour follow the reference (paths relative to its src/):
+    Arith.init                          bls12_381/building_block/arith.rs:9-17
+    PublicKey.new / .commitment         publickey.rs:21-52
+    RangeProver.commit                  range/prover.rs:28-42
+    RangeProof.prove / .verify          range/mod.rs:31-78
+    WeightedInnerProductProof.prove / .verify   weighted_inner_product_proof.rs:36-43, :238-248
+    MulVec                              bls12_381/building_block/mulvec.rs:13-53
+Everything is computed by libbpp_b200.so on the GPU; this file only marshals bytes. Scalars are Python
+ints (reduced mod the group order like PrimeFieldElem::new), points are their boundary encodings (bytes).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+from . import _lib
+from ._lib import BppParams
+
+ORDERS = {
+    0: 2**252 + 27742317777372353535851937790883648493,
+    1: 0xFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFEBAAEDCE6AF48A03BBFD25E8CD0364141,
+    2: 0x73EDA753299D7D483339D80809A1D80553BDA402FFFE5BFEFFFFFFFF00000001,
+}
+
+
+class ProofError(Exception):
+    """errors.rs:14-50; only VerificationError is ever produced by the reference path."""
+
+
+class VerificationError(ProofError):
+    pass
+
+
+class FormatError(ProofError):
+    pass
+
+
+class BppError(RuntimeError):
+    def __init__(self, rc, msg=""):
+        super().__init__(f"bpp error {rc} ({_lib.ERROR_NAMES[rc] if 0 <= rc < len(_lib.ERROR_NAMES) else '?'}) {msg}")
+        self.rc = rc
+
+
+def _sc(x: int) -> bytes:
+    return int(x).to_bytes(32, "little")
+
+
+def make_params(y, z, e_final, alpha, r, s, delta, eta, e_round, d_L, d_R) -> BppParams:
+    p = BppParams()
+    for k, v in (("y", y), ("z", z), ("e_final", e_final), ("alpha", alpha), ("r", r), ("s", s), ("delta", delta), ("eta", eta)):
+        C.memmove(getattr(p, k), _sc(v), 32)
+    p.n_rounds = len(e_round)
+    p._keep = [b"".join(_sc(x) for x in lst) for lst in (e_round, d_L, d_R)]
+    p.e_round, p.d_L, p.d_R = p._keep
+    return p
+
+
+class Arith:
+    """One context per process and device (Arith::init is a process-global Once in the reference)."""
+    _ctx: dict = {}
+
+    @classmethod
+    def init(cls, device: int = 0, stream: int | None = None) -> "Context":
+        key = (device, stream)
+        if key not in cls._ctx:
+            cls._ctx[key] = Context(device, stream)
+        return cls._ctx[key]
+
+
+class Context:
+    def __init__(self, device: int = 0, stream: int | None = None):
+        self.lib = _lib.load()
+        h = C.c_void_p()
+        rc = self.lib.bpp_init(device, C.c_void_p(stream) if stream else None, C.byref(h))
+        if rc != _lib.OK:
+            raise BppError(rc, "bpp_init failed: no usable CUDA device (this package has no CPU fallback)")  # arith.rs:12-14
+        self.h = h
+        self.device = device
+
+    def check(self, rc, what=""):
+        if rc != _lib.OK:
+            raise BppError(rc, f"{what}: {self.lib.bpp_last_error(self.h).decode()}")
+
+    def kernel_launches(self) -> int:
+        return int(self.lib.bpp_kernel_launches(self.h))
+
+    def sync(self):
+        self.check(self.lib.bpp_sync(self.h), "sync")
+
+    def int_peak_probe(self):
+        a, b, c = C.c_double(), C.c_double(), C.c_double()
+        self.check(self.lib.bpp_int_peak_probe(self.h, C.byref(a), C.byref(b), C.byref(c)), "int_peak_probe")
+        return dict(wide_imad_per_s=a.value, lo_imad_per_s=b.value, elapsed_ms=c.value)
+
+    def hot_kernel_stats(self, reset=False):
+        ms, n = C.c_double(), C.c_uint64()
+        self.check(self.lib.bpp_hot_kernel_stats(self.h, C.byref(ms), C.byref(n), 1 if reset else 0), "hot_kernel_stats")
+        return ms.value, int(n.value)
+
+    def debug_op(self, curve, op, a: bytes, b: bytes, elem: int):
+        n = len(a) // elem
+        out, ok = C.create_string_buffer(n * elem), C.create_string_buffer(n)
+        self.check(self.lib.bpp_debug_op(self.h, curve, op, n, a, b, out, ok), "debug_op")
+        return out.raw, ok.raw
+
+
+class PublicKey:
+    """publickey.rs:13-18 — g, h, G_vec, H_vec live on the device; `.g .h .G_vec .H_vec` export them."""
+
+    def __init__(self, ctx: Context, curve: int, length: int):
+        self.ctx, self.curve, self.length = ctx, curve, length
+        self.pb = ctx.lib.bpp_point_bytes(curve)
+        h = C.c_void_p()
+        ctx.check(ctx.lib.bpp_pk_new(ctx.h, curve, length, C.byref(h)), "pk_new")
+        self.h = h
+        self._exported = None
+
+    @staticmethod
+    def new(length: int, curve: int = _lib.RISTRETTO255, ctx: Context | None = None) -> "PublicKey":
+        return PublicKey(ctx or Arith.init(), curve, length)
+
+    def _export(self):
+        if self._exported is None:
+            pb, n = self.pb, self.length
+            g, h = C.create_string_buffer(pb), C.create_string_buffer(pb)
+            G, H = C.create_string_buffer(max(1, pb * n)), C.create_string_buffer(max(1, pb * n))
+            self.ctx.check(self.ctx.lib.bpp_pk_export(self.ctx.h, self.h, g, h, G, H), "pk_export")
+            self._exported = (g.raw, h.raw, [G.raw[i * pb:(i + 1) * pb] for i in range(n)], [H.raw[i * pb:(i + 1) * pb] for i in range(n)])
+        return self._exported
+
+    g = property(lambda self: self._export()[0])
+    h = property(lambda self: self._export()[1])
+    G_vec = property(lambda self: self._export()[2])
+    H_vec = property(lambda self: self._export()[3])
+
+    def commit_batch(self, vs, gammas) -> list:
+        n = len(vs)
+        arr = (C.c_uint64 * n)(*[v & (2**64 - 1) for v in vs])
+        out = C.create_string_buffer(max(1, n * self.pb))
+        gam = b"".join(_sc(g % ORDERS[self.curve]) for g in gammas)
+        self.ctx.check(self.ctx.lib.bpp_commit_batch(self.ctx.h, self.h, arr, gam, n, out), "commit_batch")
+        return [out.raw[i * self.pb:(i + 1) * self.pb] for i in range(n)]
+
+    def __del__(self):
+        try:
+            self.ctx.lib.bpp_pk_free(self.h)
+        except Exception:
+            pass
+
+
+class RangeProver:
+    """range/prover.rs:13-42 — holds the witness; commit() appends (v, gamma, V)."""
+
+    def __init__(self):
+        self.v_vec, self.gamma_vec, self.commitment_vec = [], [], []
+
+    def commit(self, pk: PublicKey, v: int, gamma: int):
+        self.v_vec.append(v)
+        self.gamma_vec.append(gamma)
+        self.commitment_vec.append(pk.commit_batch([v], [gamma])[0])
+
+
+@dataclass
+class WeightedInnerProductProof:
+    """weighted_inner_product_proof.rs:25-33"""
+    L_vec: list
+    R_vec: list
+    A: bytes
+    B: bytes
+    r_prime: int
+    s_prime: int
+    d_prime: int
+
+    def to_bytes(self) -> bytes:
+        return b"".join(self.L_vec) + b"".join(self.R_vec) + self.A + self.B + _sc(self.r_prime) + _sc(self.s_prime) + _sc(self.d_prime)
+
+    @staticmethod
+    def from_bytes(b: bytes, pb: int) -> "WeightedInnerProductProof":
+        rounds = ((len(b) - 96) // pb - 2) // 2
+        pts = [b[i * pb:(i + 1) * pb] for i in range(2 * rounds + 2)]
+        sc = [int.from_bytes(b[(2 * rounds + 2) * pb + 32 * i:(2 * rounds + 2) * pb + 32 * (i + 1)], "little") for i in range(3)]
+        return WeightedInnerProductProof(pts[:rounds], pts[rounds:2 * rounds], pts[2 * rounds], pts[2 * rounds + 1], *sc)
+
+    @staticmethod
+    def prove(pk: PublicKey, a_vec, b_vec, power_of_y_vec, gamma: int, commitment: bytes | None = None,
+              params: BppParams | None = None) -> "WeightedInnerProductProof":
+        """wip.rs:36-43. `commitment` is accepted and ignored, like the reference (dead update, :137-142)."""
+        n = pk.length
+        if not (len(a_vec) == len(b_vec) == len(power_of_y_vec) == n):
+            raise AssertionError("wip: all input vectors must have the same length")  # wip.rs:61-64
+        if n & (n - 1):
+            raise AssertionError("wip: length must be a power of two")  # wip.rs:67
+        q = ORDERS[pk.curve]
+        ln = C.c_size_t(pk.ctx.lib.bpp_wip_proof_len(pk.curve, n))
+        out = C.create_string_buffer(ln.value)
+        enc = lambda v: b"".join(_sc(x % q) for x in v)
+        pk.ctx.check(pk.ctx.lib.bpp_wip_prove(pk.ctx.h, pk.h, enc(a_vec), enc(b_vec), enc(power_of_y_vec), _sc(gamma % q), params, out,
+                                              C.byref(ln)), "wip_prove")
+        return WeightedInnerProductProof.from_bytes(out.raw[:ln.value], pk.pb)
+
+    def verify(self, pk: PublicKey, power_of_y_vec, G_exp_of_commitment, H_exp_of_commitment, g_exp_of_commitment: int,
+               V_exp_of_commitment, A_prime: bytes, V, params: BppParams | None = None) -> None:
+        """wip.rs:238-248. Returns None for Ok(()), raises VerificationError otherwise."""
+        q = ORDERS[pk.curve]
+        enc = lambda v: b"".join(_sc(x % q) for x in v)
+        proof = self.to_bytes()
+        rc = pk.ctx.lib.bpp_wip_verify(pk.ctx.h, pk.h, enc(power_of_y_vec), enc(G_exp_of_commitment), enc(H_exp_of_commitment),
+                                       _sc(g_exp_of_commitment % q), len(V), enc(V_exp_of_commitment) or None, A_prime,
+                                       b"".join(V) or None, proof, len(proof), params)
+        _raise_verdict(pk.ctx, rc)
+
+
+def _raise_verdict(ctx, rc):
+    if rc == _lib.OK:
+        return
+    if rc == _lib.ERR_VERIFICATION:
+        raise VerificationError("Proof verification failed.")
+    if rc == _lib.ERR_FORMAT:
+        raise FormatError("Proof data could not be parsed.")
+    ctx.check(rc, "verify")
+
+
+@dataclass
+class RangeProof:
+    """range/mod.rs:24-28"""
+    A: bytes
+    proof: WeightedInnerProductProof
+
+    def to_bytes(self) -> bytes:
+        return self.A + self.proof.to_bytes()
+
+    @staticmethod
+    def from_bytes(b: bytes, pb: int) -> "RangeProof":
+        return RangeProof(b[:pb], WeightedInnerProductProof.from_bytes(b[pb:], pb))
+
+    @staticmethod
+    def prove(pk: PublicKey, n: int, prover: RangeProver, params: BppParams | None = None) -> "RangeProof":
+        """range/mod.rs:31-55 (dispatches on m == 1 inside the library, like the reference)."""
+        m = len(prover.v_vec)
+        return RangeProof.from_bytes(prove_batch(pk, n, m, prover.v_vec, prover.gamma_vec, params)[0], pk.pb)
+
+    def verify(self, pk: PublicKey, n: int, commitment_vec, params: BppParams | None = None) -> None:
+        """range/mod.rs:57-78. Returns None for Ok(()), raises VerificationError otherwise."""
+        m = len(commitment_vec)
+        _raise_verdict(pk.ctx, verify_batch(pk, n, m, [self.to_bytes()], [list(commitment_vec)], params)[0])
+
+
+def _shape_asserts(pk, n, m):
+    if pk.length != n * m:
+        raise AssertionError("pk.G_vec.len() != n*m")  # range/mod.rs:90-91, :252-253
+
+
+def prove_batch(pk: PublicKey, n: int, m: int, values, gammas, params: BppParams | None = None) -> list:
+    """`count` independent aggregated proofs in one call; values/gammas are flat lists of count*m entries."""
+    _shape_asserts(pk, n, m)
+    count = len(values) // m
+    q = ORDERS[pk.curve]
+    plen = pk.ctx.lib.bpp_range_proof_len(pk.curve, n, m)
+    arr = (C.c_uint64 * (count * m))(*[v & (2**64 - 1) for v in values])
+    out = C.create_string_buffer(max(1, count * plen))
+    pk.ctx.check(pk.ctx.lib.bpp_range_prove_batch(pk.ctx.h, pk.h, n, m, count, arr, b"".join(_sc(g % q) for g in gammas), params, out),
+                 "range_prove_batch")
+    return [out.raw[i * plen:(i + 1) * plen] for i in range(count)]
+
+
+def verify_batch(pk: PublicKey, n: int, m: int, proofs, commitments, params: BppParams | None = None) -> list:
+    """Verdict code per proof (0 ok, 1 verification, 2 format). proofs: list of bytes; commitments: list of m-lists."""
+    _shape_asserts(pk, n, m)
+    count = len(proofs)
+    plen = pk.ctx.lib.bpp_range_proof_len(pk.curve, n, m)
+    if any(len(p) != plen for p in proofs):
+        raise FormatError("wrong proof length")
+    out = C.create_string_buffer(max(1, count))
+    V = b"".join(b"".join(c) for c in commitments)
+    pk.ctx.check(pk.ctx.lib.bpp_range_verify_batch(pk.ctx.h, pk.h, n, m, count, V, b"".join(proofs), params, out), "range_verify_batch")
+    return list(out.raw[:count])
+
+
+class MulVec:
+    """bls12_381/building_block/mulvec.rs:13-53 — accumulate (scalar, point) pairs, calculate() = sum s_i * P_i."""
+
+    def __init__(self, curve: int = _lib.RISTRETTO255, ctx: Context | None = None):
+        self.curve, self.ctx = curve, ctx or Arith.init()
+        self.scalars, self.points = [], []
+
+    def add_scalar(self, s: int):
+        self.scalars.append(s)
+
+    def add_scalars(self, ss):
+        self.scalars.extend(ss)
+
+    def add_point(self, p: bytes):
+        self.points.append(p)
+
+    def add_points(self, ps):
+        self.points.extend(ps)
+
+    def calculate(self) -> bytes:
+        if len(self.scalars) != len(self.points):
+            raise RuntimeError("mulvec: lengths of scalars and points must match")  # mulvec.rs:23-25
+        pb = self.ctx.lib.bpp_point_bytes(self.curve)
+        out = C.create_string_buffer(pb)
+        q = ORDERS[self.curve]
+        k = len(self.scalars)
+        self.ctx.check(self.ctx.lib.bpp_msm(self.ctx.h, self.curve, b"".join(_sc(s % q) for s in self.scalars) or None,
+                                            b"".join(self.points) or None, k, out), "msm")
+        return out.raw
+
+
+class Points:
+    """A decoded point vector resident in HBM (bpp_points) for repeated / large MSMs."""
+
+    def __init__(self, ctx: Context, curve: int, h):
+        self.ctx, self.curve, self.h = ctx, curve, h
+        self.pb = ctx.lib.bpp_point_bytes(curve)
+
+    @staticmethod
+    def upload(points: bytes, curve: int = _lib.RISTRETTO255, ctx: Context | None = None) -> "Points":
+        ctx = ctx or Arith.init()
+        h = C.c_void_p()
+        k = len(points) // ctx.lib.bpp_point_bytes(curve)
+        ctx.check(ctx.lib.bpp_points_upload(ctx.h, curve, points, k, C.byref(h)), "points_upload")
+        return Points(ctx, curve, h)
+
+    @staticmethod
+    def from_multipliers(mults: bytes, curve: int = _lib.RISTRETTO255, ctx: Context | None = None) -> "Points":
+        ctx = ctx or Arith.init()
+        h = C.c_void_p()
+        ctx.check(ctx.lib.bpp_points_from_multipliers(ctx.h, curve, mults, len(mults) // 32, C.byref(h)), "points_from_multipliers")
+        return Points(ctx, curve, h)
+
+    def __len__(self):
+        return int(self.ctx.lib.bpp_points_len(self.h))
+
+    def msm(self, scalars: bytes, k: int | None = None, n_jobs: int = 1) -> list:
+        k = k if k is not None else len(scalars) // 32 // n_jobs
+        out = C.create_string_buffer(n_jobs * self.pb)
+        self.ctx.check(self.ctx.lib.bpp_msm_prepared(self.ctx.h, self.h, scalars, k, n_jobs, out), "msm_prepared")
+        return [out.raw[i * self.pb:(i + 1) * self.pb] for i in range(n_jobs)]
+
+    def msm_raw(self, scalars: bytes, k: int | None = None) -> bytes:
+        k = k if k is not None else len(scalars) // 32
+        out = C.create_string_buffer(self.ctx.lib.bpp_raw_point_bytes(self.curve))
+        self.ctx.check(self.ctx.lib.bpp_msm_prepared_raw(self.ctx.h, self.h, scalars, k, out), "msm_prepared_raw")
+        return out.raw
+
+    def __del__(self):
+        try:
+            self.ctx.lib.bpp_points_free(self.h)
+        except Exception:
+            pass
+
+
+def points_sum_raw(raw: bytes, curve: int = _lib.RISTRETTO255, ctx: Context | None = None) -> bytes:
+    ctx = ctx or Arith.init()
+    rb = ctx.lib.bpp_raw_point_bytes(curve)
+    out = C.create_string_buffer(ctx.lib.bpp_point_bytes(curve))
+    ctx.check(ctx.lib.bpp_points_sum_raw(ctx.h, curve, raw, len(raw) // rb, out), "points_sum_raw")
+    return out.raw

@@ -1,0 +1,446 @@
+// Launch sequences for each C-ABI entry point, templated on (curve policy C, scalar modulus M).
+#pragma once
+#include "engine.cuh"
+#include "proto_misc.cuh"
+
+namespace bpp {
+
+struct HostOrder { uint8_t le[32]; };
+inline bool host_scalar_ok(const uint8_t* s, const uint8_t* order_le) {
+  for (int i = 31; i >= 0; i--) {
+    if (s[i] != order_le[i]) return s[i] < order_le[i];
+  }
+  return false;
+}
+
+__global__ void prove_jobstart_kernel(uint32_t n_proofs, uint32_t L, uint32_t N, uint32_t has_A, uint32_t terms_per_proof,
+                                      uint32_t* __restrict__ job_start) {
+  const uint32_t J = has_A + 2 * L + 2;
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t > n_proofs * J) return;
+  if (t == n_proofs * J) { job_start[t] = n_proofs * terms_per_proof; return; }
+  uint32_t p = t / J, k = t % J, off = 0;
+  if (has_A) { if (k == 0) { job_start[t] = p * terms_per_proof; return; } off = 2; k -= 1; }
+  if (k < 2 * L) off += k * (N + 2);
+  else if (k == 2 * L) off += 2 * L * (N + 2);
+  else off += 2 * L * (N + 2) + 2 * N + 2;
+  job_start[t] = p * terms_per_proof + off;
+}
+
+template <class C, class M>
+struct Api {
+  static constexpr size_t PB = C::POINT_BYTES;
+
+  // ---- parameters -----------------------------------------------------------------------------------
+  // packs (and validates) the parameter block into B_PARAMS; NULL = the reference's constants
+  static int load_params(bpp_ctx* ctx, const bpp_params* prm, bool single, uint32_t L, const uint8_t* order_le) {
+    std::vector<uint8_t> h((size_t)(P_FIXED + 3 * L) * 32, 0);
+    auto put_small = [&](size_t slot, uint32_t v) { memset(&h[slot * 32], 0, 32); memcpy(&h[slot * 32], &v, 4); };
+    if (!prm) {
+      put_small(P_Y, single ? 7 : 12); put_small(P_Z, single ? 7 : 23); put_small(P_EFINAL, 99);
+      put_small(P_ALPHA, single ? 7 : 33); put_small(P_R, 33); put_small(P_S, 44); put_small(P_DELTA, 88); put_small(P_ETA, 123);
+      for (uint32_t k = 0; k < L; k++) { put_small(P_FIXED + k, 7); put_small(P_FIXED + L + k, 4); put_small(P_FIXED + 2 * L + k, 5); }
+    } else {
+      if (prm->n_rounds < L || (L && (!prm->e_round || !prm->d_L || !prm->d_R))) { ctx->err = "params: too few rounds"; return BPP_ERR_LENGTH; }
+      const uint8_t* fixed[8] = {prm->y, prm->z, prm->e_final, prm->alpha, prm->r, prm->s, prm->delta, prm->eta};
+      for (int i = 0; i < 8; i++) memcpy(&h[(size_t)i * 32], fixed[i], 32);
+      memcpy(&h[(size_t)P_FIXED * 32], prm->e_round, (size_t)L * 32);
+      memcpy(&h[(size_t)(P_FIXED + L) * 32], prm->d_L, (size_t)L * 32);
+      memcpy(&h[(size_t)(P_FIXED + 2 * L) * 32], prm->d_R, (size_t)L * 32);
+      for (size_t i = 0; i < P_FIXED + 3 * (size_t)L; i++)
+        if (!host_scalar_ok(&h[i * 32], order_le)) { ctx->err = "params: non-canonical scalar"; return BPP_ERR_FORMAT; }
+    }
+    BPP_CK(ctx->buf[B_PARAMS].ensure(h.size()));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_PARAMS].p, h.data(), h.size(), cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaStreamSynchronize(ctx->stream));  // h is a stack-lifetime staging buffer
+    return BPP_OK;
+  }
+  static int read_flag(bpp_ctx* ctx, const uint8_t* d_flag, uint8_t* out) {
+    BPP_CK(cudaMemcpyAsync(out, d_flag, 1, cudaMemcpyDeviceToHost, ctx->stream));
+    BPP_CK(cudaStreamSynchronize(ctx->stream));
+    return BPP_OK;
+  }
+  static int clear_flags(bpp_ctx* ctx) {
+    BPP_CK(ctx->buf[B_FLAGS].ensure(16));
+    BPP_CK(cudaMemsetAsync(ctx->buf[B_FLAGS].p, 0, 16, ctx->stream));
+    return BPP_OK;
+  }
+
+  // ---- PublicKey::new ---------------------------------------------------------------------------------
+  static int pk_new(bpp_ctx* ctx, size_t len, bpp_pk** out) {
+    if (len > (1u << 24)) return BPP_ERR_LENGTH;
+    bpp_pk* pk = new bpp_pk();
+    pk->curve = C::CURVE_ID; pk->len = len; pk->device = ctx->device;
+    cudaError_t e = cudaMalloc(&pk->table, (size_t)pk->n_points() * C::AFF_WORDS * 4);
+    if (e != cudaSuccess) { delete pk; ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
+    pk_gen_kernel<C><<<ceil_div(pk->n_points(), 64), 64, 0, ctx->stream>>>((uint32_t)len, pk->table);
+    ctx->launches++;
+    e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { cudaFree(pk->table); delete pk; ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
+    *out = pk;
+    return BPP_OK;
+  }
+  // re-encode an affine table
+  static int export_table(bpp_ctx* ctx, const uint32_t* table, uint32_t n, uint8_t* host_out) {
+    BPP_CK(ctx->buf[B_OUT0].ensure((size_t)n * PB));
+    BPP_LAUNCH(points_encode_aff_kernel<C>, ceil_div(n, 64), 64, 0, n, table, ctx->buf[B_OUT0].as<uint8_t>());
+    BPP_CK(cudaMemcpyAsync(host_out, ctx->buf[B_OUT0].p, (size_t)n * PB, cudaMemcpyDeviceToHost, ctx->stream));
+    BPP_CK(cudaStreamSynchronize(ctx->stream));
+    return BPP_OK;
+  }
+  static int pk_export(bpp_ctx* ctx, const bpp_pk* pk, uint8_t* g, uint8_t* h, uint8_t* G, uint8_t* H) {
+    std::vector<uint8_t> all((size_t)pk->n_points() * PB);
+    BPP_TRY(export_table(ctx, pk->table, pk->n_points(), all.data()));
+    memcpy(g, &all[0], PB); memcpy(h, &all[PB], PB);
+    if (pk->len) { memcpy(G, &all[2 * PB], pk->len * PB); memcpy(H, &all[(2 + pk->len) * PB], pk->len * PB); }
+    return BPP_OK;
+  }
+
+  // ---- RangeProver::commit ----------------------------------------------------------------------------
+  static int commit_batch(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out) {
+    if (count == 0) return BPP_OK;
+    if (count > (1u << 26)) return BPP_ERR_LENGTH;
+    const uint32_t n = (uint32_t)count;
+    BPP_TRY(clear_flags(ctx));
+    BPP_CK(ctx->buf[B_IN0].ensure((size_t)n * 8));
+    BPP_CK(ctx->buf[B_IN1].ensure((size_t)n * 32));
+    BPP_CK(ctx->buf[B_SCALARS].ensure((size_t)n * 64));
+    BPP_CK(ctx->buf[B_PIDX].ensure((size_t)n * 8));
+    BPP_CK(ctx->buf[B_OUT0].ensure((size_t)n * PB));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN0].p, v, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, gamma, (size_t)n * 32, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_LAUNCH(commit_terms_kernel<M>, ceil_div(n, 128), 128, 0, n, ctx->buf[B_IN0].as<uint64_t>(), ctx->buf[B_IN1].as<uint32_t>(),
+               ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>(), ctx->buf[B_FLAGS].as<uint8_t>());
+    BPP_TRY(Msm<C>::run(ctx, 2 * n, n, 2, nullptr, pk->table, pk->n_points(), nullptr));
+    BPP_LAUNCH(points_encode_kernel<C>, ceil_div(n, 64), 64, 0, n, ctx->buf[B_RESULTS].as<uint32_t>(), ctx->buf[B_OUT0].as<uint8_t>());
+    BPP_CK(cudaMemcpyAsync(out, ctx->buf[B_OUT0].p, (size_t)n * PB, cudaMemcpyDeviceToHost, ctx->stream));
+    uint8_t bad = 0;
+    BPP_TRY(read_flag(ctx, ctx->buf[B_FLAGS].as<uint8_t>(), &bad));
+    return bad ? BPP_ERR_FORMAT : BPP_OK;
+  }
+
+  // ---- points / MSM -----------------------------------------------------------------------------------
+  static int points_upload(bpp_ctx* ctx, const uint8_t* points, size_t k, bool from_multipliers, bpp_points** out) {
+    if (k == 0 || k > (1u << 26)) return BPP_ERR_LENGTH;
+    const uint32_t n = (uint32_t)k;
+    BPP_TRY(clear_flags(ctx));
+    const size_t in_bytes = from_multipliers ? 32 : PB;
+    BPP_CK(ctx->buf[B_IN0].ensure((size_t)n * in_bytes));
+    BPP_CK(ctx->buf[B_DYN_OK].ensure(n));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN0].p, points, (size_t)n * in_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    bpp_points* pts = new bpp_points();
+    pts->curve = C::CURVE_ID; pts->len = k;
+    cudaError_t e = cudaMalloc(&pts->table, (size_t)n * C::AFF_WORDS * 4);
+    if (e != cudaSuccess) { delete pts; ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
+    int rc = BPP_OK;
+    uint8_t bad = 0;
+    do {
+      if (from_multipliers) {
+        base_mul_kernel<C, M><<<ceil_div(n, 64), 64, 0, ctx->stream>>>(n, ctx->buf[B_IN0].as<uint32_t>(), pts->table, ctx->buf[B_FLAGS].as<uint8_t>());
+      } else {
+        points_decode_kernel<C><<<ceil_div(n, 64), 64, 0, ctx->stream>>>(n, ctx->buf[B_IN0].as<uint8_t>(), pts->table, ctx->buf[B_DYN_OK].as<uint8_t>());
+        any_zero_kernel<<<ceil_div(n, 256), 256, 0, ctx->stream>>>(n, ctx->buf[B_DYN_OK].as<uint8_t>(), ctx->buf[B_FLAGS].as<uint8_t>());
+        ctx->launches++;
+      }
+      ctx->launches++;
+      rc = read_flag(ctx, ctx->buf[B_FLAGS].as<uint8_t>(), &bad);
+    } while (0);
+    if (rc == BPP_OK && bad) rc = BPP_ERR_FORMAT;
+    if (rc != BPP_OK) { cudaFree(pts->table); delete pts; return rc; }
+    *out = pts;
+    return BPP_OK;
+  }
+  // scalars already on device (n_jobs*k); result: n_jobs extended points in B_RESULTS
+  static int msm_prepared_core(bpp_ctx* ctx, const bpp_points* pts, const uint32_t* d_scalars, size_t k, size_t n_jobs) {
+    if (k == 0 || k > pts->len || n_jobs == 0 || k * n_jobs > (1ull << 27)) return BPP_ERR_LENGTH;
+    const uint32_t T = (uint32_t)(k * n_jobs);
+    BPP_CK(ctx->buf[B_SCALARS].ensure((size_t)T * 32));
+    BPP_CK(ctx->buf[B_PIDX].ensure((size_t)T * 4));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_SCALARS].p, d_scalars, (size_t)T * 32, cudaMemcpyDeviceToDevice, ctx->stream));
+    BPP_LAUNCH(scalars_check_kernel<M>, ceil_div(T, 256), 256, 0, T, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_FLAGS].as<uint8_t>());
+    BPP_LAUNCH(iota_kernel, ceil_div(T, 256), 256, 0, T, (uint32_t)k, ctx->buf[B_PIDX].as<uint32_t>());
+    return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, pts->table, (uint32_t)pts->len, nullptr);
+  }
+  static int msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out, bool raw) {
+    BPP_TRY(clear_flags(ctx));
+    BPP_CK(ctx->buf[B_IN1].ensure(k * n_jobs * 32));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, scalars, k * n_jobs * 32, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_TRY(msm_prepared_core(ctx, pts, ctx->buf[B_IN1].as<uint32_t>(), k, n_jobs));
+    const uint32_t J = (uint32_t)n_jobs;
+    if (raw) {
+      BPP_CK(cudaMemcpyAsync(out, ctx->buf[B_RESULTS].p, (size_t)J * C::EXT_WORDS * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    } else {
+      BPP_CK(ctx->buf[B_OUT0].ensure((size_t)J * PB));
+      BPP_LAUNCH(points_encode_kernel<C>, ceil_div(J, 64), 64, 0, J, ctx->buf[B_RESULTS].as<uint32_t>(), ctx->buf[B_OUT0].as<uint8_t>());
+      BPP_CK(cudaMemcpyAsync(out, ctx->buf[B_OUT0].p, (size_t)J * PB, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    uint8_t bad = 0;
+    BPP_TRY(read_flag(ctx, ctx->buf[B_FLAGS].as<uint8_t>(), &bad));
+    return bad ? BPP_ERR_FORMAT : BPP_OK;
+  }
+  static int msm_prepared_dev(bpp_ctx* ctx, const bpp_points* pts, const void* d_scalars, size_t k, size_t n_jobs, void* d_out) {
+    BPP_TRY(clear_flags(ctx));
+    BPP_TRY(msm_prepared_core(ctx, pts, reinterpret_cast<const uint32_t*>(d_scalars), k, n_jobs));
+    const uint32_t J = (uint32_t)n_jobs;
+    BPP_LAUNCH(points_encode_kernel<C>, ceil_div(J, 64), 64, 0, J, ctx->buf[B_RESULTS].as<uint32_t>(), reinterpret_cast<uint8_t*>(d_out));
+    return BPP_OK;
+  }
+  static int msm(bpp_ctx* ctx, const uint8_t* scalars, const uint8_t* points, size_t k, uint8_t* out) {
+    if (k == 0) {  // empty MulVec: Point::zero()
+      bpp_points* one = nullptr;
+      std::vector<uint8_t> z(32, 0), idb(PB);
+      // encode the identity by running a 1-term MSM with scalar 0 against the base point table
+      std::vector<uint8_t> mult(32, 0); mult[0] = 1;
+      BPP_TRY(points_upload(ctx, mult.data(), 1, true, &one));
+      int rc = msm_prepared(ctx, one, z.data(), 1, 1, out, false);
+      cudaFree(one->table); delete one;
+      return rc;
+    }
+    bpp_points* pts = nullptr;
+    BPP_TRY(points_upload(ctx, points, k, false, &pts));
+    int rc = msm_prepared(ctx, pts, scalars, k, 1, out, false);
+    cudaFree(pts->table); delete pts;
+    return rc;
+  }
+  static int points_sum_raw(bpp_ctx* ctx, const uint8_t* raw, size_t count, uint8_t* out) {
+    if (count == 0 || count > (1u << 20)) return BPP_ERR_LENGTH;
+    BPP_CK(ctx->buf[B_EXT].ensure(count * C::EXT_WORDS * 4));
+    BPP_CK(ctx->buf[B_RESULTS].ensure(C::EXT_WORDS * 4));
+    BPP_CK(ctx->buf[B_OUT0].ensure(PB));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_EXT].p, raw, count * C::EXT_WORDS * 4, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_LAUNCH(ext_sum_kernel<C>, 1, 128, 0, (uint32_t)count, ctx->buf[B_EXT].as<uint32_t>(), ctx->buf[B_RESULTS].as<uint32_t>());
+    BPP_LAUNCH(points_encode_kernel<C>, 1, 32, 0, 1u, ctx->buf[B_RESULTS].as<uint32_t>(), ctx->buf[B_OUT0].as<uint8_t>());
+    BPP_CK(cudaMemcpyAsync(out, ctx->buf[B_OUT0].p, PB, cudaMemcpyDeviceToHost, ctx->stream));
+    BPP_CK(cudaStreamSynchronize(ctx->stream));
+    return BPP_OK;
+  }
+
+  // ---- RangeProof::verify (batch) ---------------------------------------------------------------------
+  // mode 1/2: range single / multiple. d_V: count*m encoded commitments; d_proofs: count proofs.
+  // mode 0: standalone WIP verify (count = 1): d_proofs = A_prime | wip proof (same layout as a range proof),
+  //         ext_* = the caller's commitment exponents (device, canonical).
+  static int verify_core(bpp_ctx* ctx, const bpp_pk* pk, uint32_t mode, uint32_t n, uint32_t m, uint32_t count, const uint8_t* d_V,
+                         const uint8_t* d_proofs, size_t proof_len, const uint32_t* ext_Gc, const uint32_t* ext_Hc,
+                         const uint32_t* ext_gc, const uint32_t* ext_Vc, const uint32_t* ext_y, uint8_t* d_verdicts) {
+    VerifyShape vs;
+    vs.N = (uint32_t)pk->len; vs.L = ilog2(vs.N); vs.n = n; vs.m = m; vs.nV = m; vs.mode = mode; vs.n_proofs = count;
+    vs.pk_G0 = 2; vs.pk_H0 = 2 + vs.N; vs.dyn0 = pk->n_points();
+    const uint32_t N = vs.N, L = vs.L, ppp = 2 * L + 3, K = 5 + 2 * L + 2 * N + vs.nV;
+    if ((uint64_t)count * K > (1ull << 27)) { ctx->err = "verify: batch too large"; return BPP_ERR_LENGTH; }
+    const uint32_t n_dyn = count * (ppp + vs.nV);
+    BPP_CK(ctx->buf[B_IN0].ensure((size_t)count * ppp * PB));
+    BPP_CK(ctx->buf[B_DYN].ensure((size_t)n_dyn * C::AFF_WORDS * 4));
+    BPP_CK(ctx->buf[B_DYN_OK].ensure(n_dyn));
+    BPP_CK(ctx->buf[B_FLAGS2].ensure(count));
+    BPP_CK(ctx->buf[B_SCALARS].ensure((size_t)count * K * 32));
+    BPP_CK(ctx->buf[B_PIDX].ensure((size_t)count * K * 4));
+    for (int b = B_TAB0; b <= B_TAB6; b++) BPP_CK(ctx->buf[b].ensure(((size_t)N + 2 * L + vs.nV + 16) * 32));
+    // decode the per-proof points and the commitments into the dynamic table
+    const uint32_t gb = count * ppp * (uint32_t)PB;
+    BPP_LAUNCH(gather_proof_points_kernel, ceil_div(gb, 256), 256, 0, count, ppp * (uint32_t)PB, d_proofs, proof_len, ctx->buf[B_IN0].as<uint8_t>());
+    BPP_LAUNCH(points_decode_kernel<C>, ceil_div(count * ppp, 64), 64, 0, count * ppp, ctx->buf[B_IN0].as<uint8_t>(),
+               ctx->buf[B_DYN].as<uint32_t>(), ctx->buf[B_DYN_OK].as<uint8_t>());
+    if (vs.nV)
+      BPP_LAUNCH(points_decode_kernel<C>, ceil_div(count * vs.nV, 64), 64, 0, count * vs.nV, d_V,
+                 ctx->buf[B_DYN].as<uint32_t>() + (size_t)count * ppp * C::AFF_WORDS, ctx->buf[B_DYN_OK].as<uint8_t>() + (size_t)count * ppp);
+    VerifyTables T;
+    T.S = ctx->buf[B_TAB0].as<uint32_t>(); T.Srev = ctx->buf[B_TAB1].as<uint32_t>(); T.Gc = ctx->buf[B_TAB2].as<uint32_t>();
+    T.Hc = ctx->buf[B_TAB3].as<uint32_t>(); T.Vc = ctx->buf[B_TAB4].as<uint32_t>(); T.misc = ctx->buf[B_TAB5].as<uint32_t>();
+    T.tmp = ctx->buf[B_TAB6].as<uint32_t>();
+    BPP_LAUNCH(verify_tables_kernel<M>, 1, 256, 0, vs, ctx->buf[B_PARAMS].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
+    dim3 grid(ceil_div(K, 128), count);
+    BPP_LAUNCH(verify_scalars_kernel<M>, grid, 128, 0, vs, T, d_proofs, proof_len, (size_t)ppp * PB, ctx->buf[B_SCALARS].as<uint32_t>(),
+               ctx->buf[B_PIDX].as<uint32_t>(), ctx->buf[B_FLAGS2].as<uint8_t>());
+    BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->table, pk->n_points(), ctx->buf[B_DYN].as<uint32_t>()));
+    BPP_LAUNCH(verdict_kernel<C>, ceil_div(count, 128), 128, 0, count, ppp, vs.nV, ctx->buf[B_RESULTS].as<uint32_t>(),
+               ctx->buf[B_DYN_OK].as<uint8_t>(), ctx->buf[B_FLAGS2].as<uint8_t>(), d_verdicts);
+    return BPP_OK;
+  }
+  static int check_range_shape(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count) {
+    if (n == 0 || m == 0 || count == 0 || count > (1u << 24)) return BPP_ERR_LENGTH;
+    const size_t N = n * m;
+    if (N & (N - 1)) return BPP_ERR_NOT_POW2;  // wip.rs:67
+    if (N < 2) return BPP_ERR_LENGTH;
+    if (pk->len != N) { ctx->err = "generator count != n*m"; return BPP_ERR_GENERATORS; }  // range/mod.rs:90-91,252-253
+    return BPP_OK;
+  }
+  static int range_verify_batch_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V,
+                                    const void* d_proofs, const bpp_params* prm, void* d_verdicts, const uint8_t* order_le) {
+    BPP_TRY(check_range_shape(ctx, pk, n, m, count));
+    const uint32_t L = ilog2(n * m);
+    BPP_TRY(load_params(ctx, prm, m == 1, L, order_le));
+    const size_t plen = (2 * (size_t)L + 3) * PB + 96;
+    return verify_core(ctx, pk, m == 1 ? 1 : 2, (uint32_t)n, (uint32_t)m, (uint32_t)count, reinterpret_cast<const uint8_t*>(d_V),
+                       reinterpret_cast<const uint8_t*>(d_proofs), plen, nullptr, nullptr, nullptr, nullptr, nullptr,
+                       reinterpret_cast<uint8_t*>(d_verdicts));
+  }
+  static int range_verify_batch(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint8_t* V, const uint8_t* proofs,
+                                const bpp_params* prm, uint8_t* verdicts, const uint8_t* order_le) {
+    BPP_TRY(check_range_shape(ctx, pk, n, m, count));
+    const size_t plen = (2 * (size_t)ilog2(n * m) + 3) * PB + 96;
+    BPP_CK(ctx->buf[B_IN1].ensure(count * m * PB));
+    BPP_CK(ctx->buf[B_IN2].ensure(count * plen));
+    BPP_CK(ctx->buf[B_IN3].ensure(count));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, V, count * m * PB, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN2].p, proofs, count * plen, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_TRY(range_verify_batch_dev(ctx, pk, n, m, count, ctx->buf[B_IN1].p, ctx->buf[B_IN2].p, prm, ctx->buf[B_IN3].p, order_le));
+    BPP_CK(cudaMemcpyAsync(verdicts, ctx->buf[B_IN3].p, count, cudaMemcpyDeviceToHost, ctx->stream));
+    BPP_CK(cudaStreamSynchronize(ctx->stream));
+    return BPP_OK;
+  }
+
+  // ---- RangeProof::prove (batch) / WeightedInnerProductProof::prove -------------------------------------
+  // mode 1/2: d_v (count*m u64), d_gamma (count*m scalars). mode 0 (count = 1): d_a, d_b, d_ypow (N scalars), d_gamma (1).
+  // d_proofs: count proofs of proof_len bytes; for mode 0 the WIP proof is written at d_proofs (no leading A).
+  static int prove_core(bpp_ctx* ctx, const bpp_pk* pk, uint32_t mode, uint32_t n, uint32_t m, uint32_t count, const uint64_t* d_v,
+                        const uint32_t* d_gamma, const uint32_t* d_a, const uint32_t* d_b, const uint32_t* d_ypow, uint8_t* d_proofs,
+                        size_t proof_len, uint8_t* format_bad) {
+    ProveShape ps;
+    ps.N = (uint32_t)pk->len; ps.L = ilog2(ps.N); ps.n = n; ps.m = m; ps.mode = mode; ps.n_proofs = count;
+    ps.pk_G0 = 2; ps.pk_H0 = 2 + ps.N; ps.dyn0 = pk->n_points();
+    ps.has_A = mode != 0;
+    const uint32_t N = ps.N, L = ps.L, J = ps.has_A + 2 * L + 2;
+    ps.terms_per_proof = ps.has_A * 2 + 2 * L * (N + 2) + (2 * N + 2) + 2;
+    if ((uint64_t)count * ps.terms_per_proof > (1ull << 27)) { ctx->err = "prove: batch too large"; return BPP_ERR_LENGTH; }
+    const uint32_t T_all = count * ps.terms_per_proof;
+    BPP_TRY(clear_flags(ctx));
+    BPP_CK(ctx->buf[B_SCALARS].ensure((size_t)T_all * 32));
+    BPP_CK(ctx->buf[B_PIDX].ensure((size_t)T_all * 4));
+    BPP_CK(ctx->buf[B_JOBSTART].ensure(((size_t)count * J + 1) * 4));
+    BPP_CK(ctx->buf[B_WORK0].ensure((size_t)count * N * 32));
+    BPP_CK(ctx->buf[B_WORK1].ensure((size_t)count * N * 32));
+    BPP_CK(ctx->buf[B_WORK2].ensure((size_t)count * 32));
+    BPP_CK(ctx->buf[B_DYN].ensure((size_t)count * C::AFF_WORDS * 4));
+    BPP_CK(ctx->buf[B_TAB0].ensure((size_t)N * 32));
+    BPP_CK(ctx->buf[B_TAB1].ensure((size_t)N * 32));
+    BPP_CK(ctx->buf[B_TAB2].ensure((size_t)(L + 1) * N * 32));
+    BPP_CK(ctx->buf[B_TAB3].ensure((size_t)(L + 1) * N * 32));
+    BPP_CK(ctx->buf[B_TAB4].ensure((size_t)(4 * L + 4) * 32));
+    BPP_CK(ctx->buf[B_TAB5].ensure((size_t)(PM_HDR + m + 4) * 32));
+    ProveTables T;
+    T.ypow = ctx->buf[B_TAB0].as<uint32_t>(); T.Hexp = ctx->buf[B_TAB1].as<uint32_t>(); T.gcoef = ctx->buf[B_TAB2].as<uint32_t>();
+    T.hcoef = ctx->buf[B_TAB3].as<uint32_t>(); T.rnd = ctx->buf[B_TAB4].as<uint32_t>(); T.misc = ctx->buf[B_TAB5].as<uint32_t>();
+    const uint32_t* params = ctx->buf[B_PARAMS].as<uint32_t>();
+    uint32_t* a = ctx->buf[B_WORK0].as<uint32_t>();
+    uint32_t* b = ctx->buf[B_WORK1].as<uint32_t>();
+    uint32_t* alpha = ctx->buf[B_WORK2].as<uint32_t>();
+    BPP_LAUNCH(prove_tables_kernel<M>, 1, 256, 0, ps, params, d_ypow, T);
+    if (mode == 0) {
+      BPP_LAUNCH(wip_load_kernel<M>, ceil_div(N, 128), 128, 0, N, d_a, d_b, d_gamma, a, b, alpha, ctx->buf[B_FLAGS].as<uint8_t>());
+      BPP_LAUNCH(scalars_check_kernel<M>, ceil_div(N, 128), 128, 0, N, d_ypow, ctx->buf[B_FLAGS].as<uint8_t>());
+    } else {
+      BPP_LAUNCH(range_prove_init_kernel<M>, count, 256, 0, ps, T, params, d_v, d_gamma, a, b, alpha, ctx->buf[B_FLAGS].as<uint8_t>());
+      BPP_LAUNCH(range_bits_sum_kernel<C>, count, 128, 0, ps, d_v, pk->table, ctx->buf[B_DYN].as<uint32_t>());
+    }
+    const size_t scalar_off = (size_t)J * PB;
+    BPP_LAUNCH(wip_prove_kernel<M>, count, 256, 256 * 32, ps, T, params, a, b, alpha, ctx->buf[B_SCALARS].as<uint32_t>(),
+               ctx->buf[B_PIDX].as<uint32_t>(), d_proofs, proof_len, scalar_off);
+    BPP_LAUNCH(prove_jobstart_kernel, ceil_div(count * J + 1, 256), 256, 0, count, L, N, ps.has_A, ps.terms_per_proof,
+               ctx->buf[B_JOBSTART].as<uint32_t>());
+    BPP_TRY(Msm<C>::run(ctx, T_all, count * J, 0, ctx->buf[B_JOBSTART].as<uint32_t>(), pk->table, pk->n_points(),
+                        ctx->buf[B_DYN].as<uint32_t>()));
+    BPP_LAUNCH(encode_into_proofs_kernel<C>, ceil_div(count * J, 64), 64, 0, count, J, ctx->buf[B_RESULTS].as<uint32_t>(), d_proofs, proof_len);
+    // flag [0] set = some input scalar (a, b, y-powers, gamma) was not canonical
+    return read_flag(ctx, ctx->buf[B_FLAGS].as<uint8_t>(), format_bad);
+  }
+  static int range_prove_batch_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_v, const void* d_gamma,
+                                   const bpp_params* prm, void* d_proofs, const uint8_t* order_le) {
+    BPP_TRY(check_range_shape(ctx, pk, n, m, count));
+    const uint32_t L = ilog2(n * m);
+    BPP_TRY(load_params(ctx, prm, m == 1, L, order_le));
+    const size_t plen = (2 * (size_t)L + 3) * PB + 96;
+    uint8_t bad = 0;
+    BPP_TRY(prove_core(ctx, pk, m == 1 ? 1 : 2, (uint32_t)n, (uint32_t)m, (uint32_t)count, reinterpret_cast<const uint64_t*>(d_v),
+                       reinterpret_cast<const uint32_t*>(d_gamma), nullptr, nullptr, nullptr, reinterpret_cast<uint8_t*>(d_proofs), plen, &bad));
+    return bad ? BPP_ERR_FORMAT : BPP_OK;
+  }
+  static int range_prove_batch(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint64_t* v, const uint8_t* gamma,
+                               const bpp_params* prm, uint8_t* proofs, const uint8_t* order_le) {
+    BPP_TRY(check_range_shape(ctx, pk, n, m, count));
+    const size_t plen = (2 * (size_t)ilog2(n * m) + 3) * PB + 96;
+    BPP_CK(ctx->buf[B_IN1].ensure(count * m * 8));
+    BPP_CK(ctx->buf[B_IN2].ensure(count * m * 32));
+    BPP_CK(ctx->buf[B_IN3].ensure(count * plen));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, v, count * m * 8, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN2].p, gamma, count * m * 32, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = range_prove_batch_dev(ctx, pk, n, m, count, ctx->buf[B_IN1].p, ctx->buf[B_IN2].p, prm, ctx->buf[B_IN3].p, order_le);
+    if (rc != BPP_OK) return rc;
+    BPP_CK(cudaMemcpyAsync(proofs, ctx->buf[B_IN3].p, count * plen, cudaMemcpyDeviceToHost, ctx->stream));
+    BPP_CK(cudaStreamSynchronize(ctx->stream));
+    return BPP_OK;
+  }
+
+  // ---- WeightedInnerProductProof::prove / verify (standalone) -----------------------------------------
+  static int check_wip_shape(bpp_ctx* ctx, const bpp_pk* pk) {
+    const size_t N = pk->len;
+    if (N < 2) return BPP_ERR_LENGTH;
+    if (N & (N - 1)) return BPP_ERR_NOT_POW2;  // wip.rs:67
+    return BPP_OK;
+  }
+  static int wip_prove(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* a, const uint8_t* b, const uint8_t* ypow, const uint8_t* gamma,
+                       const bpp_params* prm, uint8_t* proof, size_t* proof_len, const uint8_t* order_le) {
+    BPP_TRY(check_wip_shape(ctx, pk));
+    const size_t N = pk->len;
+    const uint32_t L = ilog2(N);
+    const size_t plen = (2 * (size_t)L + 2) * PB + 96;
+    if (*proof_len < plen) { *proof_len = plen; return BPP_ERR_LENGTH; }
+    BPP_TRY(load_params(ctx, prm, false, L, order_le));
+    BPP_CK(ctx->buf[B_IN0].ensure(N * 32));
+    BPP_CK(ctx->buf[B_IN1].ensure(N * 32));
+    BPP_CK(ctx->buf[B_IN2].ensure(N * 32));
+    BPP_CK(ctx->buf[B_IN3].ensure(32 + plen));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN0].p, a, N * 32, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, b, N * 32, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN2].p, ypow, N * 32, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN3].p, gamma, 32, cudaMemcpyHostToDevice, ctx->stream));
+    uint8_t bad = 0;
+    uint8_t* d_proof = ctx->buf[B_IN3].as<uint8_t>() + 32;
+    BPP_TRY(prove_core(ctx, pk, 0, 0, 0, 1, nullptr, ctx->buf[B_IN3].as<uint32_t>(), ctx->buf[B_IN0].as<uint32_t>(),
+                       ctx->buf[B_IN1].as<uint32_t>(), ctx->buf[B_IN2].as<uint32_t>(), d_proof, plen, &bad));
+    if (bad) return BPP_ERR_FORMAT;
+    BPP_CK(cudaMemcpyAsync(proof, d_proof, plen, cudaMemcpyDeviceToHost, ctx->stream));
+    BPP_CK(cudaStreamSynchronize(ctx->stream));
+    *proof_len = plen;
+    return BPP_OK;
+  }
+  static int wip_verify(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* ypow, const uint8_t* Gc, const uint8_t* Hc, const uint8_t* gc, size_t nV,
+                        const uint8_t* Vc, const uint8_t* A_prime, const uint8_t* V, const uint8_t* proof, size_t proof_len,
+                        const bpp_params* prm, const uint8_t* order_le) {
+    BPP_TRY(check_wip_shape(ctx, pk));
+    const size_t N = pk->len;
+    const uint32_t L = ilog2(N);
+    const size_t wlen = (2 * (size_t)L + 2) * PB + 96;
+    if (proof_len != wlen) return BPP_ERR_FORMAT;  // wrong number of rounds: wip.rs:334-337 reports VerificationError for n != 2^|L_vec|
+    if (nV > (1u << 16)) return BPP_ERR_LENGTH;
+    BPP_TRY(load_params(ctx, prm, false, L, order_le));
+    BPP_TRY(clear_flags(ctx));
+    // scalars: [Gc N][Hc N][Vc nV][gc][y]; bytes: [A_prime | proof][V nV][verdict]
+    const size_t n_sc = 2 * N + nV + 2;
+    BPP_CK(ctx->buf[B_WORK0].ensure(n_sc * 32));
+    BPP_CK(ctx->buf[B_WORK1].ensure(PB + wlen + nV * PB + 16));
+    uint8_t* d_sc = ctx->buf[B_WORK0].as<uint8_t>();
+    uint8_t* d_by = ctx->buf[B_WORK1].as<uint8_t>();
+    BPP_CK(cudaMemcpyAsync(d_sc, Gc, N * 32, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(d_sc + N * 32, Hc, N * 32, cudaMemcpyHostToDevice, ctx->stream));
+    if (nV) BPP_CK(cudaMemcpyAsync(d_sc + 2 * N * 32, Vc, nV * 32, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(d_sc + (2 * N + nV) * 32, gc, 32, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(d_sc + (2 * N + nV + 1) * 32, ypow, 32, cudaMemcpyHostToDevice, ctx->stream));  // y = power_of_y_vec[0], wip.rs:253
+    BPP_CK(cudaMemcpyAsync(d_by, A_prime, PB, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(d_by + PB, proof, wlen, cudaMemcpyHostToDevice, ctx->stream));
+    if (nV) BPP_CK(cudaMemcpyAsync(d_by + PB + wlen, V, nV * PB, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_LAUNCH(scalars_check_kernel<M>, ceil_div((uint32_t)n_sc, 128), 128, 0, (uint32_t)n_sc, reinterpret_cast<const uint32_t*>(d_sc),
+               ctx->buf[B_FLAGS].as<uint8_t>());
+    uint8_t* d_verdict = d_by + PB + wlen + nV * PB;
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(d_sc);
+    BPP_TRY(verify_core(ctx, pk, 0, 0, (uint32_t)nV, 1, d_by + PB + wlen, d_by, PB + wlen, s32, s32 + N * 8, s32 + (2 * N + nV) * 8,
+                        s32 + 2 * N * 8, s32 + (2 * N + nV + 1) * 8, d_verdict));
+    uint8_t res[2] = {0, 0};
+    BPP_CK(cudaMemcpyAsync(&res[0], d_verdict, 1, cudaMemcpyDeviceToHost, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(&res[1], ctx->buf[B_FLAGS].p, 1, cudaMemcpyDeviceToHost, ctx->stream));
+    BPP_CK(cudaStreamSynchronize(ctx->stream));
+    if (res[1]) return BPP_ERR_FORMAT;
+    return res[0];
+  }
+};
+
+}  // namespace bpp

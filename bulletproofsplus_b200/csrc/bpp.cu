@@ -1,0 +1,291 @@
+// libbpp_b200.so — extern "C" surface (include/bpp.h). Dispatches on the curve id to the templated
+// launch sequences in api_impl.cuh. No CPU fallback exists: every entry point needs a live bpp_ctx,
+// and bpp_init fails when there is no CUDA device.
+#include "ed25519.cuh"
+#include "api_impl.cuh"
+#include "debug_ops.cuh"
+
+using namespace bpp;
+
+namespace {
+
+typedef Api<Ed25519, ModEll> ApiRistretto;
+
+const uint8_t ORDER_ELL[32] = {0xed, 0xd3, 0xf5, 0x5c, 0x1a, 0x63, 0x12, 0x58, 0xd6, 0x9c, 0xf7, 0xa2, 0xde, 0xf9, 0xde, 0x14,
+                               0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x10};
+
+int point_bytes(int curve) { return curve == 0 ? 32 : curve == 1 ? 64 : curve == 2 ? 96 : -1; }
+bool pow2(size_t x) { return x && !(x & (x - 1)); }
+
+int set_device(bpp_ctx* ctx) {
+  if (!ctx) return BPP_ERR_NOT_INIT;
+  BPP_CK(cudaSetDevice(ctx->device));
+  return BPP_OK;
+}
+
+// drain the event pairs recorded around the hot kernel
+int drain_hot(bpp_ctx* ctx) {
+  for (auto& pr : ctx->hot_pending) {
+    BPP_CK(cudaEventSynchronize(pr.second));
+    float ms = 0;
+    BPP_CK(cudaEventElapsedTime(&ms, pr.first, pr.second));
+    ctx->hot_ms += ms;
+    cudaEventDestroy(pr.first);
+    cudaEventDestroy(pr.second);
+  }
+  ctx->hot_pending.clear();
+  return BPP_OK;
+}
+
+}  // namespace
+
+#define BPP_ENTER(ctx)            \
+  do {                            \
+    int _rc = set_device(ctx);    \
+    if (_rc != BPP_OK) return _rc; \
+  } while (0)
+
+// `call` uses ApiT
+#define BPP_DISPATCH(curve, call)                                 \
+  switch (curve) {                                                \
+    case BPP_RISTRETTO255: { typedef ApiRistretto ApiT; const uint8_t* order_le = ORDER_ELL; (void)order_le; return call; } \
+    default: ctx->err = "curve not built into this library"; return BPP_ERR_UNSUPPORTED; \
+  }
+
+extern "C" {
+
+int bpp_init(int device, void* cuda_stream, bpp_ctx** out) {
+  if (!out) return BPP_ERR_LENGTH;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) return BPP_ERR_CUDA;  // no device: fail, never fall back
+  if (cudaSetDevice(device) != cudaSuccess) return BPP_ERR_CUDA;
+  bpp_ctx* ctx = new bpp_ctx();
+  ctx->device = device;
+  if (cuda_stream) {
+    ctx->stream = reinterpret_cast<cudaStream_t>(cuda_stream);
+  } else {
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return BPP_ERR_CUDA; }
+    ctx->own_stream = true;
+  }
+  *out = ctx;
+  return BPP_OK;
+}
+
+void bpp_destroy(bpp_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  drain_hot(ctx);
+  for (auto& b : ctx->buf) b.release();
+  if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+const char* bpp_last_error(const bpp_ctx* ctx) { return ctx ? ctx->err.c_str() : "no context"; }
+int bpp_point_bytes(int curve) { return point_bytes(curve); }
+int bpp_raw_point_bytes(int curve) { return curve == 0 ? 128 : -1; }
+size_t bpp_range_proof_len(int curve, size_t n, size_t m) {
+  int pb = point_bytes(curve);
+  if (pb < 0 || !pow2(n * m) || n * m < 2) return 0;
+  return (2 * (size_t)ilog2(n * m) + 3) * pb + 96;
+}
+size_t bpp_wip_proof_len(int curve, size_t len) {
+  int pb = point_bytes(curve);
+  if (pb < 0 || !pow2(len) || len < 2) return 0;
+  return (2 * (size_t)ilog2(len) + 2) * pb + 96;
+}
+uint64_t bpp_kernel_launches(const bpp_ctx* ctx) { return ctx ? ctx->launches : 0; }
+int bpp_sync(bpp_ctx* ctx) {
+  BPP_ENTER(ctx);
+  BPP_CK(cudaStreamSynchronize(ctx->stream));
+  return BPP_OK;
+}
+
+int bpp_pk_new(bpp_ctx* ctx, int curve, size_t len, bpp_pk** out) {
+  BPP_ENTER(ctx);
+  if (!out) return BPP_ERR_LENGTH;
+  BPP_DISPATCH(curve, ApiT::pk_new(ctx, len, out));
+}
+int bpp_pk_export(bpp_ctx* ctx, const bpp_pk* pk, uint8_t* g, uint8_t* h, uint8_t* G, uint8_t* H) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, ApiT::pk_export(ctx, pk, g, h, G, H));
+}
+size_t bpp_pk_len(const bpp_pk* pk) { return pk ? pk->len : 0; }
+void bpp_pk_free(bpp_pk* pk) {
+  if (!pk) return;
+  cudaSetDevice(pk->device);
+  cudaFree(pk->table);
+  delete pk;
+}
+
+int bpp_commit_batch(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out_points) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, ApiT::commit_batch(ctx, pk, v, gamma, count, out_points));
+}
+
+int bpp_msm(bpp_ctx* ctx, int curve, const uint8_t* scalars, const uint8_t* points, size_t k, uint8_t* out_point) {
+  BPP_ENTER(ctx);
+  BPP_DISPATCH(curve, ApiT::msm(ctx, scalars, points, k, out_point));
+}
+int bpp_points_upload(bpp_ctx* ctx, int curve, const uint8_t* points, size_t k, bpp_points** out) {
+  BPP_ENTER(ctx);
+  BPP_DISPATCH(curve, ApiT::points_upload(ctx, points, k, false, out));
+}
+int bpp_points_from_multipliers(bpp_ctx* ctx, int curve, const uint8_t* mult, size_t k, bpp_points** out) {
+  BPP_ENTER(ctx);
+  BPP_DISPATCH(curve, ApiT::points_upload(ctx, mult, k, true, out));
+}
+size_t bpp_points_len(const bpp_points* pts) { return pts ? pts->len : 0; }
+void bpp_points_free(bpp_points* pts) {
+  if (!pts) return;
+  cudaFree(pts->table);
+  delete pts;
+}
+int bpp_msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out_points) {
+  BPP_ENTER(ctx);
+  if (!pts) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pts->curve, ApiT::msm_prepared(ctx, pts, scalars, k, n_jobs, out_points, false));
+}
+int bpp_msm_prepared_dev(bpp_ctx* ctx, const bpp_points* pts, const void* d_scalars, size_t k, size_t n_jobs, void* d_out_points) {
+  BPP_ENTER(ctx);
+  if (!pts) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pts->curve, ApiT::msm_prepared_dev(ctx, pts, d_scalars, k, n_jobs, d_out_points));
+}
+int bpp_msm_prepared_raw(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, uint8_t* out_raw) {
+  BPP_ENTER(ctx);
+  if (!pts) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pts->curve, ApiT::msm_prepared(ctx, pts, scalars, k, 1, out_raw, true));
+}
+int bpp_points_sum_raw(bpp_ctx* ctx, int curve, const uint8_t* raw_points, size_t count, uint8_t* out_point) {
+  BPP_ENTER(ctx);
+  BPP_DISPATCH(curve, ApiT::points_sum_raw(ctx, raw_points, count, out_point));
+}
+
+int bpp_range_prove_batch(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint64_t* v, const uint8_t* gamma,
+                          const bpp_params* params, uint8_t* proofs) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, ApiT::range_prove_batch(ctx, pk, n, m, count, v, gamma, params, proofs, order_le));
+}
+int bpp_range_verify_batch(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint8_t* V, const uint8_t* proofs,
+                           const bpp_params* params, uint8_t* verdicts) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, ApiT::range_verify_batch(ctx, pk, n, m, count, V, proofs, params, verdicts, order_le));
+}
+int bpp_range_prove_batch_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_v, const void* d_gamma,
+                              const bpp_params* params, void* d_proofs) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, ApiT::range_prove_batch_dev(ctx, pk, n, m, count, d_v, d_gamma, params, d_proofs, order_le));
+}
+int bpp_range_verify_batch_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V, const void* d_proofs,
+                               const bpp_params* params, void* d_verdicts) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, ApiT::range_verify_batch_dev(ctx, pk, n, m, count, d_V, d_proofs, params, d_verdicts, order_le));
+}
+int bpp_range_prove(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, const uint64_t* v, const uint8_t* gamma, const bpp_params* params,
+                    uint8_t* proof, size_t* proof_len) {
+  if (!pk || !proof_len) return BPP_ERR_NOT_INIT;
+  size_t need = bpp_range_proof_len(pk->curve, n, m);
+  if (need == 0) return pow2(n * m) ? BPP_ERR_LENGTH : BPP_ERR_NOT_POW2;
+  if (*proof_len < need) { *proof_len = need; return BPP_ERR_LENGTH; }
+  *proof_len = need;
+  return bpp_range_prove_batch(ctx, pk, n, m, 1, v, gamma, params, proof);
+}
+int bpp_range_verify(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, const uint8_t* V, const uint8_t* proof, size_t proof_len,
+                     const bpp_params* params) {
+  if (!pk) return BPP_ERR_NOT_INIT;
+  size_t need = bpp_range_proof_len(pk->curve, n, m);
+  if (need == 0) return pow2(n * m) ? BPP_ERR_LENGTH : BPP_ERR_NOT_POW2;
+  if (proof_len != need) return BPP_ERR_FORMAT;
+  uint8_t verdict = BPP_ERR_CUDA;
+  int rc = bpp_range_verify_batch(ctx, pk, n, m, 1, V, proof, params, &verdict);
+  return rc != BPP_OK ? rc : verdict;
+}
+
+int bpp_wip_prove(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* a, const uint8_t* b, const uint8_t* power_of_y, const uint8_t* gamma,
+                  const bpp_params* params, uint8_t* proof, size_t* proof_len) {
+  BPP_ENTER(ctx);
+  if (!pk || !proof_len) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, ApiT::wip_prove(ctx, pk, a, b, power_of_y, gamma, params, proof, proof_len, order_le));
+}
+int bpp_wip_verify(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* power_of_y, const uint8_t* G_exp_of_commitment,
+                   const uint8_t* H_exp_of_commitment, const uint8_t* g_exp_of_commitment, size_t n_V, const uint8_t* V_exp_of_commitment,
+                   const uint8_t* A_prime, const uint8_t* V, const uint8_t* proof, size_t proof_len, const bpp_params* params) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, ApiT::wip_verify(ctx, pk, power_of_y, G_exp_of_commitment, H_exp_of_commitment, g_exp_of_commitment, n_V,
+                                           V_exp_of_commitment, A_prime, V, proof, proof_len, params, order_le));
+}
+
+int bpp_int_peak_probe(bpp_ctx* ctx, double* wide_imad_per_sec, double* lo_imad_per_sec, double* elapsed_ms) {
+  BPP_ENTER(ctx);
+  cudaDeviceProp prop;
+  BPP_CK(cudaGetDeviceProperties(&prop, ctx->device));
+  const int blocks = prop.multiProcessorCount * 8, threads = 256;
+  const uint32_t iters = 4096;  // 32 multiply-adds per iteration per thread
+  BPP_CK(ctx->buf[B_OUT0].ensure(64));
+  cudaEvent_t e0, e1;
+  BPP_CK(cudaEventCreate(&e0));
+  BPP_CK(cudaEventCreate(&e1));
+  double rate[2] = {0, 0}, total_ms = 0;
+  for (int mode = 0; mode < 2; mode++) {
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; rep++) {  // first repetition is the warm-up
+      BPP_CK(cudaEventRecord(e0, ctx->stream));
+      if (mode == 0) int_peak_kernel<0><<<blocks, threads, 0, ctx->stream>>>(iters, 12345u + rep, ctx->buf[B_OUT0].as<uint64_t>());
+      else int_peak_kernel<1><<<blocks, threads, 0, ctx->stream>>>(iters, 12345u + rep, ctx->buf[B_OUT0].as<uint64_t>());
+      ctx->launches++;
+      BPP_CK(cudaEventRecord(e1, ctx->stream));
+      BPP_CK(cudaEventSynchronize(e1));
+      float ms = 0;
+      BPP_CK(cudaEventElapsedTime(&ms, e0, e1));
+      total_ms += ms;
+      if (rep > 0 && ms < best) best = ms;
+    }
+    rate[mode] = (double)blocks * threads * iters * 32.0 / (best * 1e-3);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (wide_imad_per_sec) *wide_imad_per_sec = rate[0];
+  if (lo_imad_per_sec) *lo_imad_per_sec = rate[1];
+  if (elapsed_ms) *elapsed_ms = total_ms;
+  return BPP_OK;
+}
+
+// test surface: element-wise device arithmetic (see debug_ops.cuh). elem = 32 bytes for field/scalar ops, point bytes for group ops.
+int bpp_debug_op(bpp_ctx* ctx, int curve, int op, size_t n, const uint8_t* a, const uint8_t* b, uint8_t* out, uint8_t* ok) {
+  BPP_ENTER(ctx);
+  if (curve != BPP_RISTRETTO255) return BPP_ERR_UNSUPPORTED;
+  const size_t eb = (op >= 10 && op < 20) ? (size_t)point_bytes(curve) : 32;
+  BPP_CK(ctx->buf[B_IN0].ensure(n * eb));
+  BPP_CK(ctx->buf[B_IN1].ensure(n * eb));
+  BPP_CK(ctx->buf[B_OUT0].ensure(n * eb));
+  BPP_CK(ctx->buf[B_DYN_OK].ensure(n));
+  BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN0].p, a, n * eb, cudaMemcpyHostToDevice, ctx->stream));
+  BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, b, n * eb, cudaMemcpyHostToDevice, ctx->stream));
+  debug_op_kernel<Ed25519, ModEll><<<ceil_div(n, 64), 64, 0, ctx->stream>>>(op, (uint32_t)n, ctx->buf[B_IN0].as<uint8_t>(),
+      ctx->buf[B_IN1].as<uint8_t>(), ctx->buf[B_OUT0].as<uint8_t>(), ctx->buf[B_DYN_OK].as<uint8_t>());
+  ctx->launches++;
+  BPP_CK(cudaGetLastError());
+  BPP_CK(cudaMemcpyAsync(out, ctx->buf[B_OUT0].p, n * eb, cudaMemcpyDeviceToHost, ctx->stream));
+  BPP_CK(cudaMemcpyAsync(ok, ctx->buf[B_DYN_OK].p, n, cudaMemcpyDeviceToHost, ctx->stream));
+  BPP_CK(cudaStreamSynchronize(ctx->stream));
+  return BPP_OK;
+}
+
+int bpp_hot_kernel_stats(bpp_ctx* ctx, double* ms, uint64_t* launches, int reset) {
+  BPP_ENTER(ctx);
+  BPP_TRY(drain_hot(ctx));
+  if (ms) *ms = ctx->hot_ms;
+  if (launches) *launches = ctx->hot_launches;
+  if (reset) { ctx->hot_ms = 0; ctx->hot_launches = 0; }
+  ctx->hot_timing = true;  // timing is armed by the first call
+  return BPP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,200 @@
+// Ristretto255 over edwards25519 (a = -1) for sm_100a: the group behind the C-ABI's curve 0.
+// Replaces the reference's `Point(G1)` wrapper (src/bls12_381/building_block/point/point.rs:11-117)
+// for the north_star's primary group. Device representations:
+//   Ext  : extended coordinates (X:Y:Z:T), 128 B  — accumulators, bucket sums, results
+//   Aff  : affine "Niels" form (y+x, y-x, 2d*x*y), 96 B — every stored/streamed point
+//          (generator tables, decoded proof points); identity is (1, 1, 0)
+// Mixed addition Ext += Aff costs 7 field multiplies, Ext += Ext 9, doubling 4S + 4M.
+// Encoding/decoding: RFC 9496 §4.3.1 / §4.3.2.
+#pragma once
+#include "fe25519.cuh"
+
+namespace bpp {
+
+struct Ed25519 {
+  typedef Fe25519 F;
+  struct Ext { F X, Y, Z, T; };
+  struct Aff { F ypx, ymx, t2d; };
+  static constexpr int CURVE_ID = 0;
+  static constexpr int POINT_BYTES = 32;   // boundary encoding
+  static constexpr int SCALAR_BITS = 253;  // group order ell < 2^253
+  static constexpr int AFF_WORDS = 24;
+  static constexpr int EXT_WORDS = 32;
+  static constexpr const char* NAME = "ristretto255";
+
+  BPP_DEV static F constant(const uint32_t (&c)[8]) {
+    F r;
+#pragma unroll
+    for (int i = 0; i < 8; i++) r.v[i] = c[i];
+    return r;
+  }
+  BPP_DEV static F k_d() {
+    const uint32_t c[8] = {0x135978a3u, 0x75eb4dcau, 0x4141d8abu, 0x00700a4du, 0x7779e898u, 0x8cc74079u, 0x2b6ffe73u, 0x52036ceeu};
+    return constant(c);
+  }
+  BPP_DEV static F k_d2() {
+    const uint32_t c[8] = {0x26b2f159u, 0xebd69b94u, 0x8283b156u, 0x00e0149au, 0xeef3d130u, 0x198e80f2u, 0x56dffce7u, 0x2406d9dcu};
+    return constant(c);
+  }
+  BPP_DEV static F k_sqrt_m1() {
+    const uint32_t c[8] = {0x4a0ea0b0u, 0xc4ee1b27u, 0xad2fe478u, 0x2f431806u, 0x3dfbd7a7u, 0x2b4d0099u, 0x4fc1df0bu, 0x2b832480u};
+    return constant(c);
+  }
+  BPP_DEV static F k_invsqrt_a_minus_d() {
+    const uint32_t c[8] = {0x805d40eau, 0x99c8fdaau, 0x5a4172beu, 0x9d2f1617u, 0xfe01d840u, 0x16c27b91u, 0xcfaffca2u, 0x786c8905u};
+    return constant(c);
+  }
+  // base point (reference: Point::base_point(), point.rs:15-18, for its own group)
+  BPP_DEV static void base(Ext& p) {
+    const uint32_t bx[8] = {0x8f25d51au, 0xc9562d60u, 0x9525a7b2u, 0x692cc760u, 0xfdd6dc5cu, 0xc0a4e231u, 0xcd6e53feu, 0x216936d3u};
+    const uint32_t by[8] = {0x66666658u, 0x66666666u, 0x66666666u, 0x66666666u, 0x66666666u, 0x66666666u, 0x66666666u, 0x66666666u};
+    const uint32_t bt[8] = {0xa5b7dda3u, 0x6dde8ab3u, 0x775152f5u, 0x20f09f80u, 0x64abe37du, 0x66ea4e8eu, 0xd78b7665u, 0x67875f0fu};
+    p.X = constant(bx); p.Y = constant(by); p.T = constant(bt); fe_one(p.Z);
+  }
+
+  BPP_DEV static void set_identity(Ext& p) { fe_zero(p.X); fe_one(p.Y); fe_one(p.Z); fe_zero(p.T); }
+  BPP_DEV static void set_identity(Aff& p) { fe_one(p.ypx); fe_one(p.ymx); fe_zero(p.t2d); }
+
+  // p += q (q affine Niels); neg => p -= q.  madd-2008-hwcd-3, 7M
+  BPP_DEV static void madd(Ext& p, const Aff& q, bool neg) {
+    F a, b, c, d, e, f, g, h, t0, m_minus = q.ymx, m_plus = q.ypx;
+    fe_cmov(m_minus, q.ypx, neg);  // -q = (ymx, ypx, -t2d)
+    fe_cmov(m_plus, q.ymx, neg);
+    fe_sub(t0, p.Y, p.X);
+    fe_mul(a, t0, m_minus);
+    fe_add(t0, p.Y, p.X);
+    fe_mul(b, t0, m_plus);
+    fe_mul(c, p.T, q.t2d);
+    fe_dbl(d, p.Z);
+    fe_sub(e, b, a);
+    fe_add(h, b, a);
+    if (neg) { fe_add(f, d, c); fe_sub(g, d, c); }
+    else     { fe_sub(f, d, c); fe_add(g, d, c); }
+    fe_mul(p.X, e, f);
+    fe_mul(p.Y, g, h);
+    fe_mul(p.T, e, h);
+    fe_mul(p.Z, f, g);
+  }
+  // p += q, both extended; complete (add-2008-hwcd-3 with k = 2d), 9M
+  BPP_DEV static void add(Ext& p, const Ext& q) {
+    F a, b, c, d, e, f, g, h, t0, t1;
+    fe_sub(t0, p.Y, p.X); fe_sub(t1, q.Y, q.X); fe_mul(a, t0, t1);
+    fe_add(t0, p.Y, p.X); fe_add(t1, q.Y, q.X); fe_mul(b, t0, t1);
+    fe_mul(t0, p.T, q.T); fe_mul(c, t0, k_d2());
+    fe_mul(t0, p.Z, q.Z); fe_dbl(d, t0);
+    fe_sub(e, b, a); fe_sub(f, d, c); fe_add(g, d, c); fe_add(h, b, a);
+    fe_mul(p.X, e, f); fe_mul(p.Y, g, h); fe_mul(p.T, e, h); fe_mul(p.Z, f, g);
+  }
+  // dbl-2008-hwcd, a = -1
+  BPP_DEV static void dbl(Ext& p) {
+    F a, b, c, e, g, f, h, t0;
+    fe_sqr(a, p.X); fe_sqr(b, p.Y);
+    fe_sqr(t0, p.Z); fe_dbl(c, t0);
+    fe_add(t0, p.X, p.Y); fe_sqr(e, t0); fe_sub(e, e, a); fe_sub(e, e, b);  // E = 2XY
+    fe_sub(g, b, a);       // G = D + B = B - A
+    fe_sub(f, g, c);       // F = G - C
+    fe_add(h, a, b); fe_neg(h, h);  // H = D - B = -A - B
+    fe_mul(p.X, e, f); fe_mul(p.Y, g, h); fe_mul(p.T, e, h); fe_mul(p.Z, f, g);
+  }
+  BPP_DEV static void neg(Ext& p) { fe_neg(p.X, p.X); fe_neg(p.T, p.T); }
+
+  // Ext -> Aff (one inversion)
+  __device__ static void to_aff(Aff& o, const Ext& p) {
+    F zi, x, y, t;
+    fe_invert(zi, p.Z);
+    fe_mul(x, p.X, zi); fe_mul(y, p.Y, zi);
+    fe_add(o.ypx, y, x); fe_sub(o.ymx, y, x);
+    fe_mul(t, x, y); fe_mul(o.t2d, t, k_d2());
+  }
+  BPP_DEV static void aff_to_ext(Ext& p, const Aff& q) {  // via identity + q (7M; only used off the hot path)
+    set_identity(p);
+    madd(p, q, false);
+  }
+
+  // the group identity in Ristretto: the coset {X == 0 or Y == 0} (RFC 9496 §4.3.3 applied to (0,1))
+  BPP_DEV static bool is_identity(const Ext& p) { return fe_is_zero(p.X) || fe_is_zero(p.Y); }
+
+  // RFC 9496 §4.2 SQRT_RATIO_M1
+  __device__ static bool sqrt_ratio_m1(F& r, const F& u, const F& v) {
+    F v3, v7, t, check, nu, nui;
+    fe_sqr(t, v); fe_mul(v3, t, v);
+    fe_sqr(t, v3); fe_mul(v7, t, v);
+    fe_mul(t, u, v7); fe_pow22523(t, t);
+    fe_mul(r, u, v3); fe_mul(r, r, t);
+    fe_sqr(t, r); fe_mul(check, v, t);
+    fe_neg(nu, u); fe_mul(nui, nu, k_sqrt_m1());
+    bool correct = fe_eq(check, u), flipped = fe_eq(check, nu), flipped_i = fe_eq(check, nui);
+    F rp;
+    fe_mul(rp, r, k_sqrt_m1());
+    fe_cmov(r, rp, flipped || flipped_i);
+    fe_cneg(r, fe_is_neg(r));
+    return correct || flipped;
+  }
+
+  // 32 bytes -> Aff; false on any of the RFC 9496 §4.3.1 failure conditions
+  __device__ static bool decode(Aff& o, const uint8_t* b) {
+    F s, ss, u1, u2, u2s, v, t, one, invsqrt, den_x, den_y, x, y;
+    fe_one(one);
+    bool ok = fe_from_bytes(s, b);
+    ok = ok && !(s.v[0] & 1u);
+    fe_sqr(ss, s);
+    fe_sub(u1, one, ss); fe_add(u2, one, ss); fe_sqr(u2s, u2);
+    fe_sqr(t, u1); fe_mul(t, t, k_d()); fe_neg(t, t); fe_sub(v, t, u2s);
+    fe_mul(t, v, u2s);
+    bool was_square = sqrt_ratio_m1(invsqrt, one, t);
+    fe_mul(den_x, invsqrt, u2);
+    fe_mul(den_y, invsqrt, den_x); fe_mul(den_y, den_y, v);
+    fe_add(t, s, s); fe_mul(x, t, den_x);
+    fe_cneg(x, fe_is_neg(x));
+    fe_mul(y, u1, den_y);
+    fe_mul(t, x, y);
+    ok = ok && was_square && !fe_is_neg(t) && !fe_is_zero(y);
+    fe_add(o.ypx, y, x); fe_sub(o.ymx, y, x); fe_mul(o.t2d, t, k_d2());
+    if (!ok) set_identity(o);
+    return ok;
+  }
+
+  // Ext -> 32 bytes (RFC 9496 §4.3.2)
+  __device__ static void encode(uint8_t* b, const Ext& p) {
+    F u1, u2, t, invsqrt, den1, den2, z_inv, ix0, iy0, ench, x, y, den_inv, s, one;
+    fe_one(one);
+    fe_add(t, p.Z, p.Y); fe_sub(u1, p.Z, p.Y); fe_mul(u1, t, u1);
+    fe_mul(u2, p.X, p.Y);
+    fe_sqr(t, u2); fe_mul(t, t, u1);
+    sqrt_ratio_m1(invsqrt, one, t);
+    fe_mul(den1, invsqrt, u1); fe_mul(den2, invsqrt, u2);
+    fe_mul(z_inv, den1, den2); fe_mul(z_inv, z_inv, p.T);
+    fe_mul(ix0, p.X, k_sqrt_m1()); fe_mul(iy0, p.Y, k_sqrt_m1());
+    fe_mul(ench, den1, k_invsqrt_a_minus_d());
+    fe_mul(t, p.T, z_inv);
+    bool rotate = fe_is_neg(t);
+    x = p.X; y = p.Y; den_inv = den2;
+    fe_cmov(x, iy0, rotate); fe_cmov(y, ix0, rotate); fe_cmov(den_inv, ench, rotate);
+    fe_mul(t, x, z_inv);
+    fe_cneg(y, fe_is_neg(t));
+    fe_sub(t, p.Z, y); fe_mul(s, den_inv, t);
+    fe_cneg(s, fe_is_neg(s));
+    fe_to_bytes(b, s);
+  }
+};
+
+// 128-bit vectorised global loads/stores of whole points (AoS, 32-byte aligned)
+template <int WORDS, class T>
+BPP_DEV void load_words(T& dst, const void* src) {
+  const uint4* s = reinterpret_cast<const uint4*>(src);
+  uint32_t* d = reinterpret_cast<uint32_t*>(&dst);
+#pragma unroll
+  for (int i = 0; i < WORDS / 4; i++) {
+    uint4 q = __ldg(s + i);
+    d[4 * i] = q.x; d[4 * i + 1] = q.y; d[4 * i + 2] = q.z; d[4 * i + 3] = q.w;
+  }
+}
+template <int WORDS, class T>
+BPP_DEV void store_words(void* dst, const T& src) {
+  uint4* d = reinterpret_cast<uint4*>(dst);
+  const uint32_t* s = reinterpret_cast<const uint32_t*>(&src);
+#pragma unroll
+  for (int i = 0; i < WORDS / 4; i++) d[i] = make_uint4(s[4 * i], s[4 * i + 1], s[4 * i + 2], s[4 * i + 3]);
+}
+
+}  // namespace bpp

@@ -1,0 +1,140 @@
+/* bpp.h — C ABI of the B200-native Bulletproofs+ hot path (libbpp_b200.so).
+ *
+ * Drop-in boundary for gogoex/BulletProofsPlus: each entry point replaces one function of the
+ * reference crate (paths relative to the reference's src/). A Rust `bpp-sys` crate binds exactly
+ * these symbols. No torch / C++ types cross this boundary; every buffer is
+ * caller-owned; the library owns only the opaque handles. Nothing here falls back to the CPU: with
+ * no CUDA device bpp_init fails with BPP_ERR_CUDA.
+ *
+ * Encodings
+ *   scalar           32 bytes little-endian, canonical (< group order), else BPP_ERR_FORMAT
+ *   point, curve 0   Ristretto255: 32-byte canonical encoding (RFC 9496)
+ *   point, curve 1   secp256k1: x||y, 32+32 bytes little-endian; infinity = 64 zero bytes
+ *   point, curve 2   BLS12-381 G1: x||y, 48+48 bytes little-endian; infinity = 96 zero bytes
+ *   range proof      A | L[0..L) | R[0..L) | wipA | wipB | r' | s' | delta'   (L = log2(n*m))
+ *                    = RangeProof{A, proof: WeightedInnerProductProof{L_vec,R_vec,A,B,r_prime,s_prime,d_prime}}
+ *                      (range/mod.rs:24-28, weighted_inner_product_proof.rs:25-33)
+ *   WIP proof        the same without the leading A
+ */
+#ifndef BPP_H
+#define BPP_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bpp_ctx bpp_ctx;       /* one per host thread / GPU: stream + scratch arena. Not thread-safe.     */
+typedef struct bpp_pk bpp_pk;         /* PublicKey (publickey.rs:13-18): device-resident generator table         */
+typedef struct bpp_points bpp_points; /* a decoded, device-resident point vector for repeated MSMs               */
+
+enum { BPP_RISTRETTO255 = 0, BPP_SECP256K1 = 1, BPP_BLS12_381_G1 = 2 };
+
+enum {
+  BPP_OK = 0,
+  BPP_ERR_VERIFICATION = 1, /* ProofError::VerificationError (errors.rs:17; range/mod.rs:508, wip.rs:326,336) */
+  BPP_ERR_FORMAT = 2,       /* non-canonical scalar / invalid point / wrong proof length                        */
+  BPP_ERR_LENGTH = 3,       /* reference panics: mulvec.rs:23-25, wip.rs:61-64                                   */
+  BPP_ERR_NOT_POW2 = 4,     /* reference panic: wip.rs:67                                                        */
+  BPP_ERR_GENERATORS = 5,   /* reference panics: range/mod.rs:90-91, :252-253                                    */
+  BPP_ERR_NOT_INIT = 6,     /* reference panic: arith.rs:12-14                                                   */
+  BPP_ERR_CUDA = 7,         /* see bpp_last_error                                                                */
+  BPP_ERR_UNSUPPORTED = 8
+};
+
+/* Fiat-Shamir challenges and prover nonces. NULL everywhere below = the constants hard-coded in the
+ * reference snapshot (parity mode): y,z = 7,7 (m == 1) or 12,23 (range/mod.rs:109-110, :278-279);
+ * alpha = 7 / 33 (:94, :256); round e = 7, d_L = 4, d_R = 5 (wip.rs:131, :94-95); r,s,delta,eta =
+ * 33,44,88,123 (:175-178); final e = 99 (:211). The host (Merlin transcript) owns challenge derivation. */
+typedef struct bpp_params {
+  uint8_t y[32], z[32], e_final[32], alpha[32], r[32], s[32], delta[32], eta[32];
+  uint32_t n_rounds;      /* entries in each array below, >= log2(n*m) */
+  const uint8_t* e_round; /* n_rounds * 32 bytes */
+  const uint8_t* d_L;
+  const uint8_t* d_R;
+} bpp_params;
+
+/* ---- context: Arith::init (bls12_381/building_block/arith.rs:9-17) ------------------------------- */
+/* cuda_stream: a cudaStream_t to launch on (e.g. the caller's current stream), or NULL for a private one. */
+int bpp_init(int device, void* cuda_stream, bpp_ctx** out);
+void bpp_destroy(bpp_ctx* ctx);
+const char* bpp_last_error(const bpp_ctx* ctx);
+int bpp_point_bytes(int curve);
+size_t bpp_range_proof_len(int curve, size_t n, size_t m);
+size_t bpp_wip_proof_len(int curve, size_t len);
+uint64_t bpp_kernel_launches(const bpp_ctx* ctx); /* kernels launched by this context so far */
+int bpp_sync(bpp_ctx* ctx);
+
+/* ---- PublicKey::new / fields (publickey.rs:21-48) ------------------------------------------------ */
+int bpp_pk_new(bpp_ctx* ctx, int curve, size_t len, bpp_pk** out);
+int bpp_pk_export(bpp_ctx* ctx, const bpp_pk* pk, uint8_t* g, uint8_t* h, uint8_t* G, uint8_t* H);
+size_t bpp_pk_len(const bpp_pk* pk);
+void bpp_pk_free(bpp_pk* pk);
+
+/* ---- RangeProver::commit / PublicKey::commitment (range/prover.rs:28-42, publickey.rs:50-52) ----- */
+/* V_i = Fr(v_i as i32)*g + gamma_i*h  (the i32 cast of prover.rs:37 is mirrored) */
+int bpp_commit_batch(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out_points);
+
+/* ---- MulVec::calculate (bls12_381/building_block/mulvec.rs:20-33) -------------------------------- */
+int bpp_msm(bpp_ctx* ctx, int curve, const uint8_t* scalars, const uint8_t* points, size_t k, uint8_t* out_point);
+/* decode once, reuse: points stay in HBM as an affine table */
+int bpp_points_upload(bpp_ctx* ctx, int curve, const uint8_t* points, size_t k, bpp_points** out);
+/* the table {mult[i] * g}: synthetic MSM inputs generated on device */
+int bpp_points_from_multipliers(bpp_ctx* ctx, int curve, const uint8_t* mult_scalars, size_t k, bpp_points** out);
+size_t bpp_points_len(const bpp_points* pts);
+void bpp_points_free(bpp_points* pts);
+/* n_jobs independent MSMs over consecutive slices of `scalars`, all against pts[0..k): out = n_jobs points */
+int bpp_msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out_points);
+/* same with device pointers (no host copies, no synchronisation): d_scalars = n_jobs*k*32 B, d_out = n_jobs encodings */
+int bpp_msm_prepared_dev(bpp_ctx* ctx, const bpp_points* pts, const void* d_scalars, size_t k, size_t n_jobs, void* d_out_points);
+/* partial sum over pts[first, first+count) in uncompressed device form (for the multi-GPU point-range split):
+ * out_raw = bpp_raw_point_bytes(curve) bytes; combine the partials with bpp_points_sum_raw */
+int bpp_raw_point_bytes(int curve);
+int bpp_msm_prepared_raw(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, uint8_t* out_raw);
+int bpp_points_sum_raw(bpp_ctx* ctx, int curve, const uint8_t* raw_points, size_t count, uint8_t* out_point);
+
+/* ---- RangeProof::prove / verify (range/mod.rs:31-78) ---------------------------------------------- */
+/* `count` independent proofs, each aggregating m values of n bits against pk (bpp_pk_len(pk) == n*m).
+ * v: count*m values; gamma: count*m scalars; proofs: count * bpp_range_proof_len bytes. */
+int bpp_range_prove_batch(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint64_t* v,
+                          const uint8_t* gamma, const bpp_params* params, uint8_t* proofs);
+/* V: count*m commitments. verdicts[i] = BPP_OK | BPP_ERR_VERIFICATION | BPP_ERR_FORMAT. Returns BPP_OK if the
+ * batch ran (whatever the verdicts). */
+int bpp_range_verify_batch(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint8_t* V,
+                           const uint8_t* proofs, const bpp_params* params, uint8_t* verdicts);
+/* device-pointer variants: inputs already in HBM, outputs left in HBM, asynchronous on the context's stream */
+int bpp_range_prove_batch_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_v,
+                              const void* d_gamma, const bpp_params* params, void* d_proofs);
+int bpp_range_verify_batch_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V,
+                               const void* d_proofs, const bpp_params* params, void* d_verdicts);
+/* single-proof forms; verify returns the verdict */
+int bpp_range_prove(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, const uint64_t* v, const uint8_t* gamma,
+                    const bpp_params* params, uint8_t* proof, size_t* proof_len);
+int bpp_range_verify(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, const uint8_t* V, const uint8_t* proof,
+                     size_t proof_len, const bpp_params* params);
+
+/* ---- WeightedInnerProductProof::prove / verify (weighted_inner_product_proof.rs:36-43, :238-248) -- */
+/* a, b, power_of_y: len scalars each (len = bpp_pk_len(pk)); gamma: one scalar. The reference's `commitment`
+ * argument only feeds a dead update (wip.rs:137-142) and is not part of this ABI. */
+int bpp_wip_prove(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* a, const uint8_t* b, const uint8_t* power_of_y,
+                  const uint8_t* gamma, const bpp_params* params, uint8_t* proof, size_t* proof_len);
+int bpp_wip_verify(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* power_of_y, const uint8_t* G_exp_of_commitment,
+                   const uint8_t* H_exp_of_commitment, const uint8_t* g_exp_of_commitment, size_t n_V,
+                   const uint8_t* V_exp_of_commitment, const uint8_t* A_prime, const uint8_t* V, const uint8_t* proof,
+                   size_t proof_len, const bpp_params* params);
+
+/* ---- measurement support --------------------------------------------------------------------------- */
+/* Integer-pipe microbenchmark: independent IMAD.WIDE.U32 chains on every SM; returns 32x32+64 multiply-adds/s. */
+int bpp_int_peak_probe(bpp_ctx* ctx, double* wide_imad_per_sec, double* lo_imad_per_sec, double* elapsed_ms);
+/* device time (ms, CUDA events on the context's stream) spent in the bucket-accumulation kernel, and its launch
+ * count, since the last reset */
+int bpp_hot_kernel_stats(bpp_ctx* ctx, double* ms, uint64_t* launches, int reset);
+
+/* test surface: element-wise device arithmetic (field ops 0-4, group ops 10-14, scalar-field ops 20-23) */
+int bpp_debug_op(bpp_ctx* ctx, int curve, int op, size_t n, const uint8_t* a, const uint8_t* b, uint8_t* out, uint8_t* ok);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BPP_H */
