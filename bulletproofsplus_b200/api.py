@@ -114,7 +114,7 @@ class PublicKey:
         self.pb = ctx.lib.bpp_point_bytes(curve)
         h = C.c_void_p()
         ctx.check(ctx.lib.bpp_pk_new(ctx.h, curve, length, C.byref(h)), "pk_new")
-        self.h = h
+        self.handle = h
         self._exported = None
 
     @staticmethod
@@ -126,7 +126,7 @@ class PublicKey:
             pb, n = self.pb, self.length
             g, h = C.create_string_buffer(pb), C.create_string_buffer(pb)
             G, H = C.create_string_buffer(max(1, pb * n)), C.create_string_buffer(max(1, pb * n))
-            self.ctx.check(self.ctx.lib.bpp_pk_export(self.ctx.h, self.h, g, h, G, H), "pk_export")
+            self.ctx.check(self.ctx.lib.bpp_pk_export(self.ctx.h, self.handle, g, h, G, H), "pk_export")
             self._exported = (g.raw, h.raw, [G.raw[i * pb:(i + 1) * pb] for i in range(n)], [H.raw[i * pb:(i + 1) * pb] for i in range(n)])
         return self._exported
 
@@ -140,12 +140,12 @@ class PublicKey:
         arr = (C.c_uint64 * n)(*[v & (2**64 - 1) for v in vs])
         out = C.create_string_buffer(max(1, n * self.pb))
         gam = b"".join(_sc(g % ORDERS[self.curve]) for g in gammas)
-        self.ctx.check(self.ctx.lib.bpp_commit_batch(self.ctx.h, self.h, arr, gam, n, out), "commit_batch")
+        self.ctx.check(self.ctx.lib.bpp_commit_batch(self.ctx.h, self.handle, arr, gam, n, out), "commit_batch")
         return [out.raw[i * self.pb:(i + 1) * self.pb] for i in range(n)]
 
     def __del__(self):
         try:
-            self.ctx.lib.bpp_pk_free(self.h)
+            self.ctx.lib.bpp_pk_free(self.handle)
         except Exception:
             pass
 
@@ -196,7 +196,7 @@ class WeightedInnerProductProof:
         ln = C.c_size_t(pk.ctx.lib.bpp_wip_proof_len(pk.curve, n))
         out = C.create_string_buffer(ln.value)
         enc = lambda v: b"".join(_sc(x % q) for x in v)
-        pk.ctx.check(pk.ctx.lib.bpp_wip_prove(pk.ctx.h, pk.h, enc(a_vec), enc(b_vec), enc(power_of_y_vec), _sc(gamma % q), params, out,
+        pk.ctx.check(pk.ctx.lib.bpp_wip_prove(pk.ctx.h, pk.handle, enc(a_vec), enc(b_vec), enc(power_of_y_vec), _sc(gamma % q), params, out,
                                               C.byref(ln)), "wip_prove")
         return WeightedInnerProductProof.from_bytes(out.raw[:ln.value], pk.pb)
 
@@ -206,7 +206,7 @@ class WeightedInnerProductProof:
         q = ORDERS[pk.curve]
         enc = lambda v: b"".join(_sc(x % q) for x in v)
         proof = self.to_bytes()
-        rc = pk.ctx.lib.bpp_wip_verify(pk.ctx.h, pk.h, enc(power_of_y_vec), enc(G_exp_of_commitment), enc(H_exp_of_commitment),
+        rc = pk.ctx.lib.bpp_wip_verify(pk.ctx.h, pk.handle, enc(power_of_y_vec), enc(G_exp_of_commitment), enc(H_exp_of_commitment),
                                        _sc(g_exp_of_commitment % q), len(V), enc(V_exp_of_commitment) or None, A_prime,
                                        b"".join(V) or None, proof, len(proof), params)
         _raise_verdict(pk.ctx, rc)
@@ -260,7 +260,7 @@ def prove_batch(pk: PublicKey, n: int, m: int, values, gammas, params: BppParams
     plen = pk.ctx.lib.bpp_range_proof_len(pk.curve, n, m)
     arr = (C.c_uint64 * (count * m))(*[v & (2**64 - 1) for v in values])
     out = C.create_string_buffer(max(1, count * plen))
-    pk.ctx.check(pk.ctx.lib.bpp_range_prove_batch(pk.ctx.h, pk.h, n, m, count, arr, b"".join(_sc(g % q) for g in gammas), params, out),
+    pk.ctx.check(pk.ctx.lib.bpp_range_prove_batch(pk.ctx.h, pk.handle, n, m, count, arr, b"".join(_sc(g % q) for g in gammas), params, out),
                  "range_prove_batch")
     return [out.raw[i * plen:(i + 1) * plen] for i in range(count)]
 
@@ -274,7 +274,7 @@ def verify_batch(pk: PublicKey, n: int, m: int, proofs, commitments, params: Bpp
         raise FormatError("wrong proof length")
     out = C.create_string_buffer(max(1, count))
     V = b"".join(b"".join(c) for c in commitments)
-    pk.ctx.check(pk.ctx.lib.bpp_range_verify_batch(pk.ctx.h, pk.h, n, m, count, V, b"".join(proofs), params, out), "range_verify_batch")
+    pk.ctx.check(pk.ctx.lib.bpp_range_verify_batch(pk.ctx.h, pk.handle, n, m, count, V, b"".join(proofs), params, out), "range_verify_batch")
     return list(out.raw[:count])
 
 
