@@ -178,7 +178,11 @@ def main():
     dev = torch.device("cuda", local_rank)
     from bulletproofsplus_b200 import api, _lib
     import ctypes as C
-    stream = torch.cuda.current_stream()
+    # a non-default torch stream, made current: the library launches on exactly this stream, so torch.cuda.Event
+    # records on it bracket the library's kernels (the legacy default stream has handle 0 = "make a private stream")
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     ctx = api.Context(local_rank, stream.cuda_stream)
     lib, B, K_steps = ctx.lib, args.batch, args.steps
     NM = N_BITS * M_AGG
