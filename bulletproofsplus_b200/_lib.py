@@ -7,7 +7,7 @@ import os
 import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO = os.path.join(HERE, "libbpp_b200.so")
+SO = os.environ.get("BPP_LIB") or os.path.join(HERE, "libbpp_b200.so")  # BPP_LIB: kernel-variant experiments only
 
 RISTRETTO255, SECP256K1, BLS12_381_G1 = 0, 1, 2
 OK, ERR_VERIFICATION, ERR_FORMAT, ERR_LENGTH, ERR_NOT_POW2, ERR_GENERATORS, ERR_NOT_INIT, ERR_CUDA, ERR_UNSUPPORTED = range(9)

@@ -20,7 +20,7 @@ __global__ void prove_jobstart_kernel(uint32_t n_proofs, uint32_t L, uint32_t N,
   if (t > n_proofs * J) return;
   if (t == n_proofs * J) { job_start[t] = n_proofs * terms_per_proof; return; }
   uint32_t p = t / J, k = t % J, off = 0;
-  if (has_A) { if (k == 0) { job_start[t] = p * terms_per_proof; return; } off = 2; k -= 1; }
+  if (has_A) { if (k == 0) { job_start[t] = p * terms_per_proof; return; } off = 1; k -= 1; }
   if (k < 2 * L) off += k * (N + 2);
   else if (k == 2 * L) off += 2 * L * (N + 2);
   else off += 2 * L * (N + 2) + 2 * N + 2;
@@ -49,6 +49,10 @@ struct Api {
       memcpy(&h[(size_t)(P_FIXED + 2 * L) * 32], prm->d_R, (size_t)L * 32);
       for (size_t i = 0; i < P_FIXED + 3 * (size_t)L; i++)
         if (!host_scalar_ok(&h[i * 32], order_le)) { ctx->err = "params: non-canonical scalar"; return BPP_ERR_FORMAT; }
+      auto is_zero = [&](size_t slot) { for (int b = 0; b < 32; b++) if (h[slot * 32 + b]) return false; return true; };
+      bool zero_challenge = is_zero(P_Y) || is_zero(P_EFINAL);
+      for (uint32_t k = 0; k < L; k++) zero_challenge = zero_challenge || is_zero(P_FIXED + k);
+      if (zero_challenge) { ctx->err = "params: a challenge is zero (not invertible)"; return BPP_ERR_FORMAT; }
     }
     BPP_CK(ctx->buf[B_PARAMS].ensure(h.size()));
     BPP_CK(cudaMemcpyAsync(ctx->buf[B_PARAMS].p, h.data(), h.size(), cudaMemcpyHostToDevice, ctx->stream));
@@ -67,16 +71,31 @@ struct Api {
   }
 
   // ---- PublicKey::new ---------------------------------------------------------------------------------
+  static void pk_release(bpp_pk* pk) {
+    if (pk->table) cudaFree(pk->table);
+    if (pk->wtab) cudaFree(pk->wtab);
+    if (pk->comb) cudaFree(pk->comb);
+    delete pk;
+  }
   static int pk_new(bpp_ctx* ctx, size_t len, bpp_pk** out) {
-    if (len > (1u << 24)) return BPP_ERR_LENGTH;
+    if (len > (1u << 22)) return BPP_ERR_LENGTH;
     bpp_pk* pk = new bpp_pk();
     pk->curve = C::CURVE_ID; pk->len = len; pk->device = ctx->device;
-    cudaError_t e = cudaMalloc(&pk->table, (size_t)pk->n_points() * C::AFF_WORDS * 4);
-    if (e != cudaSuccess) { delete pk; ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
-    pk_gen_kernel<C><<<ceil_div(pk->n_points(), 64), 64, 0, ctx->stream>>>((uint32_t)len, pk->table);
-    ctx->launches++;
+    const uint32_t np = pk->n_points();
+    // window width for jobs of about 1.5 * len terms (L/R jobs have len + 2, the verifier and the final A 2 * len + 2)
+    pk->cA = choose_window_fixed(len + len / 2 + 2, C::SCALAR_BITS);
+    pk->WA = (C::SCALAR_BITS + 1 + pk->cA - 1) / pk->cA;
+    pk->comb_w = (C::SCALAR_BITS + 1 + COMB_C - 1) / COMB_C;
+    cudaError_t e = cudaMalloc(&pk->table, (size_t)np * C::AFF_WORDS * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&pk->wtab, (size_t)np * pk->WA * C::AFF_WORDS * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&pk->comb, (size_t)2 * pk->comb_w * COMB_D * C::AFF_WORDS * 4);
+    if (e != cudaSuccess) { pk_release(pk); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
+    pk_gen_kernel<C><<<ceil_div(np, 64), 64, 0, ctx->stream>>>((uint32_t)len, pk->table);
+    wtab_build_kernel<C><<<ceil_div(np, 32), 32, 0, ctx->stream>>>(np, pk->cA, pk->WA, pk->table, pk->wtab);
+    comb_build_kernel<C><<<ceil_div(2 * pk->comb_w * COMB_D, 64), 64, 0, ctx->stream>>>(pk->comb_w, pk->table, pk->comb);
+    ctx->launches += 3;
     e = cudaStreamSynchronize(ctx->stream);
-    if (e != cudaSuccess) { cudaFree(pk->table); delete pk; ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
+    if (e != cudaSuccess) { pk_release(pk); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
     *out = pk;
     return BPP_OK;
   }
@@ -111,7 +130,9 @@ struct Api {
     BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, gamma, (size_t)n * 32, cudaMemcpyHostToDevice, ctx->stream));
     BPP_LAUNCH(commit_terms_kernel<M>, ceil_div(n, 128), 128, 0, n, ctx->buf[B_IN0].as<uint64_t>(), ctx->buf[B_IN1].as<uint32_t>(),
                ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>(), ctx->buf[B_FLAGS].as<uint8_t>());
-    BPP_TRY(Msm<C>::run(ctx, 2 * n, n, 2, nullptr, pk->table, pk->n_points(), nullptr));
+    BPP_CK(ctx->buf[B_RESULTS].ensure((size_t)n * C::EXT_WORDS * 4));
+    BPP_LAUNCH(comb_eval_kernel<C>, ceil_div(n, 128), 128, 0, n, pk->comb_w, ctx->buf[B_SCALARS].as<uint32_t>(), pk->comb,
+               ctx->buf[B_RESULTS].as<uint32_t>());
     BPP_LAUNCH(points_encode_kernel<C>, ceil_div(n, 64), 64, 0, n, ctx->buf[B_RESULTS].as<uint32_t>(), ctx->buf[B_OUT0].as<uint8_t>());
     BPP_CK(cudaMemcpyAsync(out, ctx->buf[B_OUT0].p, (size_t)n * PB, cudaMemcpyDeviceToHost, ctx->stream));
     uint8_t bad = 0;
@@ -159,7 +180,7 @@ struct Api {
     BPP_CK(cudaMemcpyAsync(ctx->buf[B_SCALARS].p, d_scalars, (size_t)T * 32, cudaMemcpyDeviceToDevice, ctx->stream));
     BPP_LAUNCH(scalars_check_kernel<M>, ceil_div(T, 256), 256, 0, T, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_FLAGS].as<uint8_t>());
     BPP_LAUNCH(iota_kernel, ceil_div(T, 256), 256, 0, T, (uint32_t)k, ctx->buf[B_PIDX].as<uint32_t>());
-    return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, pts->table, (uint32_t)pts->len, nullptr);
+    return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, nullptr, 0, 0, 0, pts->table, (uint32_t)k);
   }
   static int msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out, bool raw) {
     BPP_TRY(clear_flags(ctx));
@@ -234,7 +255,11 @@ struct Api {
     BPP_CK(ctx->buf[B_FLAGS2].ensure(count));
     BPP_CK(ctx->buf[B_SCALARS].ensure((size_t)count * K * 32));
     BPP_CK(ctx->buf[B_PIDX].ensure((size_t)count * K * 4));
-    for (int b = B_TAB0; b <= B_TAB6; b++) BPP_CK(ctx->buf[b].ensure(((size_t)N + 2 * L + vs.nV + 16) * 32));
+    BPP_CK(ctx->buf[B_TAB0].ensure((size_t)K * 32));
+    BPP_CK(ctx->buf[B_TAB1].ensure((size_t)K * 32));
+    BPP_CK(ctx->buf[B_TAB2].ensure(((size_t)N + 64) * 32));
+    BPP_CK(ctx->buf[B_TAB3].ensure(((size_t)vs.m + 2) * 32));
+    BPP_CK(ctx->buf[B_TAB4].ensure((size_t)count * 128));
     // decode the per-proof points and the commitments into the dynamic table
     const uint32_t gb = count * ppp * (uint32_t)PB;
     BPP_LAUNCH(gather_proof_points_kernel, ceil_div(gb, 256), 256, 0, count, ppp * (uint32_t)PB, d_proofs, proof_len, ctx->buf[B_IN0].as<uint8_t>());
@@ -244,14 +269,15 @@ struct Api {
       BPP_LAUNCH(points_decode_kernel<C>, ceil_div(count * vs.nV, 64), 64, 0, count * vs.nV, d_V,
                  ctx->buf[B_DYN].as<uint32_t>() + (size_t)count * ppp * C::AFF_WORDS, ctx->buf[B_DYN_OK].as<uint8_t>() + (size_t)count * ppp);
     VerifyTables T;
-    T.S = ctx->buf[B_TAB0].as<uint32_t>(); T.Srev = ctx->buf[B_TAB1].as<uint32_t>(); T.Gc = ctx->buf[B_TAB2].as<uint32_t>();
-    T.Hc = ctx->buf[B_TAB3].as<uint32_t>(); T.Vc = ctx->buf[B_TAB4].as<uint32_t>(); T.misc = ctx->buf[B_TAB5].as<uint32_t>();
-    T.tmp = ctx->buf[B_TAB6].as<uint32_t>();
-    BPP_LAUNCH(verify_tables_kernel<M>, 1, 256, 0, vs, ctx->buf[B_PARAMS].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
-    dim3 grid(ceil_div(K, 128), count);
-    BPP_LAUNCH(verify_scalars_kernel<M>, grid, 128, 0, vs, T, d_proofs, proof_len, (size_t)ppp * PB, ctx->buf[B_SCALARS].as<uint32_t>(),
-               ctx->buf[B_PIDX].as<uint32_t>(), ctx->buf[B_FLAGS2].as<uint8_t>());
-    BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->table, pk->n_points(), ctx->buf[B_DYN].as<uint32_t>()));
+    T.Tmul = ctx->buf[B_TAB0].as<uint32_t>(); T.Tadd = ctx->buf[B_TAB1].as<uint32_t>(); T.tmp = ctx->buf[B_TAB2].as<uint32_t>();
+    T.zpow = ctx->buf[B_TAB3].as<uint32_t>();
+    uint32_t* xs = ctx->buf[B_TAB4].as<uint32_t>();
+    BPP_LAUNCH(verify_tables_kernel<M>, 1, VT_THREADS, 0, vs, ctx->buf[B_PARAMS].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
+    BPP_LAUNCH(verify_proof_scalars_kernel<M>, ceil_div(count, 128), 128, 0, count, d_proofs, proof_len, (size_t)ppp * PB, xs,
+               ctx->buf[B_FLAGS2].as<uint8_t>());
+    dim3 grid(ceil_div(K, 256), count);
+    BPP_LAUNCH(verify_scalars_kernel<M>, grid, 256, 0, vs, T, xs, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>());
+    BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), ppp + vs.nV));
     BPP_LAUNCH(verdict_kernel<C>, ceil_div(count, 128), 128, 0, count, ppp, vs.nV, ctx->buf[B_RESULTS].as<uint32_t>(),
                ctx->buf[B_DYN_OK].as<uint8_t>(), ctx->buf[B_FLAGS2].as<uint8_t>(), d_verdicts);
     return BPP_OK;
@@ -300,7 +326,7 @@ struct Api {
     ps.pk_G0 = 2; ps.pk_H0 = 2 + ps.N; ps.dyn0 = pk->n_points();
     ps.has_A = mode != 0;
     const uint32_t N = ps.N, L = ps.L, J = ps.has_A + 2 * L + 2;
-    ps.terms_per_proof = ps.has_A * 2 + 2 * L * (N + 2) + (2 * N + 2) + 2;
+    ps.terms_per_proof = ps.has_A + 2 * L * (N + 2) + (2 * N + 2) + 2;
     if ((uint64_t)count * ps.terms_per_proof > (1ull << 27)) { ctx->err = "prove: batch too large"; return BPP_ERR_LENGTH; }
     const uint32_t T_all = count * ps.terms_per_proof;
     BPP_TRY(clear_flags(ctx));
@@ -310,7 +336,7 @@ struct Api {
     BPP_CK(ctx->buf[B_WORK0].ensure((size_t)count * N * 32));
     BPP_CK(ctx->buf[B_WORK1].ensure((size_t)count * N * 32));
     BPP_CK(ctx->buf[B_WORK2].ensure((size_t)count * 32));
-    BPP_CK(ctx->buf[B_DYN].ensure((size_t)count * C::AFF_WORDS * 4));
+    BPP_CK(ctx->buf[B_EXT].ensure((size_t)count * C::EXT_WORDS * 4));
     BPP_CK(ctx->buf[B_TAB0].ensure((size_t)N * 32));
     BPP_CK(ctx->buf[B_TAB1].ensure((size_t)N * 32));
     BPP_CK(ctx->buf[B_TAB2].ensure((size_t)(L + 1) * N * 32));
@@ -330,16 +356,17 @@ struct Api {
       BPP_LAUNCH(scalars_check_kernel<M>, ceil_div(N, 128), 128, 0, N, d_ypow, ctx->buf[B_FLAGS].as<uint8_t>());
     } else {
       BPP_LAUNCH(range_prove_init_kernel<M>, count, 256, 0, ps, T, params, d_v, d_gamma, a, b, alpha, ctx->buf[B_FLAGS].as<uint8_t>());
-      BPP_LAUNCH(range_bits_sum_kernel<C>, count, 128, 0, ps, d_v, pk->table, ctx->buf[B_DYN].as<uint32_t>());
+      BPP_LAUNCH(range_bits_sum_kernel<C>, count, 128, 0, ps, d_v, pk->table, ctx->buf[B_EXT].as<uint32_t>());
     }
     const size_t scalar_off = (size_t)J * PB;
     BPP_LAUNCH(wip_prove_kernel<M>, count, 256, 256 * 32, ps, T, params, a, b, alpha, ctx->buf[B_SCALARS].as<uint32_t>(),
                ctx->buf[B_PIDX].as<uint32_t>(), d_proofs, proof_len, scalar_off);
     BPP_LAUNCH(prove_jobstart_kernel, ceil_div(count * J + 1, 256), 256, 0, count, L, N, ps.has_A, ps.terms_per_proof,
                ctx->buf[B_JOBSTART].as<uint32_t>());
-    BPP_TRY(Msm<C>::run(ctx, T_all, count * J, 0, ctx->buf[B_JOBSTART].as<uint32_t>(), pk->table, pk->n_points(),
-                        ctx->buf[B_DYN].as<uint32_t>()));
-    BPP_LAUNCH(encode_into_proofs_kernel<C>, ceil_div(count * J, 64), 64, 0, count, J, ctx->buf[B_RESULTS].as<uint32_t>(), d_proofs, proof_len);
+    BPP_TRY(Msm<C>::run(ctx, T_all, count * J, 0, ctx->buf[B_JOBSTART].as<uint32_t>(), pk->wtab, pk->n_points(), pk->cA, pk->WA, nullptr, 0));
+    // job 0 of a range proof is alpha * h; RangeProof.A = that + sum(bit ? G_i : -H_i) (range/mod.rs:98-106 / :260-277)
+    BPP_LAUNCH(encode_into_proofs_kernel<C>, ceil_div(count * J, 64), 64, 0, count, J, ctx->buf[B_RESULTS].as<uint32_t>(),
+               ps.has_A ? ctx->buf[B_EXT].as<uint32_t>() : nullptr, d_proofs, proof_len);
     // flag [0] set = some input scalar (a, b, y-powers, gamma) was not canonical
     return read_flag(ctx, ctx->buf[B_FLAGS].as<uint8_t>(), format_bad);
   }

@@ -115,7 +115,9 @@ size_t bpp_pk_len(const bpp_pk* pk) { return pk ? pk->len : 0; }
 void bpp_pk_free(bpp_pk* pk) {
   if (!pk) return;
   cudaSetDevice(pk->device);
-  cudaFree(pk->table);
+  if (pk->table) cudaFree(pk->table);
+  if (pk->wtab) cudaFree(pk->wtab);
+  if (pk->comb) cudaFree(pk->comb);
   delete pk;
 }
 

@@ -2,8 +2,10 @@
 // Replaces the reference's `Point(G1)` wrapper (src/bls12_381/building_block/point/point.rs:11-117)
 // for the north_star's primary group. Device representations:
 //   Ext  : extended coordinates (X:Y:Z:T), 128 B  — accumulators, bucket sums, results
-//   Aff  : affine "Niels" form (y+x, y-x, 2d*x*y), 96 B — every stored/streamed point
-//          (generator tables, decoded proof points); identity is (1, 1, 0)
+//   Aff  : affine "Niels" form (y+x, y-x, 2d*x*y, -2d*x*y), 128 B = one cache line — every stored/streamed
+//          point (generator and window tables, decoded proof points); identity is (1, 1, 0, 0).
+//          -Q = (y-x, y+x, -2dxy, 2dxy): subtracting a table point is pure ADDRESS selection in
+//          madd_ptr (no SEL / negation instructions in the hot loop).
 // Mixed addition Ext += Aff costs 7 field multiplies, Ext += Ext 9, doubling 4S + 4M.
 // Encoding/decoding: RFC 9496 §4.3.1 / §4.3.2.
 #pragma once
@@ -14,11 +16,11 @@ namespace bpp {
 struct Ed25519 {
   typedef Fe25519 F;
   struct Ext { F X, Y, Z, T; };
-  struct Aff { F ypx, ymx, t2d; };
+  struct Aff { F ypx, ymx, t2d, nt2d; };
   static constexpr int CURVE_ID = 0;
   static constexpr int POINT_BYTES = 32;   // boundary encoding
   static constexpr int SCALAR_BITS = 253;  // group order ell < 2^253
-  static constexpr int AFF_WORDS = 24;
+  static constexpr int AFF_WORDS = 32;
   static constexpr int EXT_WORDS = 32;
   static constexpr const char* NAME = "ristretto255";
 
@@ -53,7 +55,7 @@ struct Ed25519 {
   }
 
   BPP_DEV static void set_identity(Ext& p) { fe_zero(p.X); fe_one(p.Y); fe_one(p.Z); fe_zero(p.T); }
-  BPP_DEV static void set_identity(Aff& p) { fe_one(p.ypx); fe_one(p.ymx); fe_zero(p.t2d); }
+  BPP_DEV static void set_identity(Aff& p) { fe_one(p.ypx); fe_one(p.ymx); fe_zero(p.t2d); fe_zero(p.nt2d); }
 
   // p += q (q affine Niels); neg => p -= q.  madd-2008-hwcd-3, 7M
   BPP_DEV static void madd(Ext& p, const Aff& q, bool neg) {
@@ -74,6 +76,45 @@ struct Ed25519 {
     fe_mul(p.Y, g, h);
     fe_mul(p.T, e, h);
     fe_mul(p.Z, f, g);
+  }
+  BPP_DEV static void load_fe(F& r, const uint32_t* src) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    uint4 a = __ldg(s4), b = __ldg(s4 + 1);
+    r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  }
+  // HOT: p +/-= the table point at q (AFF_WORDS words, 128-byte aligned). neg in {0,1} only moves the three loads.
+  BPP_DEV static void madd_ptr(Ext& p, const uint32_t* q, uint32_t neg) {
+    F a, b, c, d, e, f, g, h, t0, m_minus, m_plus, td;
+    load_fe(m_plus, q + 8 * neg);         // y+x  (or y-x)
+    load_fe(m_minus, q + 8 * (1 - neg));  // y-x  (or y+x)
+    load_fe(td, q + 16 + 8 * neg);        // 2dxy (or -2dxy)
+    fe_sub(t0, p.Y, p.X);
+    fe_mul(a, t0, m_minus);
+    fe_add(t0, p.Y, p.X);
+    fe_mul(b, t0, m_plus);
+    fe_mul(c, p.T, td);
+    fe_dbl(d, p.Z);
+    fe_sub(e, b, a);
+    fe_add(h, b, a);
+    fe_sub(f, d, c);
+    fe_add(g, d, c);
+    fe_mul(p.X, e, f);
+    fe_mul(p.Y, g, h);
+    fe_mul(p.T, e, h);
+    fe_mul(p.Z, f, g);
+  }
+  // p = +/- the table point at q, as (4x : 4y : 4 : 4xy) — one multiply instead of a madd onto the identity
+  BPP_DEV static void init_from_ptr(Ext& p, const uint32_t* q, uint32_t neg) {
+    F m_minus, m_plus, dx, sy;
+    load_fe(m_plus, q + 8 * neg);
+    load_fe(m_minus, q + 8 * (1 - neg));
+    fe_sub(dx, m_plus, m_minus);  // 2x
+    fe_add(sy, m_plus, m_minus);  // 2y
+    fe_mul(p.T, dx, sy);          // 4xy
+    fe_dbl(p.X, dx);
+    fe_dbl(p.Y, sy);
+    fe_zero(p.Z);
+    p.Z.v[0] = 4;
   }
   // p += q, both extended; complete (add-2008-hwcd-3 with k = 2d), 9M
   BPP_DEV static void add(Ext& p, const Ext& q) {
@@ -104,7 +145,7 @@ struct Ed25519 {
     fe_invert(zi, p.Z);
     fe_mul(x, p.X, zi); fe_mul(y, p.Y, zi);
     fe_add(o.ypx, y, x); fe_sub(o.ymx, y, x);
-    fe_mul(t, x, y); fe_mul(o.t2d, t, k_d2());
+    fe_mul(t, x, y); fe_mul(o.t2d, t, k_d2()); fe_neg(o.nt2d, o.t2d);
   }
   BPP_DEV static void aff_to_ext(Ext& p, const Aff& q) {  // via identity + q (7M; only used off the hot path)
     set_identity(p);
@@ -149,7 +190,7 @@ struct Ed25519 {
     fe_mul(y, u1, den_y);
     fe_mul(t, x, y);
     ok = ok && was_square && !fe_is_neg(t) && !fe_is_zero(y);
-    fe_add(o.ypx, y, x); fe_sub(o.ymx, y, x); fe_mul(o.t2d, t, k_d2());
+    fe_add(o.ypx, y, x); fe_sub(o.ymx, y, x); fe_mul(o.t2d, t, k_d2()); fe_neg(o.nt2d, o.t2d);
     if (!ok) set_identity(o);
     return ok;
   }

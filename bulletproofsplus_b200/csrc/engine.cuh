@@ -30,9 +30,9 @@ struct DevBuf {
 };
 
 enum BufId {
-  B_SCALARS, B_PIDX, B_JOBSTART, B_COUNTS, B_OFFSETS, B_CURSOR, B_TILES, B_SORTED, B_BUCKETS, B_CHUNK_S, B_CHUNK_T, B_WINDOWS,
-  B_RESULTS, B_DYN, B_DYN_OK, B_IN0, B_IN1, B_IN2, B_IN3, B_OUT0, B_PARAMS, B_TAB0, B_TAB1, B_TAB2, B_TAB3, B_TAB4, B_TAB5, B_TAB6,
-  B_WORK0, B_WORK1, B_WORK2, B_FLAGS, B_FLAGS2, B_EXT, B_COUNT_
+  B_SCALARS, B_PIDX, B_JOBSTART, B_COUNTS, B_OFFSETS, B_CURSOR, B_TILES, B_SORTED, B_PERM, B_BINS, B_BUCKETS, B_CHUNK_S, B_CHUNK_T,
+  B_WINDOWS, B_FIXEDRES, B_RESULTS, B_DYN, B_DYN_OK, B_IN0, B_IN1, B_IN2, B_IN3, B_OUT0, B_PARAMS, B_TAB0, B_TAB1, B_TAB2, B_TAB3, B_TAB4,
+  B_TAB5, B_TAB6, B_WORK0, B_WORK1, B_WORK2, B_FLAGS, B_FLAGS2, B_EXT, B_COUNT_
 };
 
 }  // namespace bpp
@@ -58,6 +58,9 @@ struct bpp_pk {
   size_t len = 0;
   int device = 0;
   uint32_t* table = nullptr;  // affine: g, h, G[len], H[len]
+  uint32_t* wtab = nullptr;   // window tables: wtab[w * n_points + i] = 2^(cA * w) * table[i]
+  uint32_t* comb = nullptr;   // comb tables of g and h (K5): [(p * comb_w + w) * 128 + d - 1] = d * 2^(8w) * {g, h}
+  uint32_t cA = 0, WA = 0, comb_w = 0;
   uint32_t n_points() const { return (uint32_t)(2 + 2 * len); }
 };
 
@@ -92,14 +95,26 @@ namespace bpp {
 inline uint32_t ceil_div(uint64_t a, uint64_t b) { return (uint32_t)((a + b - 1) / b); }
 inline uint32_t ilog2(uint64_t x) { uint32_t l = 0; while ((1ull << (l + 1)) <= x) l++; return l; }
 
-// Window width minimising the algorithmic cost of SURVEY §8(d): W * (K*madd + 2*2^(c-1)*add) for K terms per job
-inline uint32_t choose_window(uint64_t terms_per_job, uint32_t scalar_bits, uint64_t n_jobs, double madd_cost, double add_cost) {
+// Cost model in units of one mixed addition (7 field multiplies); a full addition costs 9/7.
+// fixed-base: W * K additions + one reduction of 2^(c-1) buckets (2 full additions per bucket) per job
+inline uint32_t choose_window_fixed(uint64_t terms_per_job, uint32_t scalar_bits) {
+  uint32_t best = 4;
+  double best_cost = 1e300;
+  for (uint32_t c = 4; c <= 16; c++) {
+    uint64_t W = (scalar_bits + 1 + c - 1) / c, B = 1ull << (c - 1);
+    double cost = (double)W * (double)terms_per_job + 2.0 * (double)B * 9.0 / 7.0;
+    if (cost < best_cost) { best_cost = cost; best = c; }
+  }
+  return best;
+}
+// generic: W * (K additions + one reduction) + Horner
+inline uint32_t choose_window_generic(uint64_t terms_per_job, uint32_t scalar_bits, uint64_t n_jobs) {
   uint32_t best = 2;
   double best_cost = 1e300;
-  for (uint32_t c = 2; c <= 16; c++) {
+  for (uint32_t c = 2; c <= 18; c++) {
     uint64_t W = (scalar_bits + 1 + c - 1) / c, B = 1ull << (c - 1);
-    if (n_jobs * W * B > (1ull << 27)) continue;  // keep the key space (and bucket memory) bounded
-    double cost = (double)W * ((double)terms_per_job * madd_cost + 2.0 * (double)B * add_cost);
+    if (n_jobs * W * B > (1ull << 26)) continue;  // keep the key space (and bucket memory) bounded
+    double cost = (double)W * ((double)terms_per_job + 2.0 * (double)B * 9.0 / 7.0);
     if (cost < best_cost) { best_cost = cost; best = c; }
   }
   return best;
@@ -107,70 +122,120 @@ inline uint32_t choose_window(uint64_t terms_per_job, uint32_t scalar_bits, uint
 
 template <class C>
 struct Msm {
-  // Runs the segmented MSM over terms already in ctx->buf[B_SCALARS] / [B_PIDX]. job_start: device array (n_jobs+1)
-  // or nullptr when `uniform` > 0. Leaves n_jobs extended points in ctx->buf[B_RESULTS].
+  // Runs the segmented MSM over terms already in ctx->buf[B_SCALARS] / [B_PIDX]. Terms with point index < n_fixed use the
+  // window tables `wtab` (cA, WA from the public key); the others index `dyn` (per-call affine table) at idx - n_fixed and
+  // number about `dyn_per_job` per job (0 = none). job_start: device array (n_jobs+1) or nullptr when `uniform` > 0.
+  // Leaves n_jobs extended points in ctx->buf[B_RESULTS].
   static int run(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start,
-                 const uint32_t* tab0, uint32_t n0, const uint32_t* tab1, uint32_t window_override = 0) {
+                 const uint32_t* wtab, uint32_t n_fixed, uint32_t cA, uint32_t WA, const uint32_t* dyn, uint32_t dyn_per_job) {
     if (n_jobs == 0) return BPP_OK;
-    MsmShape sh;
-    sh.n_terms = n_terms;
-    sh.n_jobs = n_jobs;
-    sh.uniform = uniform;
-    uint64_t per_job = n_jobs ? (n_terms + n_jobs - 1) / n_jobs : 0;
-    sh.c = window_override ? window_override : choose_window(per_job ? per_job : 1, C::SCALAR_BITS, n_jobs, 7.0, 9.0);
-    sh.n_windows = (C::SCALAR_BITS + 1 + sh.c - 1) / sh.c;
-    sh.n_buckets = 1u << (sh.c - 1);
-    sh.chunk = sh.n_buckets < 64 ? sh.n_buckets : (sh.n_buckets >= 4096 ? 64 : 32);
-    const uint64_t n_keys64 = (uint64_t)n_jobs * sh.n_windows * sh.n_buckets;
-    if (n_keys64 >= (1ull << 31)) { ctx->err = "msm: key space too large"; return BPP_ERR_LENGTH; }
-    const uint32_t n_keys = (uint32_t)n_keys64;
-    const uint32_t n_jw = n_jobs * sh.n_windows;
-    const uint32_t n_chunks = n_jw * (sh.n_buckets / sh.chunk);
-    const uint64_t n_entries = (uint64_t)n_terms * sh.n_windows;
+    MsmPlan pl;
+    memset(&pl, 0, sizeof(pl));
+    pl.n_terms = n_terms; pl.n_jobs = n_jobs; pl.uniform = uniform;
+    if (n_fixed && wtab) {
+      pl.n_fixed = n_fixed; pl.cA = cA; pl.WA = WA; pl.NBA = 1u << (cA - 1);
+      pl.qA = pl.NBA < 16 ? pl.NBA : 16;
+    }
+    if (dyn_per_job) {
+      pl.cB = choose_window_generic(dyn_per_job, C::SCALAR_BITS, n_jobs);
+      pl.WB = (C::SCALAR_BITS + 1 + pl.cB - 1) / pl.cB;
+      pl.NBB = 1u << (pl.cB - 1);
+      pl.qB = pl.NBB < 16 ? pl.NBB : 16;
+    }
+    pl.wtab_points = pl.WA * pl.n_fixed;
+    const uint64_t keysA64 = (uint64_t)n_jobs * pl.NBA, keysB64 = (uint64_t)n_jobs * pl.WB * pl.NBB;
+    if (keysA64 + keysB64 >= (1ull << 30) || keysA64 + keysB64 == 0) { ctx->err = "msm: key space out of range"; return BPP_ERR_LENGTH; }
+    pl.keysA = (uint32_t)keysA64;
+    pl.n_keys = (uint32_t)(keysA64 + keysB64);
+    pl.chunksA = pl.NBA ? pl.keysA / pl.qA : 0;
+    const uint32_t chunksB = pl.WB ? (uint32_t)(keysB64 / pl.qB) : 0;
+    pl.n_chunks = pl.chunksA + chunksB;
+    const uint32_t n_keys = pl.n_keys;
+    const uint64_t n_entries = pl.WA ? (uint64_t)n_terms * pl.WA + (uint64_t)n_jobs * dyn_per_job * (pl.WB > pl.WA ? pl.WB - pl.WA : 0)
+                                      : (uint64_t)n_terms * pl.WB;  // upper bound; the per-job slices of the shared-memory sort
+    const uint32_t n_setsB = n_jobs * pl.WB;
     BPP_CK(ctx->buf[B_COUNTS].ensure((size_t)n_keys * 4));
     BPP_CK(ctx->buf[B_OFFSETS].ensure(((size_t)n_keys + 1) * 4));
     BPP_CK(ctx->buf[B_CURSOR].ensure((size_t)n_keys * 4));
+    BPP_CK(ctx->buf[B_PERM].ensure((size_t)n_keys * 4));
+    BPP_CK(ctx->buf[B_BINS].ensure((256 + 8) * 4));
     const uint32_t n_tiles = ceil_div(n_keys, SCAN_TILE);
     BPP_CK(ctx->buf[B_TILES].ensure((size_t)n_tiles * 4));
     BPP_CK(ctx->buf[B_SORTED].ensure((size_t)(n_entries ? n_entries : 1) * 4));
     BPP_CK(ctx->buf[B_BUCKETS].ensure((size_t)n_keys * C::EXT_WORDS * 4));
-    BPP_CK(ctx->buf[B_CHUNK_S].ensure((size_t)n_chunks * C::EXT_WORDS * 4));
-    BPP_CK(ctx->buf[B_CHUNK_T].ensure((size_t)n_chunks * C::EXT_WORDS * 4));
-    BPP_CK(ctx->buf[B_WINDOWS].ensure((size_t)n_jw * C::EXT_WORDS * 4));
+    BPP_CK(ctx->buf[B_CHUNK_S].ensure((size_t)pl.n_chunks * C::EXT_WORDS * 4));
+    BPP_CK(ctx->buf[B_CHUNK_T].ensure((size_t)pl.n_chunks * C::EXT_WORDS * 4));
+    BPP_CK(ctx->buf[B_WINDOWS].ensure((size_t)(n_setsB ? n_setsB : 1) * C::EXT_WORDS * 4));
+    BPP_CK(ctx->buf[B_FIXEDRES].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
     BPP_CK(ctx->buf[B_RESULTS].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
     uint32_t* counts = ctx->buf[B_COUNTS].as<uint32_t>();
     uint32_t* offsets = ctx->buf[B_OFFSETS].as<uint32_t>();
     uint32_t* cursor = ctx->buf[B_CURSOR].as<uint32_t>();
     uint32_t* tiles = ctx->buf[B_TILES].as<uint32_t>();
     uint32_t* sorted = ctx->buf[B_SORTED].as<uint32_t>();
+    uint32_t* perm = ctx->buf[B_PERM].as<uint32_t>();
+    uint32_t* bins = ctx->buf[B_BINS].as<uint32_t>();
     uint32_t* buckets = ctx->buf[B_BUCKETS].as<uint32_t>();
+    uint32_t* chunk_S = ctx->buf[B_CHUNK_S].as<uint32_t>();
+    uint32_t* chunk_T = ctx->buf[B_CHUNK_T].as<uint32_t>();
+    uint32_t* windows = ctx->buf[B_WINDOWS].as<uint32_t>();
+    uint32_t* fixedres = ctx->buf[B_FIXEDRES].as<uint32_t>();
+    uint32_t* results = ctx->buf[B_RESULTS].as<uint32_t>();
     const uint32_t* scalars = ctx->buf[B_SCALARS].as<uint32_t>();
     const uint32_t* pidx = ctx->buf[B_PIDX].as<uint32_t>();
-    BPP_CK(cudaMemsetAsync(counts, 0, (size_t)n_keys * 4, ctx->stream));
-    const uint32_t dg = n_terms ? (ceil_div(n_terms, 256) < 148 * 16 ? ceil_div(n_terms, 256) : 148 * 16) : 1;
-    BPP_LAUNCH(msm_digits_kernel<0>, dg, 256, 0, sh, scalars, pidx, d_job_start, counts, sorted);
-    BPP_LAUNCH(scan_tile_sums, n_tiles, SCAN_THREADS, 0, counts, n_keys, tiles);
-    BPP_LAUNCH(scan_tile_offsets, 1, SCAN_THREADS, 0, tiles, n_tiles);
-    BPP_LAUNCH(scan_apply, n_tiles, SCAN_THREADS, 0, counts, n_keys, tiles, offsets, cursor);
-    BPP_LAUNCH(msm_digits_kernel<1>, dg, 256, 0, sh, scalars, pidx, d_job_start, cursor, sorted);
+    BPP_CK(cudaMemsetAsync(bins, 0, 256 * 4, ctx->stream));
+    const uint32_t KPJ = pl.NBA + pl.WB * pl.NBB;
+    if (KPJ <= 12288) {
+      // small key space per job: one block sorts a whole job in shared memory
+      auto k = msm_sort_job_kernel<0>;
+      const size_t smem = (size_t)KPJ * 4;
+      if (smem > 48 * 1024) BPP_CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      BPP_LAUNCH(k, n_jobs, SJ_THREADS, smem, pl, dyn_per_job, scalars, pidx, d_job_start, offsets, counts, sorted);
+    } else {
+      BPP_CK(cudaMemsetAsync(counts, 0, (size_t)n_keys * 4, ctx->stream));
+      const uint32_t dg = n_terms ? (ceil_div(n_terms, 256) < 148 * 16 ? ceil_div(n_terms, 256) : 148 * 16) : 1;
+      BPP_LAUNCH(msm_digits_kernel<0>, dg, 256, 0, pl, scalars, pidx, d_job_start, counts, sorted);
+      BPP_LAUNCH(scan_tile_sums, n_tiles, SCAN_THREADS, 0, counts, n_keys, tiles);
+      BPP_LAUNCH(scan_tile_offsets, 1, SCAN_THREADS, 0, tiles, n_tiles);
+      BPP_LAUNCH(scan_apply, n_tiles, SCAN_THREADS, 0, counts, n_keys, tiles, offsets, cursor);
+      BPP_LAUNCH(msm_digits_kernel<1>, dg, 256, 0, pl, scalars, pidx, d_job_start, cursor, sorted);
+    }
+    const uint32_t ss_tiles = ceil_div(n_keys, SS_TILE);
+    BPP_LAUNCH(sizesort_hist_kernel, ss_tiles, SS_THREADS, 0, counts, n_keys, bins);
+    BPP_LAUNCH(sizesort_bins_scan_kernel, 1, 256, 0, bins, bins + 256, ACC_CAP);
+    BPP_LAUNCH(sizesort_scatter_kernel, ss_tiles, SS_THREADS, 0, counts, n_keys, bins, perm);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->hot_timing) {
       BPP_CK(cudaEventCreate(&e0));
       BPP_CK(cudaEventCreate(&e1));
       BPP_CK(cudaEventRecord(e0, ctx->stream));
     }
-    BPP_LAUNCH(msm_accumulate_kernel<C>, ceil_div(n_keys, 128), 128, 0, n_keys, offsets, sorted, tab0, n0, tab1, buckets);
+    {  // the long buckets first: a warp each for count >= 255, four lanes each for ACC_CAP < count < 255
+      const uint32_t g32 = ceil_div(n_keys, 4) < 1184 ? ceil_div(n_keys, 4) : 1184, g4 = ceil_div(n_keys, 32) < 1184 ? ceil_div(n_keys, 32) : 1184;
+      auto k32 = msm_accumulate_group_kernel<C, 32>;
+      auto k4 = msm_accumulate_group_kernel<C, 4>;
+      BPP_LAUNCH(k32, g32, 128, 0, bins + 256, 0u, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets);
+      BPP_LAUNCH(k4, g4, 128, 0, bins + 256, 1u, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets);
+    }
+    BPP_LAUNCH(msm_accumulate_kernel<C>, ceil_div(n_keys, 128), 128, 0, n_keys, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets);
     if (ctx->hot_timing) {
       BPP_CK(cudaEventRecord(e1, ctx->stream));
       ctx->hot_pending.push_back({e0, e1});
       ctx->hot_launches++;
     }
-    BPP_LAUNCH(msm_reduce_chunks_kernel<C>, ceil_div(n_chunks, 128), 128, 0, sh, buckets, ctx->buf[B_CHUNK_S].as<uint32_t>(),
-               ctx->buf[B_CHUNK_T].as<uint32_t>());
-    BPP_LAUNCH(msm_reduce_windows_kernel<C>, ceil_div(n_jw, 128), 128, 0, sh, ctx->buf[B_CHUNK_S].as<uint32_t>(),
-               ctx->buf[B_CHUNK_T].as<uint32_t>(), ctx->buf[B_WINDOWS].as<uint32_t>());
-    BPP_LAUNCH(msm_combine_kernel<C>, ceil_div(n_jobs, 128), 128, 0, sh, ctx->buf[B_WINDOWS].as<uint32_t>(),
-               ctx->buf[B_RESULTS].as<uint32_t>());
+    BPP_LAUNCH(msm_reduce_chunks_kernel<C>, ceil_div(pl.n_chunks, 128), 128, 0, pl, counts, buckets, chunk_S, chunk_T);
+    auto sets = [&](uint32_t n_sets, uint32_t first_chunk, uint32_t q, uint32_t NB, uint32_t* out) -> int {
+      const uint32_t cps = NB / q;                 // chunks per set
+      const uint32_t tps = cps < 128 ? cps : 128;  // threads per set
+      const uint32_t per = cps / tps;
+      BPP_LAUNCH(msm_reduce_sets_kernel<C>, ceil_div(n_sets, 128 / tps), 128, 0, n_sets, first_chunk, q, per, tps, chunk_S, chunk_T, out);
+      return BPP_OK;
+    };
+    if (pl.NBA) BPP_TRY(sets(n_jobs, 0, pl.qA, pl.NBA, pl.WB ? fixedres : results));
+    if (pl.WB) {
+      BPP_TRY(sets(n_setsB, pl.chunksA, pl.qB, pl.NBB, windows));
+      BPP_LAUNCH(msm_combine_kernel<C>, ceil_div(n_jobs, 128), 128, 0, pl, windows, fixedres, results);
+    }
     return BPP_OK;
   }
 };

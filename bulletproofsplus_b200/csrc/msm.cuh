@@ -1,19 +1,29 @@
-// K1/K2 — segmented signed-digit Pippenger multi-scalar multiplication for sm_100a.
+// K1/K2 — two-segment signed-digit bucket multi-scalar multiplication for sm_100a.
 //
 // Replaces MulVec::calculate (reference src/bls12_381/building_block/mulvec.rs:20-33: one full
 // G1::mul + one G1::add per term) for every caller on the path. One launch sequence evaluates J
 // independent MSMs ("jobs"): J = 1 for a large MSM (config 5), J = one per proof for batch
 // verification (weighted_inner_product_proof.rs:297-320, range/mod.rs:480-503), J = 2L+3 per proof
-// for proving. Terms are (32-byte canonical scalar, point reference) pairs; a point reference
-// indexes an affine table in HBM (bit 31 = negate).
+// for proving. A term is (32-byte canonical scalar, point index).
 //
-// Pipeline (all kernels templated on the curve policy C):
-//   msm_digits_count   signed-digit recode, c-bit windows; histogram of (job, window, bucket) keys
-//   scan_*             exclusive prefix sum of the histogram (3-phase, hand-written)
-//   msm_digits_scatter counting-sort scatter of point references by key
+// Segment A — FIXED-BASE terms (point index < n_fixed: the public key's g, h, G_i, H_i). The key
+//   carries a window table wtab[w][i] = 2^(cA*w) * P_i (affine, built once in bpp_pk_new), so all
+//   WA windows of a job drop into ONE set of 2^(cA-1) buckets: WA*K mixed additions and a single
+//   bucket reduction per job, no doublings at all.
+// Segment B — GENERIC terms (per-call points: proof elements, commitments, raw MSM inputs):
+//   classic Pippenger, one bucket set per (job, window), Horner over windows at the end.
+//
+// Pipeline (all kernels templated on the curve policy C where they touch points):
+//   msm_sort_job       small key spaces (batched proofs): per-job counting sort entirely in shared memory; else:
+//   msm_digits<0>      signed-digit recode; histogram of bucket keys (global atomics)
+//   scan_*             exclusive prefix sum of the histogram
+//   msm_digits<1>      counting-sort scatter of point references by key
+//   sizesort_*         permutation of the keys by descending bucket size: every warp of the hot
+//                      kernel then owns 32 buckets of (almost) the same length -> no lane idles
 //   msm_accumulate     HOT: one thread per bucket walks its list with mixed additions (IMAD-bound)
-//   msm_reduce_chunks / msm_reduce_windows   running-sum bucket reduction, chunked
-//   msm_combine        Horner over windows (c doublings per window)
+//   msm_reduce_chunks  running sums over chunks of 16 buckets
+//   msm_reduce_sets    per bucket set: suffix scan + tree in shared memory -> sum_b (b+1) * B_b
+//   msm_combine        Horner over the generic windows, plus the fixed-base part
 // Group addition is commutative, so the (unstable) atomic scatter order cannot change the result;
 // outputs are compared only after canonical encoding.
 #pragma once
@@ -22,14 +32,21 @@
 
 namespace bpp {
 
-struct MsmShape {
-  uint32_t n_terms;    // total terms over all jobs
+struct MsmPlan {
+  uint32_t n_terms;  // total terms over all jobs
   uint32_t n_jobs;
-  uint32_t c;          // window bits
-  uint32_t n_windows;  // ceil((scalar_bits + 1) / c)
-  uint32_t n_buckets;  // 2^(c-1)
-  uint32_t chunk;      // buckets per reduce chunk (power of two, divides n_buckets)
-  uint32_t uniform;    // > 0: every job has exactly this many terms (job = t / uniform)
+  uint32_t uniform;  // > 0: every job has exactly this many terms (job = t / uniform)
+  // segment A (fixed-base); NBA == 0 disables it
+  uint32_t n_fixed;  // points with index < n_fixed have window tables
+  uint32_t cA, WA, NBA;
+  // segment B (generic); WB == 0 disables it
+  uint32_t cB, WB, NBB;
+  uint32_t keysA;        // n_jobs * NBA
+  uint32_t n_keys;       // keysA + n_jobs * WB * NBB
+  uint32_t wtab_points;  // WA * n_fixed: references >= this index the per-call table
+  uint32_t qA, qB;       // reduce chunk sizes (powers of two dividing NBA / NBB)
+  uint32_t chunksA;      // keysA / qA
+  uint32_t n_chunks;     // chunksA + n_jobs * WB * NBB / qB
 };
 
 __device__ __forceinline__ uint32_t msm_find_job(const uint32_t* __restrict__ job_start, uint32_t n_jobs, uint32_t uniform, uint32_t t) {
@@ -51,29 +68,133 @@ __device__ __forceinline__ uint32_t msm_bits(const uint32_t* s, uint32_t off, ui
   return (uint32_t)(((hi << 32) | lo) >> sh) & ((1u << c) - 1u);
 }
 
-// MODE 0: histogram; MODE 1: scatter
+// MODE 0: histogram; MODE 1: scatter. Reference bit 31 = subtract the point.
 template <int MODE>
-__global__ void msm_digits_kernel(MsmShape sh, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
+__global__ void msm_digits_kernel(MsmPlan pl, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
                                   const uint32_t* __restrict__ job_start, uint32_t* __restrict__ counts_or_cursor,
                                   uint32_t* __restrict__ sorted) {
-  const uint32_t half = 1u << (sh.c - 1);
-  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < sh.n_terms; t += gridDim.x * blockDim.x) {
+  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < pl.n_terms; t += gridDim.x * blockDim.x) {
     uint32_t s[8];
     const uint4* sp = reinterpret_cast<const uint4*>(scalars + 8ull * t);
     uint4 a = __ldg(sp), b = __ldg(sp + 1);
     s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
-    uint32_t job = msm_find_job(job_start, sh.n_jobs, sh.uniform, t);
-    uint32_t ref = MODE ? pidx[t] : 0;
+    const uint32_t job = msm_find_job(job_start, pl.n_jobs, pl.uniform, t);
+    const uint32_t p = pidx[t];
+    const bool fixed = p < pl.n_fixed;
+    const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB;
+    const uint32_t half = 1u << (c - 1);
+    const uint32_t keybase = fixed ? job * pl.NBA : pl.keysA + job * pl.WB * pl.NBB;
+    const uint32_t refbase = fixed ? p : pl.wtab_points + (p - pl.n_fixed);
     uint32_t carry = 0;
-    for (uint32_t w = 0; w < sh.n_windows; w++) {
-      uint32_t raw = msm_bits(s, w * sh.c, sh.c) + carry;
+    for (uint32_t w = 0; w < W; w++) {
+      uint32_t raw = msm_bits(s, w * c, c) + carry;
       uint32_t neg = raw > half;
-      uint32_t mag = neg ? (1u << sh.c) - raw : raw;
+      uint32_t mag = neg ? (1u << c) - raw : raw;
       carry = neg;
       if (mag) {
-        uint32_t key = (job * sh.n_windows + w) * sh.n_buckets + (mag - 1);
+        uint32_t key = keybase + (fixed ? 0u : w * pl.NBB) + (mag - 1);
         if (MODE == 0) atomicAdd(&counts_or_cursor[key], 1u);
-        else sorted[atomicAdd(&counts_or_cursor[key], 1u)] = ref ^ (neg << 31);
+        else sorted[atomicAdd(&counts_or_cursor[key], 1u)] = (refbase + (fixed ? w * pl.n_fixed : 0u)) | (neg << 31);
+      }
+    }
+  }
+}
+
+// ---- per-job counting sort in shared memory (warp-cooperative bucket sorting) ---------------------------------
+// One block per job, for jobs whose key space (NBA + WB * NBB counters) fits in shared memory: histogram with shared
+// atomics, block scan, scatter with shared cursors. Only the sorted references and the per-key (offset, count) leave
+// the SM; the global histogram, its memset and the three scan kernels are not needed on this path. Job j owns the
+// slice [ebase_j, ebase_j + cap_j) of `sorted`, cap_j = K_j * WA + dyn_per_job * max(WB - WA, 0).
+constexpr int SJ_THREADS = 512;
+__device__ __forceinline__ void msm_job_digits(const MsmPlan& pl, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
+                                               uint32_t t, uint32_t* s, uint32_t& p) {
+  const uint4* sp = reinterpret_cast<const uint4*>(scalars + 8ull * t);
+  uint4 a = __ldg(sp), b = __ldg(sp + 1);
+  s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
+  p = pidx[t];
+}
+template <int DUMMY>
+__global__ void __launch_bounds__(SJ_THREADS)
+msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
+                    const uint32_t* __restrict__ job_start, uint32_t* __restrict__ offsets, uint32_t* __restrict__ counts,
+                    uint32_t* __restrict__ sorted) {
+  extern __shared__ uint32_t sm[];  // cnt[KPJ] (becomes the cursor)
+  __shared__ uint32_t warp_sums[SJ_THREADS / 32];
+  const uint32_t job = blockIdx.x, tid = threadIdx.x;
+  const uint32_t KPJ = pl.NBA + pl.WB * pl.NBB;
+  const uint32_t t0 = pl.uniform ? job * pl.uniform : job_start[job];
+  const uint32_t t1 = pl.uniform ? t0 + pl.uniform : job_start[job + 1];
+  const uint32_t extraW = pl.WB > pl.WA ? pl.WB - pl.WA : 0;
+  const uint32_t ebase = t0 * pl.WA + job * dyn_per_job * extraW;
+  for (uint32_t k = tid; k < KPJ; k += SJ_THREADS) sm[k] = 0;
+  __syncthreads();
+  // pass 1: histogram
+  for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS) {
+    uint32_t s[8], p;
+    msm_job_digits(pl, scalars, pidx, t, s, p);
+    const bool fixed = p < pl.n_fixed;
+    const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
+    uint32_t carry = 0;
+    for (uint32_t w = 0; w < W; w++) {
+      uint32_t raw = msm_bits(s, w * c, c) + carry;
+      uint32_t neg = raw > half;
+      uint32_t mag = neg ? (1u << c) - raw : raw;
+      carry = neg;
+      if (mag) atomicAdd(&sm[fixed ? mag - 1 : pl.NBA + w * pl.NBB + mag - 1], 1u);
+    }
+  }
+  __syncthreads();
+  // exclusive scan of cnt[0..KPJ): contiguous chunk per thread
+  const uint32_t ch = (KPJ + SJ_THREADS - 1) / SJ_THREADS;
+  const uint32_t k0 = tid * ch, k1 = k0 + ch < KPJ ? k0 + ch : KPJ;
+  uint32_t mysum = 0;
+  for (uint32_t k = k0; k < k1; k++) mysum += sm[k];
+  uint32_t x = mysum;
+  const uint32_t lane = tid & 31, wid = tid >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) warp_sums[wid] = x;
+  __syncthreads();
+  if (wid == 0) {
+    uint32_t v = lane < SJ_THREADS / 32 ? warp_sums[lane] : 0;
+#pragma unroll
+    for (int o = 1; o < SJ_THREADS / 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += y;
+    }
+    if (lane < SJ_THREADS / 32) warp_sums[lane] = v;
+  }
+  __syncthreads();
+  uint32_t run = (wid ? warp_sums[wid - 1] : 0) + x - mysum;
+  const uint32_t gA = job * pl.NBA, gB = pl.keysA + job * pl.WB * pl.NBB;
+  for (uint32_t k = k0; k < k1; k++) {
+    const uint32_t cnt = sm[k];
+    const uint32_t gkey = k < pl.NBA ? gA + k : gB + (k - pl.NBA);
+    offsets[gkey] = ebase + run;
+    counts[gkey] = cnt;
+    sm[k] = run;  // cursor
+    run += cnt;
+  }
+  __syncthreads();
+  // pass 2: scatter
+  for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS) {
+    uint32_t s[8], p;
+    msm_job_digits(pl, scalars, pidx, t, s, p);
+    const bool fixed = p < pl.n_fixed;
+    const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
+    const uint32_t refbase = fixed ? p : pl.wtab_points + (p - pl.n_fixed);
+    uint32_t carry = 0;
+    for (uint32_t w = 0; w < W; w++) {
+      uint32_t raw = msm_bits(s, w * c, c) + carry;
+      uint32_t neg = raw > half;
+      uint32_t mag = neg ? (1u << c) - raw : raw;
+      carry = neg;
+      if (mag) {
+        uint32_t pos = atomicAdd(&sm[fixed ? mag - 1 : pl.NBA + w * pl.NBB + mag - 1], 1u);
+        sorted[ebase + pos] = (refbase + (fixed ? w * pl.n_fixed : 0u)) | (neg << 31);
       }
     }
   }
@@ -152,93 +273,283 @@ __global__ void scan_apply(const uint32_t* __restrict__ in, uint32_t n, const ui
   }
 }
 
-// ---- HOT: bucket accumulation -----------------------------------------------------------------------
-// One thread per (job, window, bucket). tab0 holds the n0 resident points of the public key, tab1 the
-// per-call points; both are AoS affine, read with 128-bit loads.
+// ---- keys by descending bucket size (counting sort on min(count, 255)) ---------------------------------
+// bins[0..256): global bin totals (zeroed by the caller); after sizesort_bins_scan they hold the bin starts.
+constexpr int SS_THREADS = 256;
+constexpr int SS_ITEMS = 16;
+constexpr int SS_TILE = SS_THREADS * SS_ITEMS;
+__device__ __forceinline__ uint32_t ss_bin(uint32_t count) { return 255u - (count < 255u ? count : 255u); }
+
+__global__ void __launch_bounds__(SS_THREADS) sizesort_hist_kernel(const uint32_t* __restrict__ counts, uint32_t n, uint32_t* __restrict__ bins) {
+  __shared__ uint32_t h[256];
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  uint32_t base = blockIdx.x * SS_TILE;
+  for (uint32_t i = threadIdx.x; i < SS_TILE && base + i < n; i += SS_THREADS) atomicAdd(&h[ss_bin(counts[base + i])], 1u);
+  __syncthreads();
+  if (h[threadIdx.x]) atomicAdd(&bins[threadIdx.x], h[threadIdx.x]);
+}
+// one block: bin totals -> exclusive starts; tiers[0..2] = first perm index of the buckets with count <= 254 / <= ACC_CAP
+__global__ void __launch_bounds__(256) sizesort_bins_scan_kernel(uint32_t* __restrict__ bins, uint32_t* __restrict__ tiers, uint32_t acc_cap) {
+  uint32_t tot;
+  uint32_t ex = block_exclusive_scan(bins[threadIdx.x], &tot);
+  bins[threadIdx.x] = ex;
+  if (threadIdx.x == 0) tiers[0] = 0;
+  if (threadIdx.x == 1) tiers[1] = ex;
+  if (threadIdx.x == 255 - acc_cap) tiers[2] = ex;
+}
+__global__ void __launch_bounds__(SS_THREADS) sizesort_scatter_kernel(const uint32_t* __restrict__ counts, uint32_t n, uint32_t* __restrict__ bins,
+                                                                      uint32_t* __restrict__ perm) {
+  __shared__ uint32_t h[256], start[256];
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  uint32_t base = blockIdx.x * SS_TILE;
+  uint32_t local[SS_ITEMS], bin[SS_ITEMS];
+#pragma unroll
+  for (int k = 0; k < SS_ITEMS; k++) {
+    uint32_t i = threadIdx.x + k * SS_THREADS;
+    bin[k] = 0xffffffffu;
+    if (base + i < n) { bin[k] = ss_bin(counts[base + i]); local[k] = atomicAdd(&h[bin[k]], 1u); }
+  }
+  __syncthreads();
+  start[threadIdx.x] = h[threadIdx.x] ? atomicAdd(&bins[threadIdx.x], h[threadIdx.x]) : 0;  // reserve this tile's range of every bin
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < SS_ITEMS; k++) {
+    uint32_t i = threadIdx.x + k * SS_THREADS;
+    if (bin[k] != 0xffffffffu) perm[start[bin[k]] + local[k]] = base + i;
+  }
+}
+
+// ---- HOT: bucket accumulation ---------------------------------------------------------------------------
+// One thread per bucket, buckets taken in descending-size order. wtab: window tables of the public key
+// (wtab_points entries), dyn: per-call points; both AoS affine, C::AFF_WORDS words per point, read with
+// 128-bit loads. Empty buckets are not written (the reduce kernels test the counts). Buckets longer than
+// ACC_CAP (the partial top window always produces some; adversarial scalars produce more) are left to
+// msm_accumulate_group_kernel, which spreads each of them over 4 or 32 lanes.
+constexpr uint32_t ACC_CAP = 96;
+
+template <class C>
+__device__ __forceinline__ const uint32_t* msm_point_ptr(uint32_t ref, const uint32_t* __restrict__ wtab, uint32_t wtab_points,
+                                                         const uint32_t* __restrict__ dyn) {
+  uint32_t idx = ref & 0x7fffffffu;
+  return idx < wtab_points ? wtab + (size_t)idx * C::AFF_WORDS : dyn + (size_t)(idx - wtab_points) * C::AFF_WORDS;
+}
+
 template <class C>
 __global__ void __launch_bounds__(128)
-msm_accumulate_kernel(uint32_t n_keys, const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ sorted,
-                      const uint32_t* __restrict__ tab0, uint32_t n0, const uint32_t* __restrict__ tab1,
-                      uint32_t* __restrict__ buckets) {
-  uint32_t key = blockIdx.x * blockDim.x + threadIdx.x;
-  if (key >= n_keys) return;
-  uint32_t beg = offsets[key], end = offsets[key + 1];
+msm_accumulate_kernel(uint32_t n_keys, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ offsets,
+                      const uint32_t* __restrict__ counts, const uint32_t* __restrict__ sorted, const uint32_t* __restrict__ wtab, uint32_t wtab_points,
+                      const uint32_t* __restrict__ dyn, uint32_t* __restrict__ buckets) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_keys) return;
+  const uint32_t key = perm[t];
+  const uint32_t beg = offsets[key], cnt = counts[key], end = beg + cnt;
+  if (cnt == 0 || cnt > ACC_CAP) return;
   typename C::Ext acc;
-  C::set_identity(acc);
-  for (uint32_t e = beg; e < end; e++) {
-    uint32_t ref = __ldg(sorted + e);
-    uint32_t idx = ref & 0x7fffffffu;
-    const uint32_t* src = idx < n0 ? tab0 + (size_t)idx * C::AFF_WORDS : tab1 + (size_t)(idx - n0) * C::AFF_WORDS;
-    typename C::Aff q;
-    load_words<C::AFF_WORDS>(q, src);
-    C::madd(acc, q, ref >> 31);
+  uint32_t ref = __ldg(sorted + beg);
+  C::init_from_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+  for (uint32_t e = beg + 1; e < end; e++) {
+    ref = __ldg(sorted + e);
+    C::madd_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
   }
   store_words<C::EXT_WORDS>(buckets + (size_t)key * C::EXT_WORDS, acc);
 }
 
-// ---- bucket reduction: sum_b (b+1) * bucket[b], chunked ---------------------------------------------
-// thread per (job*window, chunk): S = sum of the chunk's buckets, T = sum_{b in chunk} (b - lo + 1) * bucket[b]
+// Buckets longer than ACC_CAP (the first entries of `perm`): G lanes per bucket — lane-strided walk, then a log2(G)-level
+// tree through shared memory. Tier 0 (count >= 255) runs with G = 32, tier 1 (ACC_CAP < count < 255) with G = 4.
+template <class C, int G>
+__global__ void __launch_bounds__(128)
+msm_accumulate_group_kernel(const uint32_t* __restrict__ tiers, uint32_t tier, const uint32_t* __restrict__ perm,
+                            const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ counts, const uint32_t* __restrict__ sorted,
+                            const uint32_t* __restrict__ wtab, uint32_t wtab_points, const uint32_t* __restrict__ dyn,
+                            uint32_t* __restrict__ buckets) {
+  __shared__ uint32_t sh[128 * C::EXT_WORDS];
+  const uint32_t tid = threadIdx.x, lane = tid % G;
+  typename C::Ext* mine = reinterpret_cast<typename C::Ext*>(sh + tid * C::EXT_WORDS);
+  const uint32_t lo = tiers[tier], hi = tiers[tier + 1];
+  const uint32_t n_groups = gridDim.x * (128 / G);
+  for (uint32_t t = lo + blockIdx.x * (128 / G) + tid / G; t < hi; t += n_groups) {
+    const uint32_t key = perm[t];
+    const uint32_t beg = offsets[key], end = beg + counts[key];  // count > ACC_CAP >= G: every lane has an entry
+    typename C::Ext acc;
+    uint32_t e = beg + lane;
+    uint32_t ref = __ldg(sorted + e);
+    C::init_from_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+    for (e += G; e < end; e += G) {
+      ref = __ldg(sorted + e);
+      C::madd_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+    }
+    *mine = acc;
+    __syncwarp();
+    for (uint32_t s = G / 2; s > 0; s >>= 1) {
+      if (lane < s) {
+        typename C::Ext o = *reinterpret_cast<typename C::Ext*>(sh + (tid + s) * C::EXT_WORDS);
+        C::add(acc, o);
+        *mine = acc;
+      }
+      __syncwarp();
+    }
+    if (lane == 0) store_words<C::EXT_WORDS>(buckets + (size_t)key * C::EXT_WORDS, acc);
+    __syncwarp();
+  }
+}
+
+// ---- bucket reduction: sum_b (b+1) * bucket[b] per bucket set ---------------------------------------------
+// level 1 — thread per chunk of q consecutive buckets: S = sum of the chunk, T = sum_k (k+1) * bucket[lo+k]
 template <class C>
 __global__ void __launch_bounds__(128)
-msm_reduce_chunks_kernel(MsmShape sh, const uint32_t* __restrict__ buckets, uint32_t* __restrict__ chunk_S,
-                         uint32_t* __restrict__ chunk_T) {
-  uint32_t n_chunks = sh.n_buckets / sh.chunk;
+msm_reduce_chunks_kernel(MsmPlan pl, const uint32_t* __restrict__ counts, const uint32_t* __restrict__ buckets,
+                         uint32_t* __restrict__ chunk_S, uint32_t* __restrict__ chunk_T) {
   uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
-  if (id >= sh.n_jobs * sh.n_windows * n_chunks) return;
-  uint32_t jw = id / n_chunks, ci = id % n_chunks;
-  const uint32_t* base = buckets + ((size_t)jw * sh.n_buckets + (size_t)ci * sh.chunk) * C::EXT_WORDS;
+  if (id >= pl.n_chunks) return;
+  uint32_t q, lo;
+  if (id < pl.chunksA) { q = pl.qA; lo = id * q; }
+  else { q = pl.qB; lo = pl.keysA + (id - pl.chunksA) * q; }
   typename C::Ext run, sum, b;
-  C::set_identity(run);
-  C::set_identity(sum);
-  for (int k = (int)sh.chunk - 1; k >= 0; k--) {
-    load_words<C::EXT_WORDS>(b, base + (size_t)k * C::EXT_WORDS);
-    C::add(run, b);
-    C::add(sum, run);
+  bool have_run = false, have_sum = false;
+  for (int k = (int)q - 1; k >= 0; k--) {
+    uint32_t key = lo + k;
+    if (counts[key]) {
+      load_words<C::EXT_WORDS>(b, buckets + (size_t)key * C::EXT_WORDS);
+      if (have_run) C::add(run, b); else { run = b; have_run = true; }
+    }
+    if (have_run) {
+      if (have_sum) C::add(sum, run); else { sum = run; have_sum = true; }
+    }
   }
+  if (!have_run) { C::set_identity(run); C::set_identity(sum); }
   store_words<C::EXT_WORDS>(chunk_S + (size_t)id * C::EXT_WORDS, run);
   store_words<C::EXT_WORDS>(chunk_T + (size_t)id * C::EXT_WORDS, sum);
 }
-// thread per (job*window): window = sum_ci T_ci + chunk * sum_ci ci * S_ci
+
+// level 2 — a group of `tps` threads per bucket set (128-thread blocks, 128 / tps sets per block); each thread owns
+// `per` consecutive chunks, then the group does a suffix scan and a tree sum in shared memory:
+//   set total = sum_t [ T'_t + (q * per) * t * S'_t ],   sum_t t * S'_t = sum_{t >= 1} (sum_{u >= t} S'_u)
+// first_chunk/first_set select the segment (A: sets = jobs, B: sets = job * WB + window). q, per, tps powers of two.
 template <class C>
 __global__ void __launch_bounds__(128)
-msm_reduce_windows_kernel(MsmShape sh, const uint32_t* __restrict__ chunk_S, const uint32_t* __restrict__ chunk_T,
-                          uint32_t* __restrict__ windows) {
-  uint32_t n_chunks = sh.n_buckets / sh.chunk;
-  uint32_t jw = blockIdx.x * blockDim.x + threadIdx.x;
-  if (jw >= sh.n_jobs * sh.n_windows) return;
-  typename C::Ext run, sum, tsum, p;
-  C::set_identity(run);
-  C::set_identity(sum);
-  C::set_identity(tsum);
-  for (int ci = (int)n_chunks - 1; ci >= 0; ci--) {
-    size_t id = (size_t)jw * n_chunks + ci;
-    load_words<C::EXT_WORDS>(p, chunk_T + id * C::EXT_WORDS);
-    C::add(tsum, p);
-    if (ci > 0) {
-      load_words<C::EXT_WORDS>(p, chunk_S + id * C::EXT_WORDS);
-      C::add(run, p);
-      C::add(sum, run);
+msm_reduce_sets_kernel(uint32_t n_sets, uint32_t first_chunk, uint32_t q, uint32_t per, uint32_t tps,
+                       const uint32_t* __restrict__ chunk_S, const uint32_t* __restrict__ chunk_T, uint32_t* __restrict__ out) {
+  __shared__ uint32_t sh[128 * C::EXT_WORDS];
+  const uint32_t tid = threadIdx.x, g = tid / tps, lane = tid % tps;
+  const uint32_t set = blockIdx.x * (128 / tps) + g;
+  const bool live = set < n_sets;
+  typename C::Ext S, T, p;
+  C::set_identity(S);
+  C::set_identity(T);
+  if (live) {
+    const size_t c0 = (size_t)first_chunk + ((size_t)set * tps + lane) * per;
+    // local: S' = sum_k S_k, T' = sum_k T_k + q * sum_k k * S_k
+    typename C::Ext acc;
+    C::set_identity(acc);
+    for (int k = (int)per - 1; k >= 0; k--) {
+      load_words<C::EXT_WORDS>(p, chunk_T + (c0 + k) * C::EXT_WORDS);
+      C::add(T, p);
+      load_words<C::EXT_WORDS>(p, chunk_S + (c0 + k) * C::EXT_WORDS);
+      if (k > 0) { C::add(S, p); C::add(acc, S); }
+      else {
+        for (uint32_t s = q; s > 1 && per > 1; s >>= 1) C::dbl(acc);
+        if (per > 1) C::add(T, acc);
+        C::add(S, p);
+      }
     }
   }
-  for (uint32_t s = sh.chunk; s > 1; s >>= 1) C::dbl(sum);
-  C::add(tsum, sum);
-  store_words<C::EXT_WORDS>(windows + (size_t)jw * C::EXT_WORDS, tsum);
+  typename C::Ext* mine = reinterpret_cast<typename C::Ext*>(sh + tid * C::EXT_WORDS);
+  // inclusive suffix scan of S' over the group
+  *mine = S;
+  __syncthreads();
+  for (uint32_t off = 1; off < tps; off <<= 1) {
+    const bool have = lane + off < tps;
+    if (have) p = *reinterpret_cast<typename C::Ext*>(sh + (tid + off) * C::EXT_WORDS);
+    __syncthreads();
+    if (have) { C::add(S, p); *mine = S; }
+    __syncthreads();
+  }
+  // V_t = T'_t + (q * per) * R_t for t >= 1
+  if (lane >= 1) {
+    for (uint32_t s = q * per; s > 1; s >>= 1) C::dbl(S);
+    C::add(T, S);
+  }
+  *mine = T;
+  __syncthreads();
+  for (uint32_t s = tps >> 1; s > 0; s >>= 1) {
+    if (lane < s) {
+      p = *reinterpret_cast<typename C::Ext*>(sh + (tid + s) * C::EXT_WORDS);
+      C::add(T, p);
+      *mine = T;
+    }
+    __syncthreads();
+  }
+  if (live && lane == 0) store_words<C::EXT_WORDS>(out + (size_t)set * C::EXT_WORDS, T);
 }
-// thread per job: Horner over windows
+
+// thread per job: Horner over the generic windows, plus the fixed-base part
 template <class C>
 __global__ void __launch_bounds__(128)
-msm_combine_kernel(MsmShape sh, const uint32_t* __restrict__ windows, uint32_t* __restrict__ results) {
+msm_combine_kernel(MsmPlan pl, const uint32_t* __restrict__ windows, const uint32_t* __restrict__ fixed_res, uint32_t* __restrict__ results) {
   uint32_t job = blockIdx.x * blockDim.x + threadIdx.x;
-  if (job >= sh.n_jobs) return;
+  if (job >= pl.n_jobs) return;
   typename C::Ext acc, p;
-  const uint32_t* base = windows + (size_t)job * sh.n_windows * C::EXT_WORDS;
-  load_words<C::EXT_WORDS>(acc, base + (size_t)(sh.n_windows - 1) * C::EXT_WORDS);
-  for (int w = (int)sh.n_windows - 2; w >= 0; w--) {
-    for (uint32_t k = 0; k < sh.c; k++) C::dbl(acc);
-    load_words<C::EXT_WORDS>(p, base + (size_t)w * C::EXT_WORDS);
-    C::add(acc, p);
+  if (pl.WB) {
+    const uint32_t* base = windows + (size_t)job * pl.WB * C::EXT_WORDS;
+    load_words<C::EXT_WORDS>(acc, base + (size_t)(pl.WB - 1) * C::EXT_WORDS);
+    for (int w = (int)pl.WB - 2; w >= 0; w--) {
+      for (uint32_t k = 0; k < pl.cB; k++) C::dbl(acc);
+      load_words<C::EXT_WORDS>(p, base + (size_t)w * C::EXT_WORDS);
+      C::add(acc, p);
+    }
+    if (pl.NBA) {
+      load_words<C::EXT_WORDS>(p, fixed_res + (size_t)job * C::EXT_WORDS);
+      C::add(acc, p);
+    }
+  } else {
+    load_words<C::EXT_WORDS>(acc, fixed_res + (size_t)job * C::EXT_WORDS);
   }
   store_words<C::EXT_WORDS>(results + (size_t)job * C::EXT_WORDS, acc);
+}
+
+// ---- window tables of a public key: wtab[w * n + i] = 2^(c*w) * P_i ------------------------------------------
+template <class C>
+__global__ void wtab_build_kernel(uint32_t n, uint32_t c, uint32_t W, const uint32_t* __restrict__ aff, uint32_t* __restrict__ wtab) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  typename C::Aff q;
+  typename C::Ext p;
+  load_words<C::AFF_WORDS>(q, aff + (size_t)i * C::AFF_WORDS);
+  store_words<C::AFF_WORDS>(wtab + (size_t)i * C::AFF_WORDS, q);
+  C::aff_to_ext(p, q);
+  for (uint32_t w = 1; w < W; w++) {
+    for (uint32_t k = 0; k < c; k++) C::dbl(p);
+    C::to_aff(q, p);
+    store_words<C::AFF_WORDS>(wtab + ((size_t)w * n + i) * C::AFF_WORDS, q);
+  }
+}
+
+// ---- K5: comb tables for the two commitment bases: comb[(p * CW + w) * 128 + d - 1] = d * 2^(8w) * P_p -------
+// (built by comb_build_kernel in proto_misc.cuh). out[j] = a_j * P_0 + b_j * P_1 (extended); scalars = (a_j, b_j)
+// pairs of canonical 256-bit values; at most 2 * CW table additions per commitment, no buckets, no doublings.
+constexpr int COMB_C = 8, COMB_D = 128;
+template <class C>
+__global__ void __launch_bounds__(128) comb_eval_kernel(uint32_t n, uint32_t CW, const uint32_t* __restrict__ scalars,
+                                                        const uint32_t* __restrict__ comb, uint32_t* __restrict__ out) {
+  uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  typename C::Ext acc;
+  C::set_identity(acc);
+  for (uint32_t pi = 0; pi < 2; pi++) {
+    uint32_t s[8];
+    for (int i = 0; i < 8; i++) s[i] = scalars[(size_t)(2 * j + pi) * 8 + i];
+    uint32_t carry = 0;
+    for (uint32_t w = 0; w < CW; w++) {
+      uint32_t raw = (w < 32 ? (s[w >> 2] >> (8 * (w & 3))) & 0xffu : 0u) + carry;
+      uint32_t neg = raw > 128u;
+      uint32_t mag = neg ? 256u - raw : raw;
+      carry = neg;
+      if (mag) C::madd_ptr(acc, comb + ((size_t)(pi * CW + w) * COMB_D + mag - 1) * C::AFF_WORDS, neg);
+    }
+  }
+  store_words<C::EXT_WORDS>(out + (size_t)j * C::EXT_WORDS, acc);
 }
 
 // ---- boundary kernels ---------------------------------------------------------------------------------
@@ -268,24 +579,6 @@ __global__ void points_encode_aff_kernel(uint32_t n, const uint32_t* __restrict_
   load_words<C::AFF_WORDS>(q, aff + (size_t)i * C::AFF_WORDS);
   C::aff_to_ext(p, q);
   C::encode(bytes + (size_t)i * C::POINT_BYTES, p);
-}
-template <class C>
-__global__ void points_is_identity_kernel(uint32_t n, const uint32_t* __restrict__ ext, uint8_t* __restrict__ out) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  typename C::Ext p;
-  load_words<C::EXT_WORDS>(p, ext + (size_t)i * C::EXT_WORDS);
-  out[i] = C::is_identity(p) ? 1 : 0;
-}
-template <class C>
-__global__ void points_ext_to_aff_kernel(uint32_t n, const uint32_t* __restrict__ ext, uint32_t* __restrict__ aff) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  typename C::Ext p;
-  typename C::Aff q;
-  load_words<C::EXT_WORDS>(p, ext + (size_t)i * C::EXT_WORDS);
-  C::to_aff(q, p);
-  store_words<C::AFF_WORDS>(aff + (size_t)i * C::AFF_WORDS, q);
 }
 
 }  // namespace bpp

@@ -124,12 +124,17 @@ __global__ void verdict_kernel(uint32_t n_proofs, uint32_t pts_per_proof, uint32
 // proof assembly: job results (A, L.., R.., wipA, wipB per proof) -> encoded points inside each proof
 template <class C>
 __global__ void encode_into_proofs_kernel(uint32_t n_proofs, uint32_t jobs_per_proof, const uint32_t* __restrict__ results,
-                                          uint8_t* __restrict__ proofs, size_t proof_stride) {
+                                          const uint32_t* __restrict__ add_to_job0, uint8_t* __restrict__ proofs, size_t proof_stride) {
   uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_proofs * jobs_per_proof) return;
   uint32_t p = t / jobs_per_proof, k = t % jobs_per_proof;
   typename C::Ext r;
   load_words<C::EXT_WORDS>(r, results + (size_t)t * C::EXT_WORDS);
+  if (k == 0 && add_to_job0) {
+    typename C::Ext s;
+    load_words<C::EXT_WORDS>(s, add_to_job0 + (size_t)p * C::EXT_WORDS);
+    C::add(r, s);
+  }
   C::encode(proofs + (size_t)p * proof_stride + (size_t)k * C::POINT_BYTES, r);
 }
 
@@ -163,6 +168,24 @@ __global__ void __launch_bounds__(128) ext_sum_kernel(uint32_t count, const uint
     __syncthreads();
   }
   if (threadIdx.x == 0) store_words<C::EXT_WORDS>(out, acc);
+}
+
+// K5 tables: comb[(p * CW + w) * 128 + d - 1] = d * 2^(8w) * P_p for the two commitment bases P_0 = g, P_1 = h
+// (publickey.rs:50-52). One thread per entry; built once per public key.
+template <class C>
+__global__ void comb_build_kernel(uint32_t CW, const uint32_t* __restrict__ aff2, uint32_t* __restrict__ comb) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= 2 * CW * COMB_D) return;
+  uint32_t d = t % COMB_D + 1, pw = t / COMB_D, w = pw % CW, pi = pw / CW;
+  typename C::Aff q;
+  typename C::Ext base, r;
+  load_words<C::AFF_WORDS>(q, aff2 + (size_t)pi * C::AFF_WORDS);
+  C::aff_to_ext(base, q);
+  for (uint32_t k = 0; k < w * COMB_C; k++) C::dbl(base);
+  uint32_t k[8] = {d, 0, 0, 0, 0, 0, 0, 0};
+  scalar_mul_vartime<C>(r, base, k);
+  C::to_aff(q, r);
+  store_words<C::AFF_WORDS>(comb + (size_t)t * C::AFF_WORDS, q);
 }
 
 // ---- integer-pipe roofline probe: ILP-8 independent chains per thread, no memory traffic -------------

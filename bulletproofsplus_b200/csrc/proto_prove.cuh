@@ -23,7 +23,7 @@ struct ProveShape {
   uint32_t mode;     // 0: standalone WIP (caller supplies a, b, y-powers, gamma); 1: range single; 2: range multiple
   uint32_t n_proofs;
   uint32_t pk_G0, pk_H0, dyn0;
-  uint32_t terms_per_proof;  // hasA*2 + 2L(N+2) + (2N+2) + 2
+  uint32_t terms_per_proof;  // hasA + 2L(N+2) + (2N+2) + 2
   uint32_t has_A;
 };
 
@@ -149,12 +149,9 @@ __global__ void wip_prove_kernel(ProveShape ps, ProveTables T, const uint32_t* _
   uint32_t* opi = out_pidx + (size_t)p * ps.terms_per_proof;
   S alpha = ld_mont<M>(alpha_all, p);
   uint32_t base = 0;
-  if (ps.has_A) {  // A = alpha*h + sum(bit ? G_i : -H_i)  (range/mod.rs:98-106 / :260-277); the sum is the K7 point
-    if (tid == 0) {
-      sc_store<M>(osc + 0, sc_load<M>(params + 8 * P_ALPHA)); opi[0] = 1;
-      sc_store<M>(osc + 8, S::one()); opi[1] = ps.dyn0 + p;
-    }
-    base = 2;
+  if (ps.has_A) {  // A = alpha*h + sum(bit ? G_i : -H_i)  (range/mod.rs:98-106 / :260-277); the sum is the K7 point, added when the proof is encoded
+    if (tid == 0) { sc_store<M>(osc + 0, sc_load<M>(params + 8 * P_ALPHA)); opi[0] = 1; }
+    base = 1;
   }
   const uint32_t offL = base, offR = base + L * (N + 2), offA = base + 2 * L * (N + 2), offB = offA + 2 * N + 2;
   for (uint32_t k = 0; k < L; k++) {
@@ -228,11 +225,11 @@ __global__ void wip_prove_kernel(ProveShape ps, ProveTables T, const uint32_t* _
   }
 }
 
-// K7: S_p = sum_i (bit_i ? G_i : -H_i), one block per proof, written as an affine table entry
+// K7: S_p = sum_i (bit_i ? G_i : -H_i), one block per proof, written as an extended point
 template <class C>
 __global__ void __launch_bounds__(128)
 range_bits_sum_kernel(ProveShape ps, const uint64_t* __restrict__ values, const uint32_t* __restrict__ tab0,
-                      uint32_t* __restrict__ dyn_aff) {
+                      uint32_t* __restrict__ out_ext) {
   __shared__ uint32_t sh[128 * C::EXT_WORDS];
   const uint32_t p = blockIdx.x, tid = threadIdx.x;
   typename C::Ext acc;
@@ -241,9 +238,7 @@ range_bits_sum_kernel(ProveShape ps, const uint64_t* __restrict__ values, const 
     uint32_t i1 = i % ps.n, i2 = i / ps.n;
     uint64_t v = values[(size_t)p * ps.m + i2];
     bool bit = i1 < 64 ? ((v >> i1) & 1) : false;
-    typename C::Aff q;
-    load_words<C::AFF_WORDS>(q, tab0 + (size_t)((bit ? ps.pk_G0 : ps.pk_H0) + i) * C::AFF_WORDS);
-    C::madd(acc, q, !bit);
+    C::madd_ptr(acc, tab0 + (size_t)((bit ? ps.pk_G0 : ps.pk_H0) + i) * C::AFF_WORDS, bit ? 0u : 1u);
   }
   uint32_t* mine = sh + tid * C::EXT_WORDS;
   *reinterpret_cast<typename C::Ext*>(mine) = acc;
@@ -256,11 +251,7 @@ range_bits_sum_kernel(ProveShape ps, const uint64_t* __restrict__ values, const 
     }
     __syncthreads();
   }
-  if (tid == 0) {
-    typename C::Aff q;
-    C::to_aff(q, acc);
-    store_words<C::AFF_WORDS>(dyn_aff + (size_t)p * C::AFF_WORDS, q);
-  }
+  if (tid == 0) store_words<C::EXT_WORDS>(out_ext + (size_t)p * C::EXT_WORDS, acc);
 }
 
 }  // namespace bpp

@@ -8,9 +8,12 @@
 // verify_multiple's exponents are exactly verify()'s multiplied by e^-2 (it divides the whole check
 // by e^2), so both paths use one kernel with a scale factor `lam` (1 or e^-2).
 //
-// Split in two phases: `verify_tables_kernel` computes everything that depends only on the
-// challenges (s-vector, powers of y, commitment exponents) once per challenge set;
-// `verify_scalars_kernel` combines it with each proof's (r', s', delta') and writes the MSM terms.
+// Every exponent of the MSM [wipB, wipA, A', g, h, L.., R.., G.., H.., V..] is affine in one of the
+// proof's scalars:    exponent_k = Tmul_k * x_k + Tadd_k,   x_k in {r', s', delta', r'*s'},
+// with Tmul, Tadd depending on the challenges only. `verify_tables_kernel` builds Tmul (Montgomery
+// form) and Tadd (canonical) once per challenge set — one batched inversion, running products, no
+// per-element exponentiation; `verify_scalars_kernel` then spends one Montgomery multiplication and
+// one modular addition per term and proof (Montgomery x canonical = canonical, so no conversions).
 #pragma once
 #include "scalar.cuh"
 
@@ -31,17 +34,13 @@ struct VerifyShape {
   uint32_t dyn0;          // table index of the first per-call point
 };
 
-// challenge-only tables, Montgomery form
+// challenge-only tables
 struct VerifyTables {
-  uint32_t* S;      // [N]  s_i * y^-(i+1)
-  uint32_t* Srev;   // [N]  s_{N-1-i}
-  uint32_t* Gc;     // [N]  commitment exponents of G
-  uint32_t* Hc;     // [N]
-  uint32_t* Vc;     // [nV]
-  uint32_t* misc;   // [8 + 2L] : gc, e, e^2, lam, y, (3 spare), ch_sqr[L], ch_inv_sqr[L]
-  uint32_t* tmp;    // [N] scratch (s-vector)
+  uint32_t* Tmul;   // [K]  Montgomery form (used for k = 3, 4 and the G, H ranges)
+  uint32_t* Tadd;   // [K]  canonical
+  uint32_t* tmp;    // [N + 64] scratch: s-vector (Montgomery), then small values
+  uint32_t* zpow;   // [m + 1] scratch: z^(2(j+1)) (Montgomery)
 };
-enum { VM_GC = 0, VM_E = 1, VM_E2 = 2, VM_LAM = 3, VM_Y = 4, VM_HDR = 8 };
 
 template <class M>
 BPP_DEV Sc<M> ld_mont(const uint32_t* p, size_t i) {
@@ -73,95 +72,133 @@ __device__ Sc<M> sum_powers_from1(const Sc<M>& x, uint32_t n) {
   return result;
 }
 
-// one block; ext_* are canonical inputs used only when mode == 0
+// one block of VT_THREADS threads; ext_* are canonical inputs used only when mode == 0
+constexpr int VT_THREADS = 512;
 template <class M>
-__global__ void verify_tables_kernel(VerifyShape vs, const uint32_t* __restrict__ params, const uint32_t* __restrict__ ext_Gc,
-                                     const uint32_t* __restrict__ ext_Hc, const uint32_t* __restrict__ ext_gc,
-                                     const uint32_t* __restrict__ ext_Vc, const uint32_t* __restrict__ ext_y, VerifyTables T) {
+__global__ void __launch_bounds__(VT_THREADS)
+verify_tables_kernel(VerifyShape vs, const uint32_t* __restrict__ params, const uint32_t* __restrict__ ext_Gc,
+                     const uint32_t* __restrict__ ext_Hc, const uint32_t* __restrict__ ext_gc,
+                     const uint32_t* __restrict__ ext_Vc, const uint32_t* __restrict__ ext_y, VerifyTables T) {
   typedef Sc<M> S;
   const uint32_t N = vs.N, L = vs.L, tid = threadIdx.x, nt = blockDim.x;
-  __shared__ uint32_t sh_einv[32 * 8];
-  __shared__ uint32_t sh_misc[4 * 8];  // yinv, s0
-  S y = vs.mode == 0 ? sc_load<M>(ext_y) : sc_load<M>(params + 8 * P_Y);
-  S z = sc_load<M>(params + 8 * P_Z);
-  S e = sc_load<M>(params + 8 * P_EFINAL);
-  // inverses of the round challenges (batch_invert, prime_field_elem.rs:239-248) and of y
-  if (tid < L) st_mont<M>(sh_einv, tid, sc_load<M>(params + 8 * (P_FIXED + tid)).inv());
-  if (tid == L) st_mont<M>(sh_misc, 0, y.inv());
+  const uint32_t K0 = 5 + 2 * L;  // first G term
+  // shared: inverses of e_0..e_{L-1}, y, e  (slots 0..L+1), scratch for the batch inversion, and a few broadcast values
+  __shared__ uint32_t sh_inv[34 * 8];
+  __shared__ uint32_t sh_scr[34 * 8];
+  __shared__ uint32_t sh_val[8 * 8];  // 0: lam*e2  1: -lam*e  2: y^N  3: lam
+  enum { V_LE2 = 0, V_NLE = 1, V_YN = 2, V_LAM = 3 };
+  const S y = vs.mode == 0 ? sc_load<M>(ext_y) : sc_load<M>(params + 8 * P_Y);
+  const S z = sc_load<M>(params + 8 * P_Z);
+  const S e = sc_load<M>(params + 8 * P_EFINAL);
+  // ---- phase 0: one inversion for all of e_k^-1 (batch_invert, prime_field_elem.rs:239-248), y^-1, e^-1 ----
+  if (tid < L) st_mont<M>(sh_inv, tid, sc_load<M>(params + 8 * (P_FIXED + tid)));
+  if (tid == L) st_mont<M>(sh_inv, L, y);
+  if (tid == L + 1) st_mont<M>(sh_inv, L + 1, e);
   __syncthreads();
+  if (tid == 0) sc_batch_invert<M>(sh_inv, sh_scr, L + 2);
+  __syncthreads();
+  const S yinv = ld_mont<M>(sh_inv, L), einv = ld_mont<M>(sh_inv, L + 1);
+  // ---- phase 1: s_0, per-round squares, broadcast values ----
   if (tid == 0) {
     S s0 = S::one();
-    for (uint32_t k = 0; k < L; k++) s0 = s0 * ld_mont<M>(sh_einv, k);
+    for (uint32_t k = 0; k < L; k++) s0 = s0 * ld_mont<M>(sh_inv, k);  // wip.rs:372
     st_mont<M>(T.tmp, 0, s0);
-    S e2 = e * e;
-    S lam = vs.mode == 2 ? e2.inv() : S::one();
-    st_mont<M>(T.misc, VM_E, e);
-    st_mont<M>(T.misc, VM_E2, e2);
-    st_mont<M>(T.misc, VM_LAM, lam);
-    st_mont<M>(T.misc, VM_Y, y);
   }
-  if (tid < L) {
-    S ek = sc_load<M>(params + 8 * (P_FIXED + tid)), ei = ld_mont<M>(sh_einv, tid);
-    st_mont<M>(T.misc, VM_HDR + tid, ek * ek);
-    st_mont<M>(T.misc, VM_HDR + L + tid, ei * ei);
+  if (tid == 32) {
+    S e2 = e * e;
+    S lam = vs.mode == 2 ? einv * einv : S::one();
+    st_mont<M>(sh_val, V_LE2, lam * e2);
+    st_mont<M>(sh_val, V_NLE, -(lam * e));
+    st_mont<M>(sh_val, V_LAM, lam);
+    // constant terms: exponents of wipB, wipA, A' are lam * [1, e, e^2]  (wip.rs:257-262 scaled)
+    sc_store<M>(T.Tadd + 8 * 0, lam);
+    sc_store<M>(T.Tadd + 8 * 1, lam * e);
+    sc_store<M>(T.Tadd + 8 * 2, lam * e2);
+    // g: lam * (-(r' s' y) + gc e^2) -> Tmul = -lam*y (times r'*s');  h: lam * (-delta') -> Tmul = -lam, Tadd = 0
+    st_mont<M>(T.Tmul, 3, -(lam * y));
+    st_mont<M>(T.Tmul, 4, -lam);
+    sc_store<M>(T.Tadd + 8 * 4, S::zero());
+  }
+  if (tid == 64) st_mont<M>(sh_val, V_YN, y.pow_u64(N));
+  __syncthreads();
+  const S le2 = ld_mont<M>(sh_val, V_LE2), nle = ld_mont<M>(sh_val, V_NLE);
+  if (tid < L) {  // L_j, R_j exponents: lam * e^2 * e_j^(+-2)  (wip.rs:265-273)
+    S ek = sc_load<M>(params + 8 * (P_FIXED + tid)), ei = ld_mont<M>(sh_inv, tid);
+    S ek2 = ek * ek;
+    st_mont<M>(sh_scr, tid, ek2);
+    sc_store<M>(T.Tadd + 8 * (5 + tid), le2 * ek2);
+    sc_store<M>(T.Tadd + 8 * (5 + L + tid), le2 * (ei * ei));
   }
   __syncthreads();
   // s_i = s_{i-k} * e^2_{L-1-log2 i}  (weighted_inner_product_proof.rs:372-380), level by level
   for (uint32_t t = 0; t < L; t++) {
-    S f = ld_mont<M>(T.misc, VM_HDR + (L - 1 - t));
+    S f = ld_mont<M>(sh_scr, L - 1 - t);
     uint32_t half = 1u << t;
     for (uint32_t j = tid; j < half; j += nt) st_mont<M>(T.tmp, half + j, ld_mont<M>(T.tmp, j) * f);
     __syncthreads();
   }
-  S yinv = ld_mont<M>(sh_misc, 0);
-  for (uint32_t i = tid; i < N; i += nt) {
-    st_mont<M>(T.S, i, ld_mont<M>(T.tmp, i) * yinv.pow_u64(i + 1));
-    st_mont<M>(T.Srev, i, ld_mont<M>(T.tmp, N - 1 - i));
+  // ---- phase 2: G and H terms, a contiguous chunk of indices per thread, running products ----
+  const bool range = vs.mode != 0, single = vs.mode == 1;
+  const S zz = z * z;
+  if (range) {  // z^(2(j+1)) (range/mod.rs:287 / :430-433)
+    for (uint32_t j = tid; j < vs.m; j += nt) st_mont<M>(T.zpow, j, zz.pow_u64(j + 1));
   }
-  // commitment exponents
-  if (vs.mode == 0) {
-    for (uint32_t i = tid; i < N; i += nt) {
-      st_mont<M>(T.Gc, i, sc_load<M>(ext_Gc + 8 * i));
-      st_mont<M>(T.Hc, i, sc_load<M>(ext_Hc + 8 * i));
+  __syncthreads();
+  {
+    const uint32_t ch = (N + nt - 1) / nt;
+    const uint32_t i0 = tid * ch, i1 = (i0 + ch < N) ? i0 + ch : N;
+    if (i0 < N) {
+      S yi = yinv.pow_u64(i0);  // y^-i
+      const S yN = ld_mont<M>(sh_val, V_YN), two = S::from_u64(2);
+      S p2 = range ? two.pow_u64(i0 % vs.n) : S::zero();
+      const S gconst = le2 * (-z);
+      for (uint32_t i = i0; i < i1; i++) {
+        // G_i: lam * (-(s_i y^-(i+1)) (r' e y) + Gc_i e^2) = [-lam e s_i y^-i] r' + lam e^2 Gc_i   (wip.rs:275-282)
+        st_mont<M>(T.Tmul, K0 + i, nle * ld_mont<M>(T.tmp, i) * yi);
+        // H_i: lam * (-(s' e) s_{N-1-i} + Hc_i e^2)                                              (wip.rs:284-288)
+        st_mont<M>(T.Tmul, K0 + N + i, nle * ld_mont<M>(T.tmp, N - 1 - i));
+        if (range) {
+          // d_i = 2^(i mod n) [* z^(2(j+1))]  (range/mod.rs:214-218 single, :435-438 multiple)
+          if (i != i0 && i % vs.n == 0) p2 = S::one();
+          S d = single ? p2 : p2 * ld_mont<M>(T.zpow, i / vs.n);
+          sc_store<M>(T.Tadd + 8 * (K0 + i), gconst);                          // Gc_i = -z  (range/mod.rs:213 / :456-459)
+          sc_store<M>(T.Tadd + 8 * (K0 + N + i), le2 * (d * (yN * yi) + z));   // Hc_i = d_i y^(N-i) + z  (:214-218 / :461-465)
+          p2 = p2 + p2;
+        } else {
+          sc_store<M>(T.Tadd + 8 * (K0 + i), le2 * sc_load<M>(ext_Gc + 8 * i));
+          sc_store<M>(T.Tadd + 8 * (K0 + N + i), le2 * sc_load<M>(ext_Hc + 8 * i));
+        }
+        yi = yi * yinv;
+      }
     }
-    for (uint32_t j = tid; j < vs.nV; j += nt) st_mont<M>(T.Vc, j, sc_load<M>(ext_Vc + 8 * j));
-    if (tid == 0) st_mont<M>(T.misc, VM_GC, sc_load<M>(ext_gc));
-  } else {
-    const bool single = vs.mode == 1;
-    S zz = z * z, mz = -z;
-    S y_N1 = y.pow_u64((uint64_t)N + 1);
-    for (uint32_t i = tid; i < N; i += nt) {
-      // d_i = 2^(i mod n) [* z^(2(j+1))]  (range/mod.rs:214-218 single, :435-438 multiple)
-      S d = S::from_u64(2).pow_u64(i % vs.n);
-      if (!single) d = d * zz.pow_u64(i / vs.n + 1);
-      st_mont<M>(T.Gc, i, mz);                                // range/mod.rs:213 / :456-459
-      st_mont<M>(T.Hc, i, d * y.pow_u64(N - i) + z);          // range/mod.rs:214-218 / :461-465
-    }
-    for (uint32_t j = tid; j < vs.nV; j += nt)                // range/mod.rs:219 / :475-477
-      st_mont<M>(T.Vc, j, single ? y_N1 : zz.pow_u64(j + 1) * y_N1);
-    if (tid == 0) {
+  }
+  // ---- phase 3: V terms and the g constant ----
+  if (range) {
+    const S y_N1 = ld_mont<M>(sh_val, V_YN) * y;
+    for (uint32_t j = tid; j < vs.nV; j += nt)  // range/mod.rs:219 / :475-477
+      sc_store<M>(T.Tadd + 8 * (K0 + 2 * N + j), le2 * (single ? y_N1 : ld_mont<M>(T.zpow, j) * y_N1));
+    if (tid == nt - 1) {
       S sum_y = sum_powers_from1<M>(y, N);
       S sum_2 = S::from_u64(2).pow_u64(vs.n) - S::one();
       S gc;
-      if (single) gc = sum_y * (z - zz) - sum_2 * y_N1 * z;                       // range/mod.rs:221-226
+      if (single) gc = sum_y * (z - zz) - sum_2 * y_N1 * z;                           // range/mod.rs:221-226
       else gc = sum_y * (z - zz) - y_N1 * z * sum_2 * sum_powers_from1<M>(zz, vs.m);  // range/mod.rs:467-471
-      st_mont<M>(T.misc, VM_GC, gc);
+      sc_store<M>(T.Tadd + 8 * 3, le2 * gc);
     }
+  } else {
+    for (uint32_t j = tid; j < vs.nV; j += nt) sc_store<M>(T.Tadd + 8 * (K0 + 2 * N + j), le2 * sc_load<M>(ext_Vc + 8 * j));
+    if (tid == nt - 1) sc_store<M>(T.Tadd + 8 * 3, le2 * sc_load<M>(ext_gc));
   }
 }
 
-// grid: (ceil(K / blockDim), n_proofs). Writes K = 5 + 2L + 2N + nV terms per proof:
-//   [wipB, wipA, A', g, h, L.., R.., G.., H.., V..] with exponents lam * [1, e, e^2, g_exp, h_exp, ...]
+// thread per proof: parse and check (r', s', delta'); per-proof scalars x = [r', s', delta', r'*s'] (canonical) -> xs[p][4][8]
 // proofs: wire layout A | L[L] | R[L] | wipA | wipB | r' | s' | d'   (include/bpp.h)
 template <class M>
-__global__ void verify_scalars_kernel(VerifyShape vs, VerifyTables T, const uint8_t* __restrict__ proofs, size_t proof_stride,
-                                      size_t scalar_off, uint32_t* __restrict__ out_scalars, uint32_t* __restrict__ out_pidx,
-                                      uint8_t* __restrict__ bad_scalar) {
+__global__ void verify_proof_scalars_kernel(uint32_t n_proofs, const uint8_t* __restrict__ proofs, size_t proof_stride, size_t scalar_off,
+                                            uint32_t* __restrict__ xs, uint8_t* __restrict__ bad_scalar) {
   typedef Sc<M> S;
-  const uint32_t N = vs.N, L = vs.L, K = 5 + 2 * L + 2 * N + vs.nV;
-  const uint32_t p = blockIdx.y;
-  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= K) return;
+  uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_proofs) return;
   const uint8_t* sb = proofs + (size_t)p * proof_stride + scalar_off;
   uint32_t raw[3][8];
   bool ok = true;
@@ -174,39 +211,46 @@ __global__ void verify_scalars_kernel(VerifyShape vs, VerifyTables T, const uint
     }
     ok = ok && S::canonical_ok(raw[j]);
   }
-  if (k == 0) bad_scalar[p] = ok ? 0 : 1;
+  bad_scalar[p] = ok ? 0 : 1;
   if (!ok) {  // keep the MSM well-formed; the verdict is FORMAT regardless of its result
 #pragma unroll
     for (int j = 0; j < 3; j++)
       for (int i = 0; i < 8; i++) raw[j][i] = 0;
   }
-  S rp = sc_load<M>(raw[0]), sp = sc_load<M>(raw[1]), dp = sc_load<M>(raw[2]);
-  S e = ld_mont<M>(T.misc, VM_E), e2 = ld_mont<M>(T.misc, VM_E2), lam = ld_mont<M>(T.misc, VM_LAM), y = ld_mont<M>(T.misc, VM_Y);
+  uint32_t* o = xs + (size_t)p * 32;
+  for (int j = 0; j < 3; j++)
+    for (int i = 0; i < 8; i++) o[8 * j + i] = raw[j][i];
+  S rs = sc_load<M>(raw[0]) * S::raw(raw[1]);  // Montgomery x canonical = canonical r' * s'
+  for (int i = 0; i < 8; i++) o[24 + i] = rs.v[i];
+}
+
+// grid: (ceil(K / blockDim), n_proofs). Writes K = 5 + 2L + 2N + nV terms per proof:
+//   [wipB, wipA, A', g, h, L.., R.., G.., H.., V..] with exponents lam * [1, e, e^2, g_exp, h_exp, ...]  (wip.rs:297-318)
+template <class M>
+__global__ void verify_scalars_kernel(VerifyShape vs, VerifyTables T, const uint32_t* __restrict__ xs,
+                                      uint32_t* __restrict__ out_scalars, uint32_t* __restrict__ out_pidx) {
+  typedef Sc<M> S;
+  const uint32_t N = vs.N, L = vs.L, K = 5 + 2 * L + 2 * N + vs.nV;
+  const uint32_t p = blockIdx.y;
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
   const uint32_t dyn = vs.dyn0 + p * (2 * L + 3);  // this proof's decoded points: A, L.., R.., wipA, wipB
-  S val;
+  const uint32_t* x = xs + (size_t)p * 32;
+  S val = S::raw(T.Tadd + 8 * k);
   uint32_t idx;
-  if (k == 0) { val = lam; idx = dyn + 2 * L + 2; }                   // wipB
-  else if (k == 1) { val = lam * e; idx = dyn + 2 * L + 1; }          // wipA
-  else if (k == 2) { val = lam * e2; idx = dyn; }                     // A' (RangeProof.A)
-  else if (k == 3) { val = lam * ((-rp) * y * sp + ld_mont<M>(T.misc, VM_GC) * e2); idx = 0; }  // wip.rs:290
-  else if (k == 4) { val = lam * (-dp); idx = 1; }                                              // wip.rs:292
-  else if (k < 5 + L) { uint32_t j = k - 5; val = lam * ld_mont<M>(T.misc, VM_HDR + j) * e2; idx = dyn + 1 + j; }          // wip.rs:265-268
-  else if (k < 5 + 2 * L) { uint32_t j = k - 5 - L; val = lam * ld_mont<M>(T.misc, VM_HDR + L + j) * e2; idx = dyn + 1 + L + j; }  // :270-273
-  else if (k < 5 + 2 * L + N) {  // wip.rs:275-282
-    uint32_t i = k - 5 - 2 * L;
-    val = lam * ((-ld_mont<M>(T.S, i)) * (rp * e * y) + ld_mont<M>(T.Gc, i) * e2);
-    idx = vs.pk_G0 + i;
-  } else if (k < 5 + 2 * L + 2 * N) {  // wip.rs:284-288
-    uint32_t i = k - 5 - 2 * L - N;
-    val = lam * ((-ld_mont<M>(T.Srev, i)) * (sp * e) + ld_mont<M>(T.Hc, i) * e2);
-    idx = vs.pk_H0 + i;
-  } else {  // wip.rs:294-297
-    uint32_t j = k - 5 - 2 * L - 2 * N;
-    val = lam * ld_mont<M>(T.Vc, j) * e2;
-    idx = vs.dyn0 + vs.n_proofs * (2 * L + 3) + p * vs.nV + j;
-  }
-  size_t o = (size_t)p * K + k;
-  sc_store<M>(out_scalars + 8 * o, val);
+  if (k == 0) idx = dyn + 2 * L + 2;                                                   // wipB
+  else if (k == 1) idx = dyn + 2 * L + 1;                                              // wipA
+  else if (k == 2) idx = dyn;                                                          // A' (RangeProof.A)
+  else if (k == 3) { val = val + S::raw(T.Tmul + 8 * 3) * S::raw(x + 24); idx = 0; }   // g  (wip.rs:290)
+  else if (k == 4) { val = S::raw(T.Tmul + 8 * 4) * S::raw(x + 16); idx = 1; }         // h  (wip.rs:292)
+  else if (k < 5 + L) idx = dyn + 1 + (k - 5);                                         // L_j (wip.rs:265-268)
+  else if (k < 5 + 2 * L) idx = dyn + 1 + L + (k - 5 - L);                             // R_j (:270-273)
+  else if (k < 5 + 2 * L + N) { val = val + S::raw(T.Tmul + 8 * k) * S::raw(x); idx = vs.pk_G0 + (k - 5 - 2 * L); }              // G_i (:275-282)
+  else if (k < 5 + 2 * L + 2 * N) { val = val + S::raw(T.Tmul + 8 * k) * S::raw(x + 8); idx = vs.pk_H0 + (k - 5 - 2 * L - N); }  // H_i (:284-288)
+  else idx = vs.dyn0 + vs.n_proofs * (2 * L + 3) + p * vs.nV + (k - 5 - 2 * L - 2 * N);                                           // V_j (:294-297)
+  const size_t o = (size_t)p * K + k;
+#pragma unroll
+  for (int i = 0; i < 8; i++) out_scalars[8 * o + i] = val.v[i];
   out_pidx[o] = idx;
 }
 

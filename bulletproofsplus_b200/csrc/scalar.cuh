@@ -2,7 +2,8 @@
 // ell (Ristretto255), n (secp256k1) and r (BLS12-381). Device stand-in for the reference's
 // PrimeFieldElem (src/bls12_381/building_block/scalar/prime_field_elem.rs:12-248: new(i32) :191-195,
 // Add/Sub/Mul :51-120, Neg :158-182, inv :229-236). Scalar work is < 1 % of the path,
-// so this is written for clarity: 64-bit C accumulation, which nvcc lowers to IMAD.WIDE.U32.
+// but its latency sits on the critical path of the challenge-only table kernels: the product reuses the base field's
+// IMAD.WIDE carry-chain schoolbook, the Montgomery reduction is 64-bit C that nvcc lowers to IMAD.WIDE.U32.
 #pragma once
 #include <cstdint>
 #include "fe25519.cuh"  // BPP_DEV
@@ -80,41 +81,35 @@ struct Sc {
     return r;
   }
   BPP_DEV Sc operator-() const { return zero() - *this; }
-  // Montgomery product, CIOS
-  BPP_DEV friend Sc operator*(const Sc& a, const Sc& b) {
-    uint32_t t[10];
-#pragma unroll
-    for (int i = 0; i < 10; i++) t[i] = 0;
+  // Montgomery reduction of a 16-limb value t < M * 2^256: returns t * 2^-256 mod M, fully reduced. Rows are written so that
+  // row i+1 only waits for limb i+1 of row i (the rows pipeline), and limbs of M that are zero constants fold away.
+  BPP_DEV static Sc mont_reduce(uint32_t* t) {
+    uint32_t extra = 0;
 #pragma unroll
     for (int i = 0; i < 8; i++) {
+      const uint32_t m = t[i] * M::NINV;
       uint64_t c = 0;
 #pragma unroll
       for (int j = 0; j < 8; j++) {
-        c += (uint64_t)a.v[j] * b.v[i] + t[j];
-        t[j] = (uint32_t)c;
+        c += (uint64_t)m * M::mod(j) + t[i + j];
+        t[i + j] = (uint32_t)c;
         c >>= 32;
       }
-      c += t[8];
-      t[8] = (uint32_t)c;
-      t[9] = (uint32_t)(c >> 32);
-      uint32_t m = t[0] * M::NINV;
-      c = (uint64_t)m * M::mod(0) + t[0];
-      c >>= 32;
-#pragma unroll
-      for (int j = 1; j < 8; j++) {
-        c += (uint64_t)m * M::mod(j) + t[j];
-        t[j - 1] = (uint32_t)c;
-        c >>= 32;
-      }
-      c += t[8];
-      t[7] = (uint32_t)c;
-      t[8] = t[9] + (uint32_t)(c >> 32);
+      c += (uint64_t)t[i + 8] + extra;
+      t[i + 8] = (uint32_t)c;
+      extra = (uint32_t)(c >> 32);
     }
-    if (t[8] || geq_mod(t)) sub_mod(t);
+    if (extra || geq_mod(t + 8)) sub_mod(t + 8);
     Sc r;
 #pragma unroll
-    for (int i = 0; i < 8; i++) r.v[i] = t[i];
+    for (int i = 0; i < 8; i++) r.v[i] = t[8 + i];
     return r;
+  }
+  // Montgomery product: 8x8 schoolbook (IMAD.WIDE carry chains, shared with the base field) + reduction
+  BPP_DEV friend Sc operator*(const Sc& a, const Sc& b) {
+    uint32_t t[16];
+    fe25519_mul_wide(t, a.v, b.v);
+    return mont_reduce(t);
   }
   BPP_DEV Sc sqr() const { return *this * *this; }
   BPP_DEV bool is_zero() const { uint32_t o = 0; for (int i = 0; i < 8; i++) o |= v[i]; return o == 0; }
@@ -127,11 +122,20 @@ struct Sc {
     return a * r2;
   }
   BPP_DEV void to_canonical(uint32_t* limbs) const {
-    Sc o = zero();
-    o.v[0] = 1;
-    Sc r = *this * o;
+    uint32_t t[16];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { t[i] = v[i]; t[8 + i] = 0; }
+    Sc r = mont_reduce(t);
 #pragma unroll
     for (int i = 0; i < 8; i++) limbs[i] = r.v[i];
+  }
+  // the limbs as they are (no conversion): for values kept canonical, where a * b with a in Montgomery form and b
+  // canonical is already the canonical product
+  BPP_DEV static Sc raw(const uint32_t* limbs) {
+    Sc a;
+#pragma unroll
+    for (int i = 0; i < 8; i++) a.v[i] = limbs[i];
+    return a;
   }
   BPP_DEV static bool canonical_ok(const uint32_t* limbs) { return !geq_mod(limbs); }
   BPP_DEV static Sc from_u64(uint64_t x) {
@@ -171,6 +175,24 @@ struct Sc {
     return r;
   }
 };
+
+// Montgomery's trick: x[0..n) (stride 8 words, Montgomery form, all non-zero) -> their inverses, in place; one
+// Fermat inversion. scratch: n * 8 words.
+template <class M>
+__device__ __noinline__ void sc_batch_invert(uint32_t* x, uint32_t* scratch, uint32_t n) {
+  Sc<M> acc = Sc<M>::one();
+  for (uint32_t i = 0; i < n; i++) {
+    for (int k = 0; k < 8; k++) scratch[8 * i + k] = acc.v[k];
+    acc = acc * Sc<M>::raw(x + 8 * i);
+  }
+  acc = acc.inv();
+  for (int i = (int)n - 1; i >= 0; i--) {
+    Sc<M> xi = Sc<M>::raw(x + 8 * i);
+    Sc<M> inv_i = acc * Sc<M>::raw(scratch + 8 * i);
+    acc = acc * xi;
+    for (int k = 0; k < 8; k++) x[8 * i + k] = inv_i.v[k];
+  }
+}
 
 template <class M>
 BPP_DEV Sc<M> sc_load(const uint32_t* canonical) { return Sc<M>::from_canonical(canonical); }
