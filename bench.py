@@ -310,6 +310,9 @@ def main():
 
     extras = {}
     cpu = None
+    split = None
+    if not args.no_extras and world > 1:
+        split = run_msm_split(args, torch, dist, api, _lib, ctx, dev, stream, rank, world, int_peak)
     if not args.no_extras and rank == 0:
         extras = run_extras(args, torch, api, _lib, ctx, pk, dev, stream, int_peak)
     if not args.no_extras and rank == 0 and world == 1:
@@ -331,9 +334,58 @@ def main():
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         }
         line.update(extras)
+        if split:
+            line["msm_point_range_split"] = split
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_msm_split(args, torch, dist, api, _lib, ctx, dev, stream, rank, world, int_peak):
+    """One MSM of 2^msm_max_log points split by point range over the ranks: per-rank MSM to one raw
+    partial point, NCCL all-gather of world x 128 B, local sum + encode. Strong scaling; time = max over ranks."""
+    lib = ctx.lib
+    n_total = 1 << args.msm_max_log
+    n_loc = n_total // world
+    g = torch.Generator().manual_seed(1234 + rank)
+    mult = torch.randint(0, 256, (n_loc, 32), dtype=torch.uint8, generator=g)
+    mult[:, 31] &= 0x0F
+    pts = api.Points.from_multipliers(bytes(mult.numpy().tobytes()), _lib.RISTRETTO255, ctx)
+    sc = torch.randint(0, 256, (n_loc, 32), dtype=torch.uint8, generator=g)
+    sc[:, 31] &= 0x0F
+    d_sc = sc.to(dev)
+    d_raw = torch.empty(128, dtype=torch.uint8, device=dev)
+    d_all = torch.empty(128 * world, dtype=torch.uint8, device=dev)
+    d_out = torch.empty(32, dtype=torch.uint8, device=dev)
+
+    def step():
+        ctx.check(lib.bpp_msm_prepared_raw_dev(ctx.h, pts.h, d_sc.data_ptr(), n_loc, d_raw.data_ptr()), "msm_raw_dev")
+        dist.all_gather_into_tensor(d_all, d_raw)
+        ctx.check(lib.bpp_points_sum_raw_dev(ctx.h, 0, d_all.data_ptr(), world, d_out.data_ptr()), "sum_raw_dev")
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    outs = [torch.empty(32, dtype=torch.uint8, device=dev) for _ in range(world)]
+    dist.all_gather(outs, d_out)
+    same = all(bool((o == outs[0]).all()) for o in outs)
+    reps = 5
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0.record(stream)
+    for _ in range(reps):
+        step()
+    e1.record(stream)
+    dist.barrier()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0])
+    W, _, _ = algorithmic_field_muls(n_total)
+    return {"log2_n": args.msm_max_log, "n_gpus": world, "ms": ms, "points_per_sec": n_total / (ms * 1e-3), "scaling": "strong",
+            "all_ranks_agree": same, "exchange": f"all-gather of {world} x 128 B partial points + local sum",
+            "int_roofline_frac_per_gpu": W * FIELD_MUL_IMAD / (ms * 1e-3) / int_peak / world}
 
 
 def run_extras(args, torch, api, _lib, ctx, pk, dev, stream, int_peak):

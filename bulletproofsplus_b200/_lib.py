@@ -18,7 +18,7 @@ SYMBOLS = [
     "bpp_init", "bpp_destroy", "bpp_last_error", "bpp_point_bytes", "bpp_range_proof_len", "bpp_wip_proof_len",
     "bpp_kernel_launches", "bpp_sync", "bpp_pk_new", "bpp_pk_export", "bpp_pk_len", "bpp_pk_free", "bpp_commit_batch", "bpp_msm",
     "bpp_points_upload", "bpp_points_from_multipliers", "bpp_points_len", "bpp_points_free", "bpp_msm_prepared",
-    "bpp_msm_prepared_dev", "bpp_raw_point_bytes", "bpp_msm_prepared_raw", "bpp_points_sum_raw", "bpp_range_prove_batch",
+    "bpp_msm_prepared_dev", "bpp_raw_point_bytes", "bpp_msm_prepared_raw", "bpp_points_sum_raw", "bpp_msm_prepared_raw_dev", "bpp_points_sum_raw_dev", "bpp_range_prove_batch",
     "bpp_range_verify_batch", "bpp_range_prove_batch_dev", "bpp_range_verify_batch_dev", "bpp_range_prove", "bpp_range_verify",
     "bpp_wip_prove", "bpp_wip_verify", "bpp_int_peak_probe", "bpp_hot_kernel_stats", "bpp_debug_op",
 ]
@@ -74,6 +74,8 @@ def load() -> C.CDLL:
     L.bpp_msm_prepared_dev.argtypes = [vp, vp, vp, sz, sz, vp]
     L.bpp_msm_prepared_raw.argtypes = [vp, vp, u8p, sz, u8p]
     L.bpp_points_sum_raw.argtypes = [vp, i, u8p, sz, u8p]
+    L.bpp_msm_prepared_raw_dev.argtypes = [vp, vp, vp, sz, vp]
+    L.bpp_points_sum_raw_dev.argtypes = [vp, i, vp, sz, vp]
     L.bpp_range_prove_batch.argtypes = [vp, vp, sz, sz, sz, C.POINTER(C.c_uint64), u8p, pp, u8p]
     L.bpp_range_verify_batch.argtypes = [vp, vp, sz, sz, sz, u8p, u8p, pp, u8p]
     L.bpp_range_prove_batch_dev.argtypes = [vp, vp, sz, sz, sz, vp, vp, pp, vp]

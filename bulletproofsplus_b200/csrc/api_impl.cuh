@@ -206,6 +206,19 @@ struct Api {
     BPP_LAUNCH(points_encode_kernel<C>, ceil_div(J, 64), 64, 0, J, ctx->buf[B_RESULTS].as<uint32_t>(), reinterpret_cast<uint8_t*>(d_out));
     return BPP_OK;
   }
+  static int msm_prepared_raw_dev(bpp_ctx* ctx, const bpp_points* pts, const void* d_scalars, size_t k, void* d_out_raw) {
+    BPP_TRY(clear_flags(ctx));
+    BPP_TRY(msm_prepared_core(ctx, pts, reinterpret_cast<const uint32_t*>(d_scalars), k, 1));
+    BPP_CK(cudaMemcpyAsync(d_out_raw, ctx->buf[B_RESULTS].p, (size_t)C::EXT_WORDS * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    return BPP_OK;
+  }
+  static int points_sum_raw_dev(bpp_ctx* ctx, const void* d_raw, size_t count, void* d_out) {
+    if (count == 0 || count > (1u << 20)) return BPP_ERR_LENGTH;
+    BPP_CK(ctx->buf[B_RESULTS].ensure(C::EXT_WORDS * 4));
+    BPP_LAUNCH(ext_sum_kernel<C>, 1, 128, 0, (uint32_t)count, reinterpret_cast<const uint32_t*>(d_raw), ctx->buf[B_RESULTS].as<uint32_t>());
+    BPP_LAUNCH(points_encode_kernel<C>, 1, 32, 0, 1u, ctx->buf[B_RESULTS].as<uint32_t>(), reinterpret_cast<uint8_t*>(d_out));
+    return BPP_OK;
+  }
   static int msm(bpp_ctx* ctx, const uint8_t* scalars, const uint8_t* points, size_t k, uint8_t* out) {
     if (k == 0) {  // empty MulVec: Point::zero()
       bpp_points* one = nullptr;

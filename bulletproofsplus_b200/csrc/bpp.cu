@@ -165,6 +165,16 @@ int bpp_points_sum_raw(bpp_ctx* ctx, int curve, const uint8_t* raw_points, size_
   BPP_DISPATCH(curve, ApiT::points_sum_raw(ctx, raw_points, count, out_point));
 }
 
+int bpp_msm_prepared_raw_dev(bpp_ctx* ctx, const bpp_points* pts, const void* d_scalars, size_t k, void* d_out_raw) {
+  BPP_ENTER(ctx);
+  if (!pts) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pts->curve, ApiT::msm_prepared_raw_dev(ctx, pts, d_scalars, k, d_out_raw));
+}
+int bpp_points_sum_raw_dev(bpp_ctx* ctx, int curve, const void* d_raw_points, size_t count, void* d_out_point) {
+  BPP_ENTER(ctx);
+  BPP_DISPATCH(curve, ApiT::points_sum_raw_dev(ctx, d_raw_points, count, d_out_point));
+}
+
 int bpp_range_prove_batch(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint64_t* v, const uint8_t* gamma,
                           const bpp_params* params, uint8_t* proofs) {
   BPP_ENTER(ctx);

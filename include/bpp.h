@@ -93,6 +93,10 @@ int bpp_msm_prepared_dev(bpp_ctx* ctx, const bpp_points* pts, const void* d_scal
 int bpp_raw_point_bytes(int curve);
 int bpp_msm_prepared_raw(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, uint8_t* out_raw);
 int bpp_points_sum_raw(bpp_ctx* ctx, int curve, const uint8_t* raw_points, size_t count, uint8_t* out_point);
+/* device-pointer forms of the two above (asynchronous on the context's stream): the NCCL all-gather of the per-rank
+ * partial sums sits between them (point addition is not an NCCL reduction operator) */
+int bpp_msm_prepared_raw_dev(bpp_ctx* ctx, const bpp_points* pts, const void* d_scalars, size_t k, void* d_out_raw);
+int bpp_points_sum_raw_dev(bpp_ctx* ctx, int curve, const void* d_raw_points, size_t count, void* d_out_point);
 
 /* ---- RangeProof::prove / verify (range/mod.rs:31-78) ---------------------------------------------- */
 /* `count` independent proofs, each aggregating m values of n bits against pk (bpp_pk_len(pk) == n*m).

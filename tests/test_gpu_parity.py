@@ -361,3 +361,48 @@ def test_golden_fixture_proofs(api, ctx, name):
     V = pk.commit_batch(fx["v"], gs)
     assert b"".join(V).hex() == fx["V"]
     assert api.verify_batch(pk, n, m, [bytes.fromhex(fx["proof"])], [V]) == [0]
+
+
+# ---------------------------------------------------------------------------------- multi-GPU decomposition, one GPU
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_sharded_msm_point_range_split(api, ctx, oracle, world):
+    """The N-range split of one MSM: per-"rank" partial sums in the raw device form + bpp_points_sum_raw equal the
+    unsplit result and the oracle's (sum s_i k_i) * g. The ranks are emulated as slices on one GPU."""
+    from bulletproofsplus_b200 import parallel
+    rng = random.Random(world)
+    k = 1500
+    mult = [rng.randrange(ELL) for _ in range(k)]
+    sc = [rng.randrange(ELL) for _ in range(k)]
+    want = oracle.scalar_mul(R, sum(a * b for a, b in zip(mult, sc)) % ELL)
+    raws = b""
+    for r in range(world):
+        lo, hi = parallel.shard_range(k, r, world)
+        pts = api.Points.from_multipliers(b"".join(le32(x) for x in mult[lo:hi]), R, ctx)
+        raws += pts.msm_raw(b"".join(le32(x) for x in sc[lo:hi]))
+    assert api.points_sum_raw(raws, R, ctx) == want
+    whole = api.Points.from_multipliers(b"".join(le32(x) for x in mult), R, ctx)
+    assert whole.msm(b"".join(le32(x) for x in sc))[0] == want
+
+
+def test_sharded_verify_blocks_match_whole_batch(api, ctx, oracle):
+    """Block-sharding a batch of proofs (parallel.verify_batch_sharded without a process group = world 1, and manual
+    2-way blocks) gives the verdicts of the whole batch."""
+    from bulletproofsplus_b200 import parallel
+    n, m, count = 16, 2, 7
+    pk = api.PublicKey.new(n * m, R, ctx)
+    rng = random.Random(9)
+    vs = [rng.randrange(2**n) for _ in range(count * m)]
+    gs = [rng.randrange(ELL) for _ in range(count * m)]
+    proofs = api.prove_batch(pk, n, m, vs, gs)
+    Vs = pk.commit_batch(vs, gs)
+    Vl = [Vs[i * m:(i + 1) * m] for i in range(count)]
+    bad = bytearray(proofs[5]); bad[40] ^= 4
+    proofs[5] = bytes(bad)
+    whole = api.verify_batch(pk, n, m, proofs, Vl)
+    assert whole == [oracle.range_verify(R, n, m, b"".join(Vl[i]), proofs[i]) for i in range(count)]
+    assert parallel.verify_batch_sharded(lambda p, c: api.verify_batch(pk, n, m, list(p), list(c)), proofs, Vl) == whole
+    blocks = []
+    for r in range(2):
+        lo, hi = parallel.shard_range(count, r, 2)
+        blocks += api.verify_batch(pk, n, m, proofs[lo:hi], Vl[lo:hi])
+    assert blocks == whole
