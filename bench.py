@@ -146,10 +146,28 @@ def run_reference(args, rank):
             "config": {"workload": "range-proof verify n=64 m=16, Ristretto255, reference CPU algorithm (oracle port)"},
             "cpu_baseline": {"value": total, "unit": "proofs/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": total, "unit": "proofs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """The one JSON line goes to the real stdout; everything else a library prints (NCCL banners, torchrun notices) was
+    rerouted to stderr by quiet_stdout()."""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
+def quiet_stdout():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
 
 
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -336,7 +354,7 @@ def main():
         line.update(extras)
         if split:
             line["msm_point_range_split"] = split
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
