@@ -13,7 +13,7 @@ inline bool host_scalar_ok(const uint8_t* s, const uint8_t* order_le) {
   return false;
 }
 
-__global__ void prove_jobstart_kernel(uint32_t n_proofs, uint32_t L, uint32_t N, uint32_t has_A, uint32_t terms_per_proof,
+static __global__ void prove_jobstart_kernel(uint32_t n_proofs, uint32_t L, uint32_t N, uint32_t has_A, uint32_t terms_per_proof,
                                       uint32_t* __restrict__ job_start) {
   const uint32_t J = has_A + 2 * L + 2;
   uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;

@@ -1,18 +1,30 @@
 // libbpp_b200.so — extern "C" surface (include/bpp.h). Dispatches on the curve id to the templated
 // launch sequences in api_impl.cuh. No CPU fallback exists: every entry point needs a live bpp_ctx,
 // and bpp_init fails when there is no CUDA device.
-#include "ed25519.cuh"
-#include "api_impl.cuh"
-#include "debug_ops.cuh"
+#include "fe25519.cuh"
+#include "engine.cuh"
+#include "proto_misc.cuh"
 
 using namespace bpp;
 
+namespace bpp {
+struct CurveVtbl;
+const CurveVtbl* vtbl_ristretto255();
+const CurveVtbl* vtbl_secp256k1();
+const CurveVtbl* vtbl_bls12_381_g1();
+}  // namespace bpp
+#include "curve_vtbl.cuh"
+
 namespace {
 
-typedef Api<Ed25519, ModEll> ApiRistretto;
-
-const uint8_t ORDER_ELL[32] = {0xed, 0xd3, 0xf5, 0x5c, 0x1a, 0x63, 0x12, 0x58, 0xd6, 0x9c, 0xf7, 0xa2, 0xde, 0xf9, 0xde, 0x14,
-                               0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x00, 0x10};
+const CurveVtbl* vtbl(int curve) {
+  switch (curve) {
+    case BPP_RISTRETTO255: return vtbl_ristretto255();
+    case BPP_SECP256K1: return vtbl_secp256k1();
+    case BPP_BLS12_381_G1: return vtbl_bls12_381_g1();
+    default: return nullptr;
+  }
+}
 
 int point_bytes(int curve) { return curve == 0 ? 32 : curve == 1 ? 64 : curve == 2 ? 96 : -1; }
 bool pow2(size_t x) { return x && !(x & (x - 1)); }
@@ -45,12 +57,13 @@ int drain_hot(bpp_ctx* ctx) {
     if (_rc != BPP_OK) return _rc; \
   } while (0)
 
-// `call` uses ApiT
-#define BPP_DISPATCH(curve, call)                                 \
-  switch (curve) {                                                \
-    case BPP_RISTRETTO255: { typedef ApiRistretto ApiT; const uint8_t* order_le = ORDER_ELL; (void)order_le; return call; } \
-    default: ctx->err = "curve not built into this library"; return BPP_ERR_UNSUPPORTED; \
-  }
+// `call` is a member call on the curve's table
+#define BPP_DISPATCH(curve, call)                                                          \
+  do {                                                                                     \
+    const CurveVtbl* vt_ = vtbl(curve);                                                    \
+    if (!vt_) { ctx->err = "unknown curve id"; return BPP_ERR_UNSUPPORTED; }                 \
+    return vt_->call;                                                                      \
+  } while (0)
 
 extern "C" {
 
@@ -83,7 +96,7 @@ void bpp_destroy(bpp_ctx* ctx) {
 
 const char* bpp_last_error(const bpp_ctx* ctx) { return ctx ? ctx->err.c_str() : "no context"; }
 int bpp_point_bytes(int curve) { return point_bytes(curve); }
-int bpp_raw_point_bytes(int curve) { return curve == 0 ? 128 : -1; }
+int bpp_raw_point_bytes(int curve) { const CurveVtbl* V = vtbl(curve); return V ? V->raw_bytes : -1; }
 size_t bpp_range_proof_len(int curve, size_t n, size_t m) {
   int pb = point_bytes(curve);
   if (pb < 0 || !pow2(n * m) || n * m < 2) return 0;
@@ -104,12 +117,12 @@ int bpp_sync(bpp_ctx* ctx) {
 int bpp_pk_new(bpp_ctx* ctx, int curve, size_t len, bpp_pk** out) {
   BPP_ENTER(ctx);
   if (!out) return BPP_ERR_LENGTH;
-  BPP_DISPATCH(curve, ApiT::pk_new(ctx, len, out));
+  BPP_DISPATCH(curve, pk_new(ctx, len, out));
 }
 int bpp_pk_export(bpp_ctx* ctx, const bpp_pk* pk, uint8_t* g, uint8_t* h, uint8_t* G, uint8_t* H) {
   BPP_ENTER(ctx);
   if (!pk) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pk->curve, ApiT::pk_export(ctx, pk, g, h, G, H));
+  BPP_DISPATCH(pk->curve, pk_export(ctx, pk, g, h, G, H));
 }
 size_t bpp_pk_len(const bpp_pk* pk) { return pk ? pk->len : 0; }
 void bpp_pk_free(bpp_pk* pk) {
@@ -124,20 +137,20 @@ void bpp_pk_free(bpp_pk* pk) {
 int bpp_commit_batch(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out_points) {
   BPP_ENTER(ctx);
   if (!pk) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pk->curve, ApiT::commit_batch(ctx, pk, v, gamma, count, out_points));
+  BPP_DISPATCH(pk->curve, commit_batch(ctx, pk, v, gamma, count, out_points));
 }
 
 int bpp_msm(bpp_ctx* ctx, int curve, const uint8_t* scalars, const uint8_t* points, size_t k, uint8_t* out_point) {
   BPP_ENTER(ctx);
-  BPP_DISPATCH(curve, ApiT::msm(ctx, scalars, points, k, out_point));
+  BPP_DISPATCH(curve, msm(ctx, scalars, points, k, out_point));
 }
 int bpp_points_upload(bpp_ctx* ctx, int curve, const uint8_t* points, size_t k, bpp_points** out) {
   BPP_ENTER(ctx);
-  BPP_DISPATCH(curve, ApiT::points_upload(ctx, points, k, false, out));
+  BPP_DISPATCH(curve, points_upload(ctx, points, k, false, out));
 }
 int bpp_points_from_multipliers(bpp_ctx* ctx, int curve, const uint8_t* mult, size_t k, bpp_points** out) {
   BPP_ENTER(ctx);
-  BPP_DISPATCH(curve, ApiT::points_upload(ctx, mult, k, true, out));
+  BPP_DISPATCH(curve, points_upload(ctx, mult, k, true, out));
 }
 size_t bpp_points_len(const bpp_points* pts) { return pts ? pts->len : 0; }
 void bpp_points_free(bpp_points* pts) {
@@ -148,56 +161,56 @@ void bpp_points_free(bpp_points* pts) {
 int bpp_msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out_points) {
   BPP_ENTER(ctx);
   if (!pts) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pts->curve, ApiT::msm_prepared(ctx, pts, scalars, k, n_jobs, out_points, false));
+  BPP_DISPATCH(pts->curve, msm_prepared(ctx, pts, scalars, k, n_jobs, out_points, false));
 }
 int bpp_msm_prepared_dev(bpp_ctx* ctx, const bpp_points* pts, const void* d_scalars, size_t k, size_t n_jobs, void* d_out_points) {
   BPP_ENTER(ctx);
   if (!pts) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pts->curve, ApiT::msm_prepared_dev(ctx, pts, d_scalars, k, n_jobs, d_out_points));
+  BPP_DISPATCH(pts->curve, msm_prepared_dev(ctx, pts, d_scalars, k, n_jobs, d_out_points));
 }
 int bpp_msm_prepared_raw(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, uint8_t* out_raw) {
   BPP_ENTER(ctx);
   if (!pts) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pts->curve, ApiT::msm_prepared(ctx, pts, scalars, k, 1, out_raw, true));
+  BPP_DISPATCH(pts->curve, msm_prepared(ctx, pts, scalars, k, 1, out_raw, true));
 }
 int bpp_points_sum_raw(bpp_ctx* ctx, int curve, const uint8_t* raw_points, size_t count, uint8_t* out_point) {
   BPP_ENTER(ctx);
-  BPP_DISPATCH(curve, ApiT::points_sum_raw(ctx, raw_points, count, out_point));
+  BPP_DISPATCH(curve, points_sum_raw(ctx, raw_points, count, out_point));
 }
 
 int bpp_msm_prepared_raw_dev(bpp_ctx* ctx, const bpp_points* pts, const void* d_scalars, size_t k, void* d_out_raw) {
   BPP_ENTER(ctx);
   if (!pts) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pts->curve, ApiT::msm_prepared_raw_dev(ctx, pts, d_scalars, k, d_out_raw));
+  BPP_DISPATCH(pts->curve, msm_prepared_raw_dev(ctx, pts, d_scalars, k, d_out_raw));
 }
 int bpp_points_sum_raw_dev(bpp_ctx* ctx, int curve, const void* d_raw_points, size_t count, void* d_out_point) {
   BPP_ENTER(ctx);
-  BPP_DISPATCH(curve, ApiT::points_sum_raw_dev(ctx, d_raw_points, count, d_out_point));
+  BPP_DISPATCH(curve, points_sum_raw_dev(ctx, d_raw_points, count, d_out_point));
 }
 
 int bpp_range_prove_batch(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint64_t* v, const uint8_t* gamma,
                           const bpp_params* params, uint8_t* proofs) {
   BPP_ENTER(ctx);
   if (!pk) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pk->curve, ApiT::range_prove_batch(ctx, pk, n, m, count, v, gamma, params, proofs, order_le));
+  BPP_DISPATCH(pk->curve, range_prove_batch(ctx, pk, n, m, count, v, gamma, params, proofs));
 }
 int bpp_range_verify_batch(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint8_t* V, const uint8_t* proofs,
                            const bpp_params* params, uint8_t* verdicts) {
   BPP_ENTER(ctx);
   if (!pk) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pk->curve, ApiT::range_verify_batch(ctx, pk, n, m, count, V, proofs, params, verdicts, order_le));
+  BPP_DISPATCH(pk->curve, range_verify_batch(ctx, pk, n, m, count, V, proofs, params, verdicts));
 }
 int bpp_range_prove_batch_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_v, const void* d_gamma,
                               const bpp_params* params, void* d_proofs) {
   BPP_ENTER(ctx);
   if (!pk) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pk->curve, ApiT::range_prove_batch_dev(ctx, pk, n, m, count, d_v, d_gamma, params, d_proofs, order_le));
+  BPP_DISPATCH(pk->curve, range_prove_batch_dev(ctx, pk, n, m, count, d_v, d_gamma, params, d_proofs));
 }
 int bpp_range_verify_batch_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V, const void* d_proofs,
                                const bpp_params* params, void* d_verdicts) {
   BPP_ENTER(ctx);
   if (!pk) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pk->curve, ApiT::range_verify_batch_dev(ctx, pk, n, m, count, d_V, d_proofs, params, d_verdicts, order_le));
+  BPP_DISPATCH(pk->curve, range_verify_batch_dev(ctx, pk, n, m, count, d_V, d_proofs, params, d_verdicts));
 }
 int bpp_range_prove(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, const uint64_t* v, const uint8_t* gamma, const bpp_params* params,
                     uint8_t* proof, size_t* proof_len) {
@@ -223,15 +236,15 @@ int bpp_wip_prove(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* a, const uint8_
                   const bpp_params* params, uint8_t* proof, size_t* proof_len) {
   BPP_ENTER(ctx);
   if (!pk || !proof_len) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pk->curve, ApiT::wip_prove(ctx, pk, a, b, power_of_y, gamma, params, proof, proof_len, order_le));
+  BPP_DISPATCH(pk->curve, wip_prove(ctx, pk, a, b, power_of_y, gamma, params, proof, proof_len));
 }
 int bpp_wip_verify(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* power_of_y, const uint8_t* G_exp_of_commitment,
                    const uint8_t* H_exp_of_commitment, const uint8_t* g_exp_of_commitment, size_t n_V, const uint8_t* V_exp_of_commitment,
                    const uint8_t* A_prime, const uint8_t* V, const uint8_t* proof, size_t proof_len, const bpp_params* params) {
   BPP_ENTER(ctx);
   if (!pk) return BPP_ERR_NOT_INIT;
-  BPP_DISPATCH(pk->curve, ApiT::wip_verify(ctx, pk, power_of_y, G_exp_of_commitment, H_exp_of_commitment, g_exp_of_commitment, n_V,
-                                           V_exp_of_commitment, A_prime, V, proof, proof_len, params, order_le));
+  BPP_DISPATCH(pk->curve, wip_verify(ctx, pk, power_of_y, G_exp_of_commitment, H_exp_of_commitment, g_exp_of_commitment, n_V,
+                                           V_exp_of_commitment, A_prime, V, proof, proof_len, params));
 }
 
 int bpp_int_peak_probe(bpp_ctx* ctx, double* wide_imad_per_sec, double* lo_imad_per_sec, double* elapsed_ms) {
@@ -269,25 +282,10 @@ int bpp_int_peak_probe(bpp_ctx* ctx, double* wide_imad_per_sec, double* lo_imad_
   return BPP_OK;
 }
 
-// test surface: element-wise device arithmetic (see debug_ops.cuh). elem = 32 bytes for field/scalar ops, point bytes for group ops.
+// test surface: element-wise device arithmetic (see debug_ops.cuh). elem = field bytes (ops 0-4), point bytes (10-14), 32 (20-23).
 int bpp_debug_op(bpp_ctx* ctx, int curve, int op, size_t n, const uint8_t* a, const uint8_t* b, uint8_t* out, uint8_t* ok) {
   BPP_ENTER(ctx);
-  if (curve != BPP_RISTRETTO255) return BPP_ERR_UNSUPPORTED;
-  const size_t eb = (op >= 10 && op < 20) ? (size_t)point_bytes(curve) : 32;
-  BPP_CK(ctx->buf[B_IN0].ensure(n * eb));
-  BPP_CK(ctx->buf[B_IN1].ensure(n * eb));
-  BPP_CK(ctx->buf[B_OUT0].ensure(n * eb));
-  BPP_CK(ctx->buf[B_DYN_OK].ensure(n));
-  BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN0].p, a, n * eb, cudaMemcpyHostToDevice, ctx->stream));
-  BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, b, n * eb, cudaMemcpyHostToDevice, ctx->stream));
-  debug_op_kernel<Ed25519, ModEll><<<ceil_div(n, 64), 64, 0, ctx->stream>>>(op, (uint32_t)n, ctx->buf[B_IN0].as<uint8_t>(),
-      ctx->buf[B_IN1].as<uint8_t>(), ctx->buf[B_OUT0].as<uint8_t>(), ctx->buf[B_DYN_OK].as<uint8_t>());
-  ctx->launches++;
-  BPP_CK(cudaGetLastError());
-  BPP_CK(cudaMemcpyAsync(out, ctx->buf[B_OUT0].p, n * eb, cudaMemcpyDeviceToHost, ctx->stream));
-  BPP_CK(cudaMemcpyAsync(ok, ctx->buf[B_DYN_OK].p, n, cudaMemcpyDeviceToHost, ctx->stream));
-  BPP_CK(cudaStreamSynchronize(ctx->stream));
-  return BPP_OK;
+  BPP_DISPATCH(curve, debug_op(ctx, op, n, a, b, out, ok));
 }
 
 int bpp_hot_kernel_stats(bpp_ctx* ctx, double* ms, uint64_t* launches, int reset) {

@@ -5,7 +5,7 @@
 
 namespace bpp {
 
-// ops 0..4 (field): a, b are raw 256-bit little-endian values (any value < 2^256); out = canonical result
+// ops 0..4 (field): C::FIELD_BYTES per element; curve 0: raw 256-bit values (any value < 2^256), curves 1, 2: canonical; out canonical
 // ops 10..14 (group): a, b are encoded points; out = encoded result
 // ops 20..23 (scalar field): canonical scalars in, canonical out
 template <class C, class M>
@@ -13,21 +13,8 @@ __global__ void debug_op_kernel(int op, uint32_t n, const uint8_t* __restrict__ 
                                 uint8_t* __restrict__ ok) {
   uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
-  typedef typename C::F F;
   if (op < 10) {
-    F x, y, r;
-    for (int i = 0; i < 8; i++) {
-      x.v[i] = reinterpret_cast<const uint32_t*>(a)[8 * (size_t)t + i];
-      y.v[i] = reinterpret_cast<const uint32_t*>(b)[8 * (size_t)t + i];
-    }
-    switch (op) {
-      case 0: fe_mul(r, x, y); break;
-      case 1: fe_add(r, x, y); break;
-      case 2: fe_sub(r, x, y); break;
-      case 3: fe_invert(r, x); break;
-      default: fe_sqr(r, x); break;
-    }
-    fe_to_bytes(out + 32 * (size_t)t, r);
+    C::dbg_field(op, a + (size_t)t * C::FIELD_BYTES, b + (size_t)t * C::FIELD_BYTES, out + (size_t)t * C::FIELD_BYTES);
     ok[t] = 1;
   } else if (op < 20) {
     typename C::Aff qa, qb;

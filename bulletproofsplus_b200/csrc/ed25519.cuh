@@ -18,6 +18,7 @@ struct Ed25519 {
   struct Ext { F X, Y, Z, T; };
   struct Aff { F ypx, ymx, t2d, nt2d; };
   static constexpr int CURVE_ID = 0;
+  static constexpr int FIELD_BYTES = 32;
   static constexpr int POINT_BYTES = 32;   // boundary encoding
   static constexpr int SCALAR_BITS = 253;  // group order ell < 2^253
   static constexpr int AFF_WORDS = 32;
@@ -195,6 +196,24 @@ struct Ed25519 {
     return ok;
   }
 
+  // test surface (bpp_debug_op ops 0..4): a, b are raw 256-bit little-endian values (any value < 2^256, the loose
+  // representation); out = canonical result
+  __device__ static void dbg_field(int op, const uint8_t* a, const uint8_t* b, uint8_t* out) {
+    F x, y, r;
+    for (int i = 0; i < 8; i++) {
+      x.v[i] = (uint32_t)a[4 * i] | ((uint32_t)a[4 * i + 1] << 8) | ((uint32_t)a[4 * i + 2] << 16) | ((uint32_t)a[4 * i + 3] << 24);
+      y.v[i] = (uint32_t)b[4 * i] | ((uint32_t)b[4 * i + 1] << 8) | ((uint32_t)b[4 * i + 2] << 16) | ((uint32_t)b[4 * i + 3] << 24);
+    }
+    switch (op) {
+      case 0: fe_mul(r, x, y); break;
+      case 1: fe_add(r, x, y); break;
+      case 2: fe_sub(r, x, y); break;
+      case 3: fe_invert(r, x); break;
+      default: fe_sqr(r, x); break;
+    }
+    fe_to_bytes(out, r);
+  }
+
   // Ext -> 32 bytes (RFC 9496 §4.3.2)
   __device__ static void encode(uint8_t* b, const Ext& p) {
     F u1, u2, t, invsqrt, den1, den2, z_inv, ix0, iy0, ench, x, y, den_inv, s, one;
@@ -218,24 +237,5 @@ struct Ed25519 {
     fe_to_bytes(b, s);
   }
 };
-
-// 128-bit vectorised global loads/stores of whole points (AoS, 32-byte aligned)
-template <int WORDS, class T>
-BPP_DEV void load_words(T& dst, const void* src) {
-  const uint4* s = reinterpret_cast<const uint4*>(src);
-  uint32_t* d = reinterpret_cast<uint32_t*>(&dst);
-#pragma unroll
-  for (int i = 0; i < WORDS / 4; i++) {
-    uint4 q = __ldg(s + i);
-    d[4 * i] = q.x; d[4 * i + 1] = q.y; d[4 * i + 2] = q.z; d[4 * i + 3] = q.w;
-  }
-}
-template <int WORDS, class T>
-BPP_DEV void store_words(void* dst, const T& src) {
-  uint4* d = reinterpret_cast<uint4*>(dst);
-  const uint32_t* s = reinterpret_cast<const uint32_t*>(&src);
-#pragma unroll
-  for (int i = 0; i < WORDS / 4; i++) d[i] = make_uint4(s[4 * i], s[4 * i + 1], s[4 * i + 2], s[4 * i + 3]);
-}
 
 }  // namespace bpp

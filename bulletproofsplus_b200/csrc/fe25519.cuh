@@ -248,4 +248,23 @@ BPP_DEV void fe_to_bytes(uint8_t* b, const Fe25519& a) {
   }
 }
 
+// 128-bit vectorised global loads/stores of whole points (AoS, 32-byte aligned)
+template <int WORDS, class T>
+BPP_DEV void load_words(T& dst, const void* src) {
+  const uint4* s = reinterpret_cast<const uint4*>(src);
+  uint32_t* d = reinterpret_cast<uint32_t*>(&dst);
+#pragma unroll
+  for (int i = 0; i < WORDS / 4; i++) {
+    uint4 q = __ldg(s + i);
+    d[4 * i] = q.x; d[4 * i + 1] = q.y; d[4 * i + 2] = q.z; d[4 * i + 3] = q.w;
+  }
+}
+template <int WORDS, class T>
+BPP_DEV void store_words(void* dst, const T& src) {
+  uint4* d = reinterpret_cast<uint4*>(dst);
+  const uint32_t* s = reinterpret_cast<const uint32_t*>(&src);
+#pragma unroll
+  for (int i = 0; i < WORDS / 4; i++) d[i] = make_uint4(s[4 * i], s[4 * i + 1], s[4 * i + 2], s[4 * i + 3]);
+}
+
 }  // namespace bpp

@@ -234,7 +234,7 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* t
   return base + x - v;
 }
 
-__global__ void scan_tile_sums(const uint32_t* __restrict__ in, uint32_t n, uint32_t* __restrict__ tile_sums) {
+static __global__ void scan_tile_sums(const uint32_t* __restrict__ in, uint32_t n, uint32_t* __restrict__ tile_sums) {
   uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
   uint32_t s = 0;
 #pragma unroll
@@ -243,7 +243,7 @@ __global__ void scan_tile_sums(const uint32_t* __restrict__ in, uint32_t n, uint
   block_exclusive_scan(s, &tot);
   if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
 }
-__global__ void scan_tile_offsets(uint32_t* tile_sums, uint32_t n_tiles) {  // single block, in place -> exclusive
+static __global__ void scan_tile_offsets(uint32_t* tile_sums, uint32_t n_tiles) {  // single block, in place -> exclusive
   __shared__ uint32_t carry;
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
@@ -257,7 +257,7 @@ __global__ void scan_tile_offsets(uint32_t* tile_sums, uint32_t n_tiles) {  // s
     __syncthreads();
   }
 }
-__global__ void scan_apply(const uint32_t* __restrict__ in, uint32_t n, const uint32_t* __restrict__ tile_offsets,
+static __global__ void scan_apply(const uint32_t* __restrict__ in, uint32_t n, const uint32_t* __restrict__ tile_offsets,
                            uint32_t* __restrict__ out, uint32_t* __restrict__ out2) {
   uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
   uint32_t v[SCAN_ITEMS], s = 0;
@@ -280,7 +280,7 @@ constexpr int SS_ITEMS = 16;
 constexpr int SS_TILE = SS_THREADS * SS_ITEMS;
 __device__ __forceinline__ uint32_t ss_bin(uint32_t count) { return 255u - (count < 255u ? count : 255u); }
 
-__global__ void __launch_bounds__(SS_THREADS) sizesort_hist_kernel(const uint32_t* __restrict__ counts, uint32_t n, uint32_t* __restrict__ bins) {
+static __global__ void __launch_bounds__(SS_THREADS) sizesort_hist_kernel(const uint32_t* __restrict__ counts, uint32_t n, uint32_t* __restrict__ bins) {
   __shared__ uint32_t h[256];
   h[threadIdx.x] = 0;
   __syncthreads();
@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(SS_THREADS) sizesort_hist_kernel(const uint32_
   if (h[threadIdx.x]) atomicAdd(&bins[threadIdx.x], h[threadIdx.x]);
 }
 // one block: bin totals -> exclusive starts; tiers[0..2] = first perm index of the buckets with count <= 254 / <= ACC_CAP
-__global__ void __launch_bounds__(256) sizesort_bins_scan_kernel(uint32_t* __restrict__ bins, uint32_t* __restrict__ tiers, uint32_t acc_cap) {
+static __global__ void __launch_bounds__(256) sizesort_bins_scan_kernel(uint32_t* __restrict__ bins, uint32_t* __restrict__ tiers, uint32_t acc_cap) {
   uint32_t tot;
   uint32_t ex = block_exclusive_scan(bins[threadIdx.x], &tot);
   bins[threadIdx.x] = ex;
@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(256) sizesort_bins_scan_kernel(uint32_t* __res
   if (threadIdx.x == 1) tiers[1] = ex;
   if (threadIdx.x == 255 - acc_cap) tiers[2] = ex;
 }
-__global__ void __launch_bounds__(SS_THREADS) sizesort_scatter_kernel(const uint32_t* __restrict__ counts, uint32_t n, uint32_t* __restrict__ bins,
+static __global__ void __launch_bounds__(SS_THREADS) sizesort_scatter_kernel(const uint32_t* __restrict__ counts, uint32_t n, uint32_t* __restrict__ bins,
                                                                       uint32_t* __restrict__ perm) {
   __shared__ uint32_t h[256], start[256];
   h[threadIdx.x] = 0;

@@ -81,11 +81,11 @@ __global__ void scalars_check_kernel(uint32_t n, const uint32_t* __restrict__ s,
   uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < n && !Sc<M>::canonical_ok(s + 8 * (size_t)t)) bad[0] = 1;
 }
-__global__ void iota_kernel(uint32_t n, uint32_t period, uint32_t* __restrict__ out) {
+static __global__ void iota_kernel(uint32_t n, uint32_t period, uint32_t* __restrict__ out) {
   uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < n) out[t] = period ? t % period : t;
 }
-__global__ void any_zero_kernel(uint32_t n, const uint8_t* __restrict__ ok, uint8_t* __restrict__ bad) {
+static __global__ void any_zero_kernel(uint32_t n, const uint8_t* __restrict__ ok, uint8_t* __restrict__ bad) {
   uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < n && !ok[t]) bad[0] = 1;
 }
@@ -139,7 +139,7 @@ __global__ void encode_into_proofs_kernel(uint32_t n_proofs, uint32_t jobs_per_p
 }
 
 // gather the point bytes of every proof (first pts_per_proof points of each) into one contiguous array
-__global__ void gather_proof_points_kernel(uint32_t n_proofs, uint32_t bytes_per_proof, const uint8_t* __restrict__ proofs,
+static __global__ void gather_proof_points_kernel(uint32_t n_proofs, uint32_t bytes_per_proof, const uint8_t* __restrict__ proofs,
                                            size_t proof_stride, uint8_t* __restrict__ out) {
   size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= (size_t)n_proofs * bytes_per_proof) return;

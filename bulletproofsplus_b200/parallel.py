@@ -8,8 +8,8 @@ Only the two decompositions SURVEY §8(e) says shard naturally are here:
   its slice to ONE uncompressed partial point, all-gather of world x raw bytes, local sum + encode. Point addition is
   not a reduction operator NCCL knows, hence all-gather + a local sum and never all_reduce.
 
-The compute callables are injected, so the same code runs against libbpp_b200.so on the GPUs and against the CPU
-oracle in the world_size-2 gloo tests (tests/test_parallel_gloo.py). A single proof's WIP rounds do not shard
+The compute callables are injected, so the same code runs against libbpp_b200.so on the GPUs and against a CPU
+checker in the world_size-2 gloo tests (tests/test_parallel_gloo.py). A single proof's WIP rounds do not shard
 ("replicas only").
 """
 from __future__ import annotations
