@@ -36,7 +36,7 @@ FIELD_MUL_IMAD = 72           # 8x8 schoolbook + 8-limb fold
 MIXED, FULL, DOUBLE = 7, 8, 8  # field multiplies per point operation
 
 
-def algorithmic_field_muls(n_terms: int, bits: int = 253):
+def algorithmic_field_muls(n_terms: int, bits: int = 253, MIXED: int = MIXED, FULL: int = FULL, DOUBLE: int = DOUBLE):
     """W(N) of SURVEY §8(d); returns (W, c*, accumulate-only share)."""
     best = None
     for c in range(1, 25):
@@ -246,7 +246,7 @@ def main():
 
     # ---- integer-pipe peak (live) ----
     probe = ctx.int_peak_probe()
-    int_peak = probe["wide_imad_per_s"]
+    int_peak = probe["imad32_per_s"]  # issue peak of the integer multiply pipe (64 lanes/clk/SM on sm_100a)
 
     # ---- device-resident timing ----
     for i in range(args.warmup):
@@ -314,7 +314,12 @@ def main():
         "bound": "int32-imad (no tensor/HBM bound applies: ~20k multiply-adds per 128 B term)", "kernel": "msm_accumulate_kernel<Ed25519> (+ its two long-bucket variants msm_accumulate_group_kernel<.,32|4>, timed together)",
         "achieved": ach_kernel / 1e12 if ach_kernel else None, "peak": int_peak / 1e12, "unit": "T 32x32+64 multiply-adds/s",
         "frac": (ach_kernel / int_peak) if ach_kernel else None, "traffic": None,
-        "peak_source": "bpp_int_peak_probe, IMAD.WIDE.U32 chains on all SMs, measured in this run",
+        "peak_source": "bpp_int_peak_probe: 32-bit IMAD chains with loop-produced operands on all SMs, measured in this run — the "
+                       "issue peak of the integer multiply pipe, which every form of 32x32 multiply shares",
+        "pipe_ceiling": {"wide_chain_T_per_s": probe["wide_chain_per_s"] / 1e12, "wide_fused_T_per_s": probe["wide_fused_per_s"] / 1e12,
+                         "note": "same probe, the two 32x32+64 forms a limb product can use: carry-chained IMAD.WIDE.U32.X (what "
+                                 "mul_wide_n emits) and IMAD.WIDE.U32 with a 64-bit register addend; both issue at well under half "
+                                 "the IMAD peak on sm_100a, so ~0.43 of `peak` is the ceiling of any multi-limb multiply (DESIGN.md §3.1)"},
         "executed": {"achieved": exec_kernel / 1e12 if exec_kernel else None, "frac": (exec_kernel / int_peak) if exec_kernel else None,
                      "note": "multiply-adds the kernel really issues (upper bound: zero digits skipped): the window tables of the public key "
                              "beat the algorithmic count, so `frac` above overstates pipe utilisation by algorithmic/executed"},
@@ -323,7 +328,6 @@ def main():
         "whole_step": {"achieved": ach_whole / 1e12, "frac": ach_whole / int_peak, "algorithmic": "B*W(2089)*72 (SURVEY §8(d))"},
         "hbm": {"achieved_gbs": alg_bytes / (elapsed_ms / K_steps * 1e-3) / 1e9, "peak_gbs": hbm_peak,
                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback", "note": "secondary: shows the path is not memory-bound"},
-        "lo_imad_peak": probe["lo_imad_per_s"] / 1e12,
     }
 
     extras = {}
@@ -433,36 +437,42 @@ def run_extras(args, torch, api, _lib, ctx, pk, dev, stream, int_peak):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
     out["proves_per_sec_n64_m16"] = {"value": PB / (ms * 1e-3), "unit": "proofs/s", "batch": PB, "ms_per_batch": ms}
-    # MSM sweep
-    sweep = []
-    max_log = args.msm_max_log
-    n_max = 1 << max_log
-    mult = torch.randint(0, 256, (n_max, 32), dtype=torch.uint8)
-    mult[:, 31] &= 0x0F  # < 2^252 < ell
-    pts = api.Points.from_multipliers(bytes(mult.numpy().tobytes()), _lib.RISTRETTO255, ctx)
-    sc = torch.randint(0, 256, (n_max, 32), dtype=torch.uint8)
-    sc[:, 31] &= 0x0F
-    d_sc = sc.to(dev)
-    d_out = torch.empty(32, dtype=torch.uint8, device=dev)
-    for lg in range(10, max_log + 1, 2):
-        n = 1 << lg
+    # MSM sweep, all three curves (field multiply = 72 IMAD for 2^255-19 and the secp256k1 prime, 300 for
+    # BLS12-381; Edwards mixed/full/double = 7/8/8, short Weierstrass 11/16/7 field multiplies)
+    curves = (("", _lib.RISTRETTO255, args.msm_max_log, 253, 72, (7, 8, 8)),
+              ("_secp256k1", _lib.SECP256K1, min(args.msm_max_log, 20), 256, 72, (11, 16, 7)),
+              ("_bls12_381_g1", _lib.BLS12_381_G1, min(args.msm_max_log, 20), 255, 300, (11, 16, 7)))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for suffix, curve, max_log, bits, imad, costs in curves:
+        sweep = []
+        n_max = 1 << max_log
+        mult = torch.randint(0, 256, (n_max, 32), dtype=torch.uint8)
+        mult[:, 31] &= 0x0F  # < 2^252 < every group order
+        pts = api.Points.from_multipliers(bytes(mult.numpy().tobytes()), curve, ctx)
+        sc = torch.randint(0, 256, (n_max, 32), dtype=torch.uint8)
+        sc[:, 31] &= 0x0F
+        d_sc = sc.to(dev)
+        d_out = torch.empty(lib.bpp_point_bytes(curve), dtype=torch.uint8, device=dev)
+        for lg in range(10, max_log + 1, 2):
+            n = 1 << lg
 
-        def msm():
-            ctx.check(lib.bpp_msm_prepared_dev(ctx.h, pts.h, d_sc.data_ptr(), n, 1, d_out.data_ptr()), "msm")
+            def msm():
+                ctx.check(lib.bpp_msm_prepared_dev(ctx.h, pts.h, d_sc.data_ptr(), n, 1, d_out.data_ptr()), "msm")
 
-        for _ in range(2):
-            msm()
-        torch.cuda.synchronize()
-        reps = 5
-        e0.record(stream)
-        for _ in range(reps):
-            msm()
-        e1.record(stream)
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / reps
-        W, c_star, _ = algorithmic_field_muls(n)
-        sweep.append({"log2_n": lg, "ms": ms, "points_per_sec": n / (ms * 1e-3), "int_roofline_frac": W * FIELD_MUL_IMAD / (ms * 1e-3) / int_peak})
-    out["msm_points_per_sec"] = sweep
+            for _ in range(3):
+                msm()
+            torch.cuda.synchronize()
+            reps = 5
+            e0.record(stream)
+            for _ in range(reps):
+                msm()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / reps
+            W, c_star, _ = algorithmic_field_muls(n, bits, *costs)
+            sweep.append({"log2_n": lg, "ms": ms, "points_per_sec": n / (ms * 1e-3), "int_roofline_frac": W * imad / (ms * 1e-3) / int_peak})
+        out["msm_points_per_sec" + suffix] = sweep
+        del pts
     return out
 
 

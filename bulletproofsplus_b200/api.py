@@ -90,9 +90,9 @@ class Context:
         self.check(self.lib.bpp_sync(self.h), "sync")
 
     def int_peak_probe(self):
-        a, b, c = C.c_double(), C.c_double(), C.c_double()
-        self.check(self.lib.bpp_int_peak_probe(self.h, C.byref(a), C.byref(b), C.byref(c)), "int_peak_probe")
-        return dict(wide_imad_per_s=a.value, lo_imad_per_s=b.value, elapsed_ms=c.value)
+        rates, ms = (C.c_double * 3)(), C.c_double()
+        self.check(self.lib.bpp_int_peak_probe(self.h, rates, C.byref(ms)), "int_peak_probe")
+        return dict(imad32_per_s=rates[0], wide_chain_per_s=rates[1], wide_fused_per_s=rates[2], elapsed_ms=ms.value)
 
     def hot_kernel_stats(self, reset=False):
         ms, n = C.c_double(), C.c_uint64()

@@ -65,6 +65,24 @@ int drain_hot(bpp_ctx* ctx) {
     return vt_->call;                                                                      \
   } while (0)
 
+// Field-multiply throughput probe: ILP independent dependent-chains of fe_mul per thread, no memory traffic. Tells how much
+// of the IMAD.WIDE peak the 72-IMAD carry-chain multiply can reach by itself at a given occupancy.
+template <int ILP>
+__global__ void fe_mul_probe_kernel(uint32_t iters, uint32_t seed, uint32_t* __restrict__ sink) {
+  Fe25519 x[ILP], y;
+  for (int k = 0; k < ILP; k++)
+    for (int i = 0; i < 8; i++) x[k].v[i] = seed * (k + 3) + threadIdx.x * 2654435761u + i * 40503u;
+  for (int i = 0; i < 8; i++) y.v[i] = (seed + threadIdx.x) ^ (0x9e3779b9u * (i + 1));
+  for (uint32_t it = 0; it < iters; it++) {
+#pragma unroll
+    for (int k = 0; k < ILP; k++) fe_mul(x[k], x[k], y);
+  }
+  uint32_t acc = 0;
+  for (int k = 0; k < ILP; k++)
+    for (int i = 0; i < 8; i++) acc ^= x[k].v[i];
+  if (acc == 0x12345u) sink[0] = acc;
+}
+
 extern "C" {
 
 int bpp_init(int device, void* cuda_stream, bpp_ctx** out) {
@@ -247,7 +265,7 @@ int bpp_wip_verify(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* power_of_y, co
                                            V_exp_of_commitment, A_prime, V, proof, proof_len, params));
 }
 
-int bpp_int_peak_probe(bpp_ctx* ctx, double* wide_imad_per_sec, double* lo_imad_per_sec, double* elapsed_ms) {
+int bpp_int_peak_probe(bpp_ctx* ctx, double* rates3, double* elapsed_ms) {
   BPP_ENTER(ctx);
   cudaDeviceProp prop;
   BPP_CK(cudaGetDeviceProperties(&prop, ctx->device));
@@ -257,13 +275,15 @@ int bpp_int_peak_probe(bpp_ctx* ctx, double* wide_imad_per_sec, double* lo_imad_
   cudaEvent_t e0, e1;
   BPP_CK(cudaEventCreate(&e0));
   BPP_CK(cudaEventCreate(&e1));
-  double rate[2] = {0, 0}, total_ms = 0;
-  for (int mode = 0; mode < 2; mode++) {
+  double total_ms = 0;
+  for (int mode = 0; mode < 3; mode++) {
     float best = 1e30f;
     for (int rep = 0; rep < 5; rep++) {  // first repetition is the warm-up
+      uint64_t* sink = ctx->buf[B_OUT0].as<uint64_t>();
       BPP_CK(cudaEventRecord(e0, ctx->stream));
-      if (mode == 0) int_peak_kernel<0><<<blocks, threads, 0, ctx->stream>>>(iters, 12345u + rep, ctx->buf[B_OUT0].as<uint64_t>());
-      else int_peak_kernel<1><<<blocks, threads, 0, ctx->stream>>>(iters, 12345u + rep, ctx->buf[B_OUT0].as<uint64_t>());
+      if (mode == 0) int_peak_kernel<0><<<blocks, threads, 0, ctx->stream>>>(iters, 12345u + rep, sink);
+      else if (mode == 1) int_peak_kernel<1><<<blocks, threads, 0, ctx->stream>>>(iters, 12345u + rep, sink);
+      else int_peak_kernel<2><<<blocks, threads, 0, ctx->stream>>>(iters, 12345u + rep, sink);
       ctx->launches++;
       BPP_CK(cudaEventRecord(e1, ctx->stream));
       BPP_CK(cudaEventSynchronize(e1));
@@ -272,13 +292,45 @@ int bpp_int_peak_probe(bpp_ctx* ctx, double* wide_imad_per_sec, double* lo_imad_
       total_ms += ms;
       if (rep > 0 && ms < best) best = ms;
     }
-    rate[mode] = (double)blocks * threads * iters * 32.0 / (best * 1e-3);
+    if (rates3) rates3[mode] = (double)blocks * threads * iters * 32.0 / (best * 1e-3);
   }
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
-  if (wide_imad_per_sec) *wide_imad_per_sec = rate[0];
-  if (lo_imad_per_sec) *lo_imad_per_sec = rate[1];
   if (elapsed_ms) *elapsed_ms = total_ms;
+  return BPP_OK;
+}
+
+int bpp_fe_mul_probe(bpp_ctx* ctx, int ilp, int threads_per_block, int blocks_per_sm, double* muls_per_sec) {
+  BPP_ENTER(ctx);
+  cudaDeviceProp prop;
+  BPP_CK(cudaGetDeviceProperties(&prop, ctx->device));
+  const int blocks = prop.multiProcessorCount * blocks_per_sm;
+  const uint32_t iters = 2048;
+  BPP_CK(ctx->buf[B_OUT0].ensure(64));
+  cudaEvent_t e0, e1;
+  BPP_CK(cudaEventCreate(&e0));
+  BPP_CK(cudaEventCreate(&e1));
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; rep++) {
+    BPP_CK(cudaEventRecord(e0, ctx->stream));
+    uint32_t* sink = ctx->buf[B_OUT0].as<uint32_t>();
+    switch (ilp) {
+      case 1: fe_mul_probe_kernel<1><<<blocks, threads_per_block, 0, ctx->stream>>>(iters, 77u + rep, sink); break;
+      case 2: fe_mul_probe_kernel<2><<<blocks, threads_per_block, 0, ctx->stream>>>(iters, 77u + rep, sink); break;
+      case 3: fe_mul_probe_kernel<3><<<blocks, threads_per_block, 0, ctx->stream>>>(iters, 77u + rep, sink); break;
+      default: ilp = 4; fe_mul_probe_kernel<4><<<blocks, threads_per_block, 0, ctx->stream>>>(iters, 77u + rep, sink); break;
+    }
+    ctx->launches++;
+    BPP_CK(cudaGetLastError());
+    BPP_CK(cudaEventRecord(e1, ctx->stream));
+    BPP_CK(cudaEventSynchronize(e1));
+    float ms = 0;
+    BPP_CK(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep > 0 && ms < best) best = ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (muls_per_sec) *muls_per_sec = (double)blocks * threads_per_block * iters * ilp / (best * 1e-3);
   return BPP_OK;
 }
 

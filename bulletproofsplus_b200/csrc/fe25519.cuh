@@ -8,50 +8,13 @@
 // call sites listed in SURVEY.md §8(b)).
 #pragma once
 #include <cstdint>
+#include "common.cuh"
 
 namespace bpp {
 
 struct Fe25519 {
   uint32_t v[8];
 };
-
-#define BPP_DEV __device__ __forceinline__
-
-// ---- 8x8 -> 16 limb product ------------------------------------------------------------
-BPP_DEV void fe25519_mul_wide(uint32_t* r, const uint32_t* a, const uint32_t* b) {
-  uint32_t E[16], O[16];
-#pragma unroll
-  for (int i = 0; i < 16; i++) { E[i] = 0; O[i] = 0; }
-#pragma unroll
-  for (int i = 0; i < 8; i++) {
-    const int je = i & 1, jo = 1 - je;
-    {  // products with i+j even, 64-bit aligned on even columns
-      const int c = i + je;
-      asm volatile("mad.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;"
-                   : "+r"(E[c]), "+r"(E[c + 1]) : "r"(a[je]), "r"(b[i]));
-#pragma unroll
-      for (int j = je + 2; j < 8; j += 2)
-        asm volatile("madc.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;"
-                     : "+r"(E[i + j]), "+r"(E[i + j + 1]) : "r"(a[j]), "r"(b[i]));
-      if (c + 8 < 16) asm volatile("addc.u32 %0, %0, 0;" : "+r"(E[c + 8]));
-    }
-    {  // products with i+j odd, kept one column down in O
-      const int c = i + jo - 1;
-      asm volatile("mad.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;"
-                   : "+r"(O[c]), "+r"(O[c + 1]) : "r"(a[jo]), "r"(b[i]));
-#pragma unroll
-      for (int j = jo + 2; j < 8; j += 2)
-        asm volatile("madc.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;"
-                     : "+r"(O[i + j - 1]), "+r"(O[i + j]) : "r"(a[j]), "r"(b[i]));
-      if (c + 8 < 16) asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[c + 8]));
-    }
-  }
-  r[0] = E[0];
-  asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(r[1]) : "r"(E[1]), "r"(O[0]));
-#pragma unroll
-  for (int i = 2; i < 15; i++) asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[i]) : "r"(E[i]), "r"(O[i - 1]));
-  asm volatile("addc.u32 %0, %1, %2;" : "=r"(r[15]) : "r"(E[15]), "r"(O[14]));
-}
 
 // ---- fold a 16-limb value to 8 loose limbs: lo + 38*hi ----------------------------------
 BPP_DEV void fe25519_reduce_wide(Fe25519& out, const uint32_t* t) {
@@ -86,7 +49,7 @@ BPP_DEV void fe25519_reduce_wide(Fe25519& out, const uint32_t* t) {
 
 BPP_DEV void fe_mul(Fe25519& r, const Fe25519& a, const Fe25519& b) {
   uint32_t t[16];
-  fe25519_mul_wide(t, a.v, b.v);
+  mul_wide_n<8>(t, a.v, b.v);
   fe25519_reduce_wide(r, t);
 }
 BPP_DEV void fe_sqr(Fe25519& r, const Fe25519& a) { fe_mul(r, a, a); }
@@ -248,23 +211,5 @@ BPP_DEV void fe_to_bytes(uint8_t* b, const Fe25519& a) {
   }
 }
 
-// 128-bit vectorised global loads/stores of whole points (AoS, 32-byte aligned)
-template <int WORDS, class T>
-BPP_DEV void load_words(T& dst, const void* src) {
-  const uint4* s = reinterpret_cast<const uint4*>(src);
-  uint32_t* d = reinterpret_cast<uint32_t*>(&dst);
-#pragma unroll
-  for (int i = 0; i < WORDS / 4; i++) {
-    uint4 q = __ldg(s + i);
-    d[4 * i] = q.x; d[4 * i + 1] = q.y; d[4 * i + 2] = q.z; d[4 * i + 3] = q.w;
-  }
-}
-template <int WORDS, class T>
-BPP_DEV void store_words(void* dst, const T& src) {
-  uint4* d = reinterpret_cast<uint4*>(dst);
-  const uint32_t* s = reinterpret_cast<const uint32_t*>(&src);
-#pragma unroll
-  for (int i = 0; i < WORDS / 4; i++) d[i] = make_uint4(s[4 * i], s[4 * i + 1], s[4 * i + 2], s[4 * i + 3]);
-}
 
 }  // namespace bpp

@@ -6,46 +6,9 @@
 // per 32x32 product); the Montgomery reduction is row-pipelined 64-bit C. No tensor cores: carry chains.
 #pragma once
 #include <cstdint>
-#include "fe25519.cuh"  // BPP_DEV
+#include "common.cuh"
 
 namespace bpp {
-
-// r[0..2NL) = a * b
-template <int NL>
-BPP_DEV void mul_wide_n(uint32_t* r, const uint32_t* a, const uint32_t* b) {
-  uint32_t E[2 * NL], O[2 * NL];
-#pragma unroll
-  for (int i = 0; i < 2 * NL; i++) { E[i] = 0; O[i] = 0; }
-#pragma unroll
-  for (int i = 0; i < NL; i++) {
-    const int je = i & 1, jo = 1 - je;
-    {  // products with i+j even, 64-bit aligned on even columns
-      const int c = i + je;
-      asm volatile("mad.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;"
-                   : "+r"(E[c]), "+r"(E[c + 1]) : "r"(a[je]), "r"(b[i]));
-#pragma unroll
-      for (int j = je + 2; j < NL; j += 2)
-        asm volatile("madc.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;"
-                     : "+r"(E[i + j]), "+r"(E[i + j + 1]) : "r"(a[j]), "r"(b[i]));
-      if (c + NL < 2 * NL) asm volatile("addc.u32 %0, %0, 0;" : "+r"(E[c + NL]));
-    }
-    {  // products with i+j odd, kept one column down in O
-      const int c = i + jo - 1;
-      asm volatile("mad.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;"
-                   : "+r"(O[c]), "+r"(O[c + 1]) : "r"(a[jo]), "r"(b[i]));
-#pragma unroll
-      for (int j = jo + 2; j < NL; j += 2)
-        asm volatile("madc.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;"
-                     : "+r"(O[i + j - 1]), "+r"(O[i + j]) : "r"(a[j]), "r"(b[i]));
-      if (c + NL < 2 * NL) asm volatile("addc.u32 %0, %0, 0;" : "+r"(O[c + NL]));
-    }
-  }
-  r[0] = E[0];
-  asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(r[1]) : "r"(E[1]), "r"(O[0]));
-#pragma unroll
-  for (int i = 2; i < 2 * NL - 1; i++) asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[i]) : "r"(E[i]), "r"(O[i - 1]));
-  asm volatile("addc.u32 %0, %1, %2;" : "=r"(r[2 * NL - 1]) : "r"(E[2 * NL - 1]), "r"(O[2 * NL - 2]));
-}
 
 // P supplies: NL, mod(i), r1(i) (= 2^(32 NL) mod p), r2(i) (= 2^(64 NL) mod p), NINV (= -p^-1 mod 2^32)
 template <class P>

@@ -189,27 +189,38 @@ __global__ void comb_build_kernel(uint32_t CW, const uint32_t* __restrict__ aff2
 }
 
 // ---- integer-pipe roofline probe: ILP-8 independent chains per thread, no memory traffic -------------
-// MODE 0: mad.wide.u32 (IMAD.WIDE.U32, one 32x32+64 multiply-add); MODE 1: mad.lo.u32 (IMAD)
+// Every multiplicand is a value the loop itself produces, so ptxas can neither hoist the product nor turn the chain into
+// additions (it does both when the operands are loop-invariant: a first version of this probe measured 64-bit adds).
+// MODE 0: 32-bit multiply-add (IMAD)                        — the issue-rate peak of the integer multiply pipe
+// MODE 1: carry-chained 32x32+64 multiply-add (IMAD.WIDE.U32.X rows of 4, as in mul_wide_n) — what a limb product can reach
+// MODE 2: 32x32+64 multiply-add with a plain 64-bit register addend (IMAD.WIDE.U32 Rd, Ra, Rb, Rc)
 template <int MODE>
 __global__ void __launch_bounds__(256) int_peak_kernel(uint32_t iters, uint32_t seed, uint64_t* __restrict__ sink) {
   uint32_t a = seed + threadIdx.x * 2654435761u + 1u, b = a ^ 0x9e3779b9u;
   uint64_t acc[8];
-  uint32_t lo[8];
+  uint32_t lo[8], hi[8];
 #pragma unroll
-  for (int i = 0; i < 8; i++) { acc[i] = a + i; lo[i] = b + i; }
+  for (int i = 0; i < 8; i++) { acc[i] = a + i; lo[i] = b + i; hi[i] = a * (i + 3); }
   for (uint32_t it = 0; it < iters; it++) {
 #pragma unroll
     for (int u = 0; u < 4; u++) {
 #pragma unroll
       for (int i = 0; i < 8; i++) {
-        if (MODE == 0) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(a), "r"(b));
-        else asm volatile("mad.lo.u32 %0, %1, %2, %0;" : "+r"(lo[i]) : "r"(a), "r"(b));
+        if (MODE == 0) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(lo[i]) : "r"(a), "r"(b));
+        if (MODE == 1) {
+          if ((i & 3) == 0)
+            asm volatile("mad.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;" : "+r"(lo[i]), "+r"(hi[i]) : "r"(lo[(i + 1) & 7]), "r"(b));
+          else
+            asm volatile("madc.lo.cc.u32 %0, %2, %3, %0; madc.hi.cc.u32 %1, %2, %3, %1;" : "+r"(lo[i]), "+r"(hi[i]) : "r"(lo[(i + 1) & 7]), "r"(b));
+          if ((i & 3) == 3) asm volatile("addc.u32 %0, %0, 0;" : "+r"(hi[(i + 1) & 7]));
+        }
+        if (MODE == 2) acc[i] += (uint64_t)(uint32_t)acc[i] * b;
       }
     }
   }
   uint64_t s = 0;
 #pragma unroll
-  for (int i = 0; i < 8; i++) s += acc[i] + lo[i];
+  for (int i = 0; i < 8; i++) s += acc[i] + lo[i] + hi[i];
   if (s == 0x1234567ull) sink[0] = s;  // never true in practice; keeps the chains alive
 }
 

@@ -6,7 +6,7 @@
 // IMAD.WIDE carry-chain schoolbook, the Montgomery reduction is 64-bit C that nvcc lowers to IMAD.WIDE.U32.
 #pragma once
 #include <cstdint>
-#include "fe25519.cuh"  // BPP_DEV
+#include "common.cuh"
 
 namespace bpp {
 
@@ -108,7 +108,7 @@ struct Sc {
   // Montgomery product: 8x8 schoolbook (IMAD.WIDE carry chains, shared with the base field) + reduction
   BPP_DEV friend Sc operator*(const Sc& a, const Sc& b) {
     uint32_t t[16];
-    fe25519_mul_wide(t, a.v, b.v);
+    mul_wide_n<8>(t, a.v, b.v);
     return mont_reduce(t);
   }
   BPP_DEV Sc sqr() const { return *this * *this; }

@@ -129,8 +129,14 @@ int bpp_wip_verify(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* power_of_y, co
                    size_t proof_len, const bpp_params* params);
 
 /* ---- measurement support --------------------------------------------------------------------------- */
-/* Integer-pipe microbenchmark: independent IMAD.WIDE.U32 chains on every SM; returns 32x32+64 multiply-adds/s. */
-int bpp_int_peak_probe(bpp_ctx* ctx, double* wide_imad_per_sec, double* lo_imad_per_sec, double* elapsed_ms);
+/* Integer-pipe microbenchmark, register-only chains on every SM with loop-produced multiplicands. rates3[0] = 32-bit
+ * multiply-adds/s (IMAD: the issue peak of the integer multiply pipe), rates3[1] = carry-chained 32x32+64 multiply-adds/s
+ * (IMAD.WIDE.U32.X, the form a multi-limb product is made of), rates3[2] = 32x32+64 multiply-adds/s with a plain 64-bit
+ * register addend (IMAD.WIDE.U32). */
+int bpp_int_peak_probe(bpp_ctx* ctx, double* rates3, double* elapsed_ms);
+/* Field-multiply probe: `ilp` independent chains of GF(2^255-19) multiplications per thread on blocks_per_sm x threads_per_block
+ * threads per SM, no memory traffic: field multiplications/s (x 72 = multiply-adds/s the carry-chain multiply reaches alone). */
+int bpp_fe_mul_probe(bpp_ctx* ctx, int ilp, int threads_per_block, int blocks_per_sm, double* muls_per_sec);
 /* device time (ms, CUDA events on the context's stream) spent in the bucket-accumulation kernel, and its launch
  * count, since the last reset */
 int bpp_hot_kernel_stats(bpp_ctx* ctx, double* ms, uint64_t* launches, int reset);
