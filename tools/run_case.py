@@ -1,11 +1,12 @@
 """One workload of the hot path, timed with the wall clock around a stream sync (development aid; bench.py is the
-measurement of record).  usage: run_case.py verify|prove|msm|commit SIZE [reps]"""
+measurement of record).  usage: run_case.py verify|prove|msm|commit SIZE [reps] [curve]"""
 import ctypes as C, os, sys, time, random
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from bulletproofsplus_b200 import api, _lib
 
 case, size = sys.argv[1], int(sys.argv[2])
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
+curve = int(sys.argv[4]) if len(sys.argv) > 4 else 0  # msm only
 ctx = api.Context(0)
 lib = ctx.lib
 ELL = api.ORDERS[0]
@@ -39,9 +40,10 @@ if case in ("verify", "prove"):
         timeit(lambda: api.verify_batch(pk, n, m, proofs, Vl), f"verify_batch host-ABI B={size}")
 elif case == "msm":
     N = 1 << size
-    mult = b"".join(rng.randrange(ELL).to_bytes(32, "little") for _ in range(N))
-    pts = api.Points.from_multipliers(mult, 0, ctx)
-    sc = b"".join(rng.randrange(ELL).to_bytes(32, "little") for _ in range(N))
+    order = api.ORDERS[curve]
+    mult = b"".join(rng.randrange(order).to_bytes(32, "little") for _ in range(N))
+    pts = api.Points.from_multipliers(mult, curve, ctx)
+    sc = b"".join(rng.randrange(order).to_bytes(32, "little") for _ in range(N))
     size = N
     timeit(lambda: pts.msm(sc), f"msm N=2^{sys.argv[2]}")
 elif case == "commit":
