@@ -443,36 +443,47 @@ def run_extras(args, torch, api, _lib, ctx, pk, dev, stream, int_peak):
               ("_secp256k1", _lib.SECP256K1, min(args.msm_max_log, 20), 256, 72, (11, 16, 7)),
               ("_bls12_381_g1", _lib.BLS12_381_G1, min(args.msm_max_log, 20), 255, 300, (11, 16, 7)))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        reps = 5
+        e0.record(stream)
+        for _ in range(reps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
     for suffix, curve, max_log, bits, imad, costs in curves:
         sweep = []
         n_max = 1 << max_log
         mult = torch.randint(0, 256, (n_max, 32), dtype=torch.uint8)
         mult[:, 31] &= 0x0F  # < 2^252 < every group order
-        pts = api.Points.from_multipliers(bytes(mult.numpy().tobytes()), curve, ctx)
         sc = torch.randint(0, 256, (n_max, 32), dtype=torch.uint8)
         sc[:, 31] &= 0x0F
         d_sc = sc.to(dev)
         d_out = torch.empty(lib.bpp_point_bytes(curve), dtype=torch.uint8, device=dev)
         for lg in range(10, max_log + 1, 2):
             n = 1 << lg
+            # one point set per size: P_i = mult_i * g generated on the device
+            pts = api.Points.from_multipliers(bytes(mult[:n].numpy().tobytes()), curve, ctx)
 
             def msm():
                 ctx.check(lib.bpp_msm_prepared_dev(ctx.h, pts.h, d_sc.data_ptr(), n, 1, d_out.data_ptr()), "msm")
 
-            for _ in range(3):
-                msm()
-            torch.cuda.synchronize()
-            reps = 5
-            e0.record(stream)
-            for _ in range(reps):
-                msm()
-            e1.record(stream)
-            torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / reps
+            generic_ms = timed(msm)          # Pippenger over the bare points (what a one-shot MulVec::calculate gets)
+            first = bytes(d_out.cpu().numpy().tobytes())
+            pts.precompute()                 # window tables for a reused point set: no doublings, one bucket set
+            tables_ms = timed(msm)
+            assert bytes(d_out.cpu().numpy().tobytes()) == first, "window-table MSM disagrees with the generic one"
+            # tables win while the Horner pass dominates (small N); beyond ~2^18 points the 16x larger gather footprint costs more
+            ms, path = (tables_ms, "window tables") if tables_ms < generic_ms else (generic_ms, "generic")
             W, c_star, _ = algorithmic_field_muls(n, bits, *costs)
-            sweep.append({"log2_n": lg, "ms": ms, "points_per_sec": n / (ms * 1e-3), "int_roofline_frac": W * imad / (ms * 1e-3) / int_peak})
+            sweep.append({"log2_n": lg, "ms": ms, "points_per_sec": n / (ms * 1e-3), "int_roofline_frac": W * imad / (ms * 1e-3) / int_peak,
+                          "path": path, "generic_ms": generic_ms, "tables_ms": tables_ms})
+            del pts
         out["msm_points_per_sec" + suffix] = sweep
-        del pts
     return out
 
 

@@ -334,6 +334,11 @@ class Points:
     def __len__(self):
         return int(self.ctx.lib.bpp_points_len(self.h))
 
+    def precompute(self) -> "Points":
+        """Build window tables for this point set (bpp_points_precompute): same results, no doublings in later MSMs."""
+        self.ctx.check(self.ctx.lib.bpp_points_precompute(self.ctx.h, self.h), "points_precompute")
+        return self
+
     def msm(self, scalars: bytes, k: int | None = None, n_jobs: int = 1) -> list:
         k = k if k is not None else len(scalars) // 32 // n_jobs
         out = C.create_string_buffer(n_jobs * self.pb)

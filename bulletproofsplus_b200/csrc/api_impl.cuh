@@ -54,10 +54,22 @@ struct Api {
       for (uint32_t k = 0; k < L; k++) zero_challenge = zero_challenge || is_zero(P_FIXED + k);
       if (zero_challenge) { ctx->err = "params: a challenge is zero (not invertible)"; return BPP_ERR_FORMAT; }
     }
+    if (ctx->params_gen && h == ctx->params_host) return BPP_OK;  // same block as the previous call: already on the device
     BPP_CK(ctx->buf[B_PARAMS].ensure(h.size()));
-    BPP_CK(cudaMemcpyAsync(ctx->buf[B_PARAMS].p, h.data(), h.size(), cudaMemcpyHostToDevice, ctx->stream));
-    BPP_CK(cudaStreamSynchronize(ctx->stream));  // h is a stack-lifetime staging buffer
+    ctx->params_gen++;
+    ctx->tab_gen = 0;
+    ctx->params_host.swap(h);  // staging buffer with context lifetime: the copy below needs no synchronisation
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_PARAMS].p, ctx->params_host.data(), ctx->params_host.size(), cudaMemcpyHostToDevice, ctx->stream));
     return BPP_OK;
+  }
+  // true when B_TAB* already hold the tables for (kind, current parameter block, shape, pk); otherwise records that they will
+  static bool tables_cached(bpp_ctx* ctx, uint32_t kind, const bpp_pk* pk, uint32_t N, uint32_t n, uint32_t m, uint32_t mode) {
+    const bool hit = mode != 0 && ctx->tab_gen == ctx->params_gen && ctx->tab_kind == kind && ctx->tab_pk == pk && ctx->tab_shape[0] == N &&
+                     ctx->tab_shape[1] == n && ctx->tab_shape[2] == m && ctx->tab_shape[3] == mode && ctx->tab_shape[4] == (uint32_t)C::CURVE_ID;
+    ctx->tab_gen = mode != 0 ? ctx->params_gen : 0;  // mode 0 (standalone WIP) tables depend on caller vectors: never reused
+    ctx->tab_kind = kind; ctx->tab_pk = pk;
+    ctx->tab_shape[0] = N; ctx->tab_shape[1] = n; ctx->tab_shape[2] = m; ctx->tab_shape[3] = mode; ctx->tab_shape[4] = (uint32_t)C::CURVE_ID;
+    return hit;
   }
   static int read_flag(bpp_ctx* ctx, const uint8_t* d_flag, uint8_t* out) {
     BPP_CK(cudaMemcpyAsync(out, d_flag, 1, cudaMemcpyDeviceToHost, ctx->stream));
@@ -167,9 +179,34 @@ struct Api {
       rc = read_flag(ctx, ctx->buf[B_FLAGS].as<uint8_t>(), &bad);
     } while (0);
     if (rc == BPP_OK && bad) rc = BPP_ERR_FORMAT;
-    if (rc != BPP_OK) { cudaFree(pts->table); delete pts; return rc; }
+    if (rc != BPP_OK) { points_release(pts); return rc; }
     *out = pts;
     return BPP_OK;
+  }
+  // Window tables for a point set that will be multiplied many times (the same construction as the public key's): about
+  // SCALAR_BITS doublings and WA affine conversions per point once, WA x the memory; MSMs against it then need no doublings,
+  // no per-window bucket sets and no Horner pass.
+  static int points_precompute(bpp_ctx* ctx, bpp_points* pts) {
+    if (pts->wtab) return BPP_OK;
+    const uint32_t n = (uint32_t)pts->len;
+    const uint32_t c = choose_window_fixed(n, C::SCALAR_BITS), W = (C::SCALAR_BITS + 1 + c - 1) / c;
+    const size_t bytes = (size_t)n * W * C::AFF_WORDS * 4;
+    if (bytes > ((size_t)48 << 30)) { ctx->err = "points_precompute: window tables would exceed 48 GB"; return BPP_ERR_LENGTH; }
+    uint32_t* wtab = nullptr;
+    cudaError_t e = cudaMalloc(&wtab, bytes);
+    if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
+    wtab_build_kernel<C><<<ceil_div(n, 64), 64, 0, ctx->stream>>>(n, c, W, pts->table, wtab);
+    ctx->launches++;
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { cudaFree(wtab); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
+    pts->wtab = wtab; pts->cA = c; pts->WA = W;
+    return BPP_OK;
+  }
+  static void points_release(bpp_points* pts) {
+    if (pts->table) cudaFree(pts->table);
+    if (pts->wtab) cudaFree(pts->wtab);
+    delete pts;
   }
   // scalars already on device (n_jobs*k); result: n_jobs extended points in B_RESULTS
   static int msm_prepared_core(bpp_ctx* ctx, const bpp_points* pts, const uint32_t* d_scalars, size_t k, size_t n_jobs) {
@@ -180,6 +217,8 @@ struct Api {
     BPP_CK(cudaMemcpyAsync(ctx->buf[B_SCALARS].p, d_scalars, (size_t)T * 32, cudaMemcpyDeviceToDevice, ctx->stream));
     BPP_LAUNCH(scalars_check_kernel<M>, ceil_div(T, 256), 256, 0, T, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_FLAGS].as<uint8_t>());
     BPP_LAUNCH(iota_kernel, ceil_div(T, 256), 256, 0, T, (uint32_t)k, ctx->buf[B_PIDX].as<uint32_t>());
+    if (pts->wtab)  // point index i < len: fixed-base segment only
+      return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, pts->wtab, (uint32_t)pts->len, pts->cA, pts->WA, nullptr, 0);
     return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, nullptr, 0, 0, 0, pts->table, (uint32_t)k);
   }
   static int msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out, bool raw) {
@@ -227,13 +266,13 @@ struct Api {
       std::vector<uint8_t> mult(32, 0); mult[0] = 1;
       BPP_TRY(points_upload(ctx, mult.data(), 1, true, &one));
       int rc = msm_prepared(ctx, one, z.data(), 1, 1, out, false);
-      cudaFree(one->table); delete one;
+      points_release(one);
       return rc;
     }
     bpp_points* pts = nullptr;
     BPP_TRY(points_upload(ctx, points, k, false, &pts));
     int rc = msm_prepared(ctx, pts, scalars, k, 1, out, false);
-    cudaFree(pts->table); delete pts;
+    points_release(pts);
     return rc;
   }
   static int points_sum_raw(bpp_ctx* ctx, const uint8_t* raw, size_t count, uint8_t* out) {
@@ -285,7 +324,10 @@ struct Api {
     T.Tmul = ctx->buf[B_TAB0].as<uint32_t>(); T.Tadd = ctx->buf[B_TAB1].as<uint32_t>(); T.tmp = ctx->buf[B_TAB2].as<uint32_t>();
     T.zpow = ctx->buf[B_TAB3].as<uint32_t>();
     uint32_t* xs = ctx->buf[B_TAB4].as<uint32_t>();
-    BPP_LAUNCH(verify_tables_kernel<M>, 1, VT_THREADS, 0, vs, ctx->buf[B_PARAMS].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
+    const size_t cap0 = ctx->buf[B_TAB0].cap + ctx->buf[B_TAB1].cap + ctx->buf[B_TAB2].cap + ctx->buf[B_TAB3].cap;
+    if (!tables_cached(ctx, 1, pk, N, n, m, mode) || cap0 != ctx->tab_caps)
+      BPP_LAUNCH(verify_tables_kernel<M>, 1, VT_THREADS, 0, vs, ctx->buf[B_PARAMS].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
+    ctx->tab_caps = cap0;
     BPP_LAUNCH(verify_proof_scalars_kernel<M>, ceil_div(count, 128), 128, 0, count, d_proofs, proof_len, (size_t)ppp * PB, xs,
                ctx->buf[B_FLAGS2].as<uint8_t>());
     dim3 grid(ceil_div(K, 256), count);
@@ -363,7 +405,11 @@ struct Api {
     uint32_t* a = ctx->buf[B_WORK0].as<uint32_t>();
     uint32_t* b = ctx->buf[B_WORK1].as<uint32_t>();
     uint32_t* alpha = ctx->buf[B_WORK2].as<uint32_t>();
-    BPP_LAUNCH(prove_tables_kernel<M>, 1, 256, 0, ps, params, d_ypow, T);
+    const size_t cap0 = ctx->buf[B_TAB0].cap + ctx->buf[B_TAB1].cap + ctx->buf[B_TAB2].cap + ctx->buf[B_TAB3].cap + ctx->buf[B_TAB4].cap +
+                        ctx->buf[B_TAB5].cap;
+    if (!tables_cached(ctx, 2, pk, N, n, m, mode) || cap0 != ctx->tab_caps)
+      BPP_LAUNCH(prove_tables_kernel<M>, 1, 256, 0, ps, params, d_ypow, T);
+    ctx->tab_caps = cap0;
     if (mode == 0) {
       BPP_LAUNCH(wip_load_kernel<M>, ceil_div(N, 128), 128, 0, N, d_a, d_b, d_gamma, a, b, alpha, ctx->buf[B_FLAGS].as<uint8_t>());
       BPP_LAUNCH(scalars_check_kernel<M>, ceil_div(N, 128), 128, 0, N, d_ypow, ctx->buf[B_FLAGS].as<uint8_t>());

@@ -174,7 +174,13 @@ size_t bpp_points_len(const bpp_points* pts) { return pts ? pts->len : 0; }
 void bpp_points_free(bpp_points* pts) {
   if (!pts) return;
   cudaFree(pts->table);
+  if (pts->wtab) cudaFree(pts->wtab);
   delete pts;
+}
+int bpp_points_precompute(bpp_ctx* ctx, bpp_points* pts) {
+  BPP_ENTER(ctx);
+  if (!pts) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pts->curve, points_precompute(ctx, pts));
 }
 int bpp_msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out_points) {
   BPP_ENTER(ctx);

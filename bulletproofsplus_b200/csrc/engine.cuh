@@ -51,6 +51,16 @@ struct bpp_ctx {
   uint64_t hot_launches = 0;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hot_pending;
   std::vector<uint32_t> host_jobstart;
+  // The challenge-only tables of the prover / verifier (B_TAB0..5) depend on the parameter block and the proof shape, not on
+  // the proofs: a call that repeats the previous call's parameters and shape reuses them (one single-block kernel and one
+  // upload + sync less per batch). params_gen counts distinct uploads; tab_* describe what B_TAB* currently holds.
+  std::vector<uint8_t> params_host;
+  uint64_t params_gen = 0;
+  uint64_t tab_gen = 0;      // params_gen the tables were built from; 0 = none
+  uint32_t tab_kind = 0;     // 1 verifier tables, 2 prover tables
+  uint32_t tab_shape[5] = {0, 0, 0, 0, 0};  // N, n, m, mode, curve
+  const void* tab_pk = nullptr;
+  size_t tab_caps = 0;       // capacities of the table buffers when they were filled (a re-allocation invalidates them)
 };
 
 struct bpp_pk {
@@ -68,6 +78,8 @@ struct bpp_points {
   int curve = 0;
   size_t len = 0;
   uint32_t* table = nullptr;  // affine
+  uint32_t* wtab = nullptr;   // optional window tables (bpp_points_precompute): wtab[w * len + i] = 2^(cA * w) * table[i]
+  uint32_t cA = 0, WA = 0;
 };
 
 namespace bpp {

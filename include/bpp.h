@@ -84,6 +84,12 @@ int bpp_points_upload(bpp_ctx* ctx, int curve, const uint8_t* points, size_t k, 
 int bpp_points_from_multipliers(bpp_ctx* ctx, int curve, const uint8_t* mult_scalars, size_t k, bpp_points** out);
 size_t bpp_points_len(const bpp_points* pts);
 void bpp_points_free(bpp_points* pts);
+/* Optional, for a point set that many MSMs will reuse (what the builder pattern of mulvec.rs:35-53 cannot express: the
+ * reference clones its points into every MulVec): window tables 2^(c*w) * P_i, as the public key carries for its generators.
+ * Costs about 254 doublings and ceil(254/c) affine conversions per point once and ceil(254/c) x the table memory (refused
+ * above 48 GB); later bpp_msm_prepared* calls against `pts` run without doublings, per-window bucket sets or Horner pass.
+ * Results are identical with and without it. */
+int bpp_points_precompute(bpp_ctx* ctx, bpp_points* pts);
 /* n_jobs independent MSMs over consecutive slices of `scalars`, all against pts[0..k): out = n_jobs points */
 int bpp_msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out_points);
 /* same with device pointers (no host copies, no synchronisation): d_scalars = n_jobs*k*32 B, d_out = n_jobs encodings */

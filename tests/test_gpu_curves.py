@@ -131,7 +131,13 @@ def test_msm(api, ctx, oracle, R):
     mult = [rng.randrange(q) for _ in range(n)]
     sc = [rng.randrange(q) for _ in range(n)]
     pts = api.Points.from_multipliers(b"".join(le32(x) for x in mult), R, ctx)
-    assert pts.msm(b"".join(le32(x) for x in sc))[0] == oracle.scalar_mul(R, sum(a * b for a, b in zip(mult, sc)) % q)
+    want = oracle.scalar_mul(R, sum(a * b for a, b in zip(mult, sc)) % q)
+    assert pts.msm(b"".join(le32(x) for x in sc))[0] == want
+    assert pts.precompute().msm(b"".join(le32(x) for x in sc))[0] == want  # window tables: same point, no doublings
+    dup = api.Points.from_multipliers(b"".join(le32(mult[i // 2] if i % 2 == 0 else (q - mult[i // 2])) for i in range(256)), R, ctx).precompute()
+    s256 = sc[:256]
+    want = sum(s * (mult[i // 2] if i % 2 == 0 else q - mult[i // 2]) for i, s in enumerate(s256)) % q
+    assert dup.msm(b"".join(le32(x) for x in s256))[0] == oracle.scalar_mul(R, want)  # P, -P pairs: exceptional additions in the buckets
 
 
 @pytest.mark.parametrize("R", CURVES)

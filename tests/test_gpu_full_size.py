@@ -104,7 +104,9 @@ def test_config5_msm_large(api, ctx, oracle, logn):
         unit = bytearray(32 * n)
         unit[32 * i] = 1
         assert pts.msm(bytes(unit))[0] == oracle.scalar_mul(R, ks[i])
-    assert pts.msm(_enc(ss))[0] == oracle.scalar_mul(R, sum(s * k for s, k in zip(ss, ks)) % ELL)
+    want = oracle.scalar_mul(R, sum(s * k for s, k in zip(ss, ks)) % ELL)
+    assert pts.msm(_enc(ss))[0] == want
+    assert pts.precompute().msm(_enc(ss))[0] == want  # window tables of the same points: same point
 
 
 @pytest.mark.parametrize("logn", [16, 20])
@@ -120,13 +122,18 @@ def test_config5_msm_distributions(api, ctx, oracle, logn):
         "below 2^16": _scalars(0xC5E + logn, n, 2**16),
         "quarter zero": [0 if i % 4 == 0 else s for i, s in enumerate(full)],
     }
-    for name, ss in dists.items():
-        assert pts.msm(_enc(ss))[0] == oracle.scalar_mul(R, sum(s * k for s, k in zip(ss, ks)) % ELL), name
     same = api.Points.from_multipliers(le32(ks[0]) * n, R, ctx)
-    assert same.msm(_enc(full))[0] == oracle.scalar_mul(R, sum(full) * ks[0] % ELL)
     alt = [ks[1] if i % 2 == 0 else ELL - ks[1] for i in range(n)]  # P, -P, P, -P, ...
     pm = api.Points.from_multipliers(_enc(alt), R, ctx)
-    assert pm.msm(_enc(full))[0] == oracle.scalar_mul(R, sum(s * k for s, k in zip(full, alt)) % ELL)
     gens = [3 * (i + 1) if i < n // 2 else 5 * (i - n // 2 + 1) for i in range(n)]  # the reference's structured generators
     pg = api.Points.from_multipliers(_enc(gens), R, ctx)
-    assert pg.msm(_enc(full))[0] == oracle.scalar_mul(R, sum(s * k for s, k in zip(full, gens)) % ELL)
+    want = {name: oracle.scalar_mul(R, sum(s * k for s, k in zip(ss, ks)) % ELL) for name, ss in dists.items()}
+    for tables in (False, True):
+        if tables:
+            for p in (pts, same, pm, pg):
+                p.precompute()
+        for name, ss in dists.items():
+            assert pts.msm(_enc(ss))[0] == want[name], (name, tables)
+        assert same.msm(_enc(full))[0] == oracle.scalar_mul(R, sum(full) * ks[0] % ELL)
+        assert pm.msm(_enc(full))[0] == oracle.scalar_mul(R, sum(s * k for s, k in zip(full, alt)) % ELL)
+        assert pg.msm(_enc(full))[0] == oracle.scalar_mul(R, sum(s * k for s, k in zip(full, gens)) % ELL)

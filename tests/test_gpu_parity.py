@@ -159,17 +159,20 @@ def test_msm_large_device_generated_points(api, ctx, oracle, logn):
     ss = [pyref.prng_scalar(0xB2000001, i, ELL) for i in range(n)]
     pts = api.Points.from_multipliers(b"".join(le32(k) for k in ks), R, ctx)
     assert len(pts) == n
-    got = pts.msm(b"".join(le32(s) for s in ss))[0]
-    assert got == oracle.scalar_mul(R, sum(s * k for s, k in zip(ss, ks)) % ELL)
-    # several jobs against the same table; and the raw partial-sum path used for the multi-GPU split
-    jobs = 3
-    s2 = [pyref.prng_scalar(0xB2000011, i, ELL) for i in range(jobs * 256)]
-    got = pts.msm(b"".join(le32(s) for s in s2), k=256, n_jobs=jobs)
-    for j in range(jobs):
-        assert got[j] == oracle.scalar_mul(R, sum(s * k for s, k in zip(s2[j * 256:(j + 1) * 256], ks)) % ELL)
-    raw = pts.msm_raw(b"".join(le32(s) for s in ss[:512]), 512) + pts.msm_raw(b"".join(le32(s) for s in ss[:7]), 7)
-    want = (sum(s * k for s, k in zip(ss[:512], ks)) + sum(s * k for s, k in zip(ss[:7], ks))) % ELL
-    assert api.points_sum_raw(raw, R, ctx) == oracle.scalar_mul(R, want)
+    s2 = [pyref.prng_scalar(0xB2000011, i, ELL) for i in range(3 * 256)]
+    for tables in (False, True):  # generic Pippenger, then the same calls against window tables of the same points
+        if tables:
+            pts.precompute()
+        got = pts.msm(b"".join(le32(s) for s in ss))[0]
+        assert got == oracle.scalar_mul(R, sum(s * k for s, k in zip(ss, ks)) % ELL)
+        # several jobs against the same table; and the raw partial-sum path used for the multi-GPU split
+        jobs = 3
+        got = pts.msm(b"".join(le32(s) for s in s2), k=256, n_jobs=jobs)
+        for j in range(jobs):
+            assert got[j] == oracle.scalar_mul(R, sum(s * k for s, k in zip(s2[j * 256:(j + 1) * 256], ks)) % ELL)
+        raw = pts.msm_raw(b"".join(le32(s) for s in ss[:512]), 512) + pts.msm_raw(b"".join(le32(s) for s in ss[:7]), 7)
+        want = (sum(s * k for s, k in zip(ss[:512], ks)) + sum(s * k for s, k in zip(ss[:7], ks))) % ELL
+        assert api.points_sum_raw(raw, R, ctx) == oracle.scalar_mul(R, want)
 
 
 def test_msm_degenerate_distributions(api, ctx, oracle):
@@ -178,11 +181,19 @@ def test_msm_degenerate_distributions(api, ctx, oracle):
     pts = api.Points.from_multipliers(b"".join(le32(k) for k in ks), R, ctx)
     rng = random.Random(8)
     s_eq = rng.randrange(ELL)
-    for ss in ([s_eq] * n, [rng.randrange(2**16) for _ in range(n)], [0 if i % 4 == 0 else rng.randrange(ELL) for i in range(n)]):
-        assert pts.msm(b"".join(le32(s) for s in ss))[0] == oracle.scalar_mul(R, sum(s * k for s, k in zip(ss, ks)) % ELL)
+    dists = ([s_eq] * n, [rng.randrange(2**16) for _ in range(n)], [0 if i % 4 == 0 else rng.randrange(ELL) for i in range(n)],
+             [ELL - 1] * n, [0] * n)
     same = api.Points.from_multipliers(le32(ks[0]) * n, R, ctx)
-    ss = [rng.randrange(ELL) for _ in range(n)]
-    assert same.msm(b"".join(le32(s) for s in ss))[0] == oracle.scalar_mul(R, sum(ss) * ks[0] % ELL)
+    with_identity = api.Points.from_multipliers(b"".join(le32(0 if i % 5 == 0 else k) for i, k in enumerate(ks)), R, ctx)
+    s_full = [rng.randrange(ELL) for _ in range(n)]
+    for tables in (False, True):
+        if tables:
+            pts.precompute(); same.precompute(); with_identity.precompute()
+        for ss in dists:
+            assert pts.msm(b"".join(le32(s) for s in ss))[0] == oracle.scalar_mul(R, sum(s * k for s, k in zip(ss, ks)) % ELL)
+        assert same.msm(b"".join(le32(s) for s in s_full))[0] == oracle.scalar_mul(R, sum(s_full) * ks[0] % ELL)
+        want = sum(s * k for i, (s, k) in enumerate(zip(s_full, ks)) if i % 5) % ELL
+        assert with_identity.msm(b"".join(le32(s) for s in s_full))[0] == oracle.scalar_mul(R, want)
 
 
 # ---------------------------------------------------------------------------------- RangeProof::prove / verify
@@ -290,6 +301,41 @@ def test_custom_challenges_and_nonces(api, ctx, oracle):
     exp = ec.Checker(ELL).range_prove(n, m, vs, gs, ec.Params(**vals))
     rp = api.RangeProof.from_bytes(proof, 32)
     assert (rp.proof.r_prime, rp.proof.s_prime, rp.proof.d_prime) == (exp.r_prime, exp.s_prime, exp.d_prime)
+
+
+def test_challenge_table_reuse_across_calls(api, ctx, oracle):
+    """The library keeps the challenge-only tables of the previous call when parameters and shape repeat. Interleave
+    repeats, parameter changes, shape changes and prove/verify on ONE context: every result must still match the oracle."""
+    rng = random.Random(99)
+    rounds = 6
+    vals = dict(y=rng.randrange(1, ELL), z=rng.randrange(1, ELL), e_final=rng.randrange(1, ELL), alpha=rng.randrange(ELL),
+                r=rng.randrange(ELL), s=rng.randrange(ELL), delta=rng.randrange(ELL), eta=rng.randrange(ELL),
+                e_round=[rng.randrange(1, ELL) for _ in range(rounds)], d_L=[rng.randrange(ELL) for _ in range(rounds)],
+                d_R=[rng.randrange(ELL) for _ in range(rounds)])
+    bp, op = api.make_params(**vals), oracle_lib.make_params(oracle_lib.OrcParams, **vals)
+    shapes = {(16, 4): api.PublicKey.new(64, R, ctx), (8, 8): api.PublicKey.new(64, R, ctx), (32, 1): api.PublicKey.new(32, R, ctx)}
+    data = {}
+    for (n, m) in shapes:
+        vs, gs = _inputs(n, m, 31 * n + m)
+        data[(n, m)] = (vs, gs, oracle.commit(R, vs, gs))
+    script = [((16, 4), None), ((16, 4), None), ((16, 4), "custom"), ((16, 4), "custom"), ((8, 8), "custom"), ((8, 8), None),
+              ((16, 4), None), ((32, 1), None), ((32, 1), None), ((16, 4), "custom"), ((16, 4), None)]
+    for step, (shape, which) in enumerate(script):
+        n, m = shape
+        if m == 1 and which:
+            continue
+        pk = shapes[shape]
+        vs, gs, V = data[shape]
+        b_par, o_par = (bp, op) if which else (None, None)
+        want = oracle.range_prove(R, n, m, vs, gs, o_par) if o_par else oracle.range_prove(R, n, m, vs, gs)
+        Vl = [[V[i * 32:(i + 1) * 32] for i in range(m)]]
+        if step % 3 != 1:  # prove on most steps: it overwrites the verifier's tables
+            assert api.prove_batch(pk, n, m, vs, gs, b_par)[0] == want, (step, shape, which)
+        assert api.verify_batch(pk, n, m, [want], Vl, b_par) == [0], (step, shape, which)
+        assert api.verify_batch(pk, n, m, [want], Vl, b_par) == [0], (step, shape, which)  # immediate repeat: tables reused
+        other = None if which else bp
+        if m > 1:
+            assert api.verify_batch(pk, n, m, [want], Vl, other) == [1], (step, shape, which)  # other challenges must reject
 
 
 def test_batch_prove_and_verify_many(api, ctx, oracle):

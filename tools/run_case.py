@@ -43,6 +43,8 @@ elif case == "msm":
     order = api.ORDERS[curve]
     mult = b"".join(rng.randrange(order).to_bytes(32, "little") for _ in range(N))
     pts = api.Points.from_multipliers(mult, curve, ctx)
+    if os.environ.get('BPP_TABLES'):
+        pts.precompute()
     sc = b"".join(rng.randrange(order).to_bytes(32, "little") for _ in range(N))
     size = N
     timeit(lambda: pts.msm(sc), f"msm N=2^{sys.argv[2]}")
