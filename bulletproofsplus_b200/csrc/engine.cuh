@@ -32,7 +32,7 @@ struct DevBuf {
 enum BufId {
   B_SCALARS, B_PIDX, B_JOBSTART, B_COUNTS, B_OFFSETS, B_CURSOR, B_TILES, B_SORTED, B_PERM, B_BINS, B_BUCKETS, B_CHUNK_S, B_CHUNK_T,
   B_WINDOWS, B_FIXEDRES, B_RESULTS, B_DYN, B_DYN_OK, B_IN0, B_IN1, B_IN2, B_IN3, B_OUT0, B_PARAMS, B_TAB0, B_TAB1, B_TAB2, B_TAB3, B_TAB4,
-  B_TAB5, B_TAB6, B_WORK0, B_WORK1, B_WORK2, B_FLAGS, B_FLAGS2, B_EXT, B_COUNT_
+  B_TAB5, B_TAB6, B_WORK0, B_WORK1, B_WORK2, B_FLAGS, B_FLAGS2, B_EXT, B_GIANT_CTL, B_GIANT_ITEMS, B_GIANT_KEYS, B_GIANT_PART, B_COUNT_
 };
 
 }  // namespace bpp
@@ -180,6 +180,16 @@ struct Msm {
     BPP_CK(ctx->buf[B_WINDOWS].ensure((size_t)(n_setsB ? n_setsB : 1) * C::EXT_WORDS * 4));
     BPP_CK(ctx->buf[B_FIXEDRES].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
     BPP_CK(ctx->buf[B_RESULTS].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
+    // giant buckets: sum over buckets of ceil(count / GIANT_SEG) <= entries / GIANT_SEG + (number of giant buckets)
+    const size_t max_items = 2 * (size_t)(n_entries / GIANT_SEG) + 64;
+    BPP_CK(ctx->buf[B_GIANT_CTL].ensure(16));
+    BPP_CK(ctx->buf[B_GIANT_ITEMS].ensure(max_items * sizeof(uint2)));
+    BPP_CK(ctx->buf[B_GIANT_KEYS].ensure(max_items * sizeof(uint4)));
+    BPP_CK(ctx->buf[B_GIANT_PART].ensure(max_items * C::EXT_WORDS * 4));
+    uint32_t* gctl = ctx->buf[B_GIANT_CTL].as<uint32_t>();
+    uint2* gitems = ctx->buf[B_GIANT_ITEMS].as<uint2>();
+    uint4* gkeys = ctx->buf[B_GIANT_KEYS].as<uint4>();
+    uint32_t* gpart = ctx->buf[B_GIANT_PART].as<uint32_t>();
     uint32_t* counts = ctx->buf[B_COUNTS].as<uint32_t>();
     uint32_t* offsets = ctx->buf[B_OFFSETS].as<uint32_t>();
     uint32_t* cursor = ctx->buf[B_CURSOR].as<uint32_t>();
@@ -196,6 +206,7 @@ struct Msm {
     const uint32_t* scalars = ctx->buf[B_SCALARS].as<uint32_t>();
     const uint32_t* pidx = ctx->buf[B_PIDX].as<uint32_t>();
     BPP_CK(cudaMemsetAsync(bins, 0, 256 * 4, ctx->stream));
+    BPP_CK(cudaMemsetAsync(gctl, 0, 16, ctx->stream));
     const uint32_t KPJ = pl.NBA + pl.WB * pl.NBB;
     if (KPJ <= 12288) {
       // small key space per job: one block sorts a whole job in shared memory
@@ -226,6 +237,11 @@ struct Msm {
       const uint32_t g32 = ceil_div(n_keys, 4) < 1184 ? ceil_div(n_keys, 4) : 1184, g4 = ceil_div(n_keys, 32) < 1184 ? ceil_div(n_keys, 32) : 1184;
       auto k32 = msm_accumulate_group_kernel<C, 32>;
       auto k4 = msm_accumulate_group_kernel<C, 4>;
+      if (n_entries > GIANT_SEG) {  // a bucket can only be giant if there are that many entries at all
+        BPP_LAUNCH(msm_giant_enum_kernel, g32 < 148 ? g32 : 148, 256, 0, bins + 256, perm, counts, gctl, gitems, gkeys);
+        BPP_LAUNCH(msm_giant_accumulate_kernel<C>, g32, 128, 0, gctl, gitems, offsets, counts, sorted, wtab, pl.wtab_points, dyn, gpart);
+        BPP_LAUNCH(msm_giant_merge_kernel<C>, g32 < 296 ? g32 : 296, 128, 0, gctl, gkeys, gpart, buckets);
+      }
       BPP_LAUNCH(k32, g32, 128, 0, bins + 256, 0u, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets);
       BPP_LAUNCH(k4, g4, 128, 0, bins + 256, 1u, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets);
     }

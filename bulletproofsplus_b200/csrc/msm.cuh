@@ -328,6 +328,10 @@ static __global__ void __launch_bounds__(SS_THREADS) sizesort_scatter_kernel(con
 // ACC_CAP (the partial top window always produces some; adversarial scalars produce more) are left to
 // msm_accumulate_group_kernel, which spreads each of them over 4 or 32 lanes.
 constexpr uint32_t ACC_CAP = 96;
+// Buckets longer than GIANT_SEG entries are cut into segments of GIANT_SEG, one warp per segment, and merged afterwards:
+// skewed scalar sets (all equal, P/-P pairs, a top window of one or two bits) put a large share of ALL terms into a few
+// buckets, which would otherwise serialise on one warp each.
+constexpr uint32_t GIANT_SEG = 2048;
 
 template <class C>
 __device__ __forceinline__ const uint32_t* msm_point_ptr(uint32_t ref, const uint32_t* __restrict__ wtab, uint32_t wtab_points,
@@ -371,6 +375,7 @@ msm_accumulate_group_kernel(const uint32_t* __restrict__ tiers, uint32_t tier, c
   const uint32_t n_groups = gridDim.x * (128 / G);
   for (uint32_t t = lo + blockIdx.x * (128 / G) + tid / G; t < hi; t += n_groups) {
     const uint32_t key = perm[t];
+    if (counts[key] > GIANT_SEG) continue;  // split over several warps by the msm_giant_* kernels (warp-uniform test)
     const uint32_t beg = offsets[key], end = beg + counts[key];  // count > ACC_CAP >= G: every lane has an entry
     typename C::Ext acc;
     uint32_t e = beg + lane;
@@ -391,6 +396,86 @@ msm_accumulate_group_kernel(const uint32_t* __restrict__ tiers, uint32_t tier, c
       __syncwarp();
     }
     if (lane == 0) store_words<C::EXT_WORDS>(buckets + (size_t)key * C::EXT_WORDS, acc);
+    __syncwarp();
+  }
+}
+
+// ---- giant buckets: enumerate (bucket, segment) work items, accumulate a segment per warp, merge per bucket -------------
+// ctl[0] = number of work items, ctl[1] = number of giant buckets (both zeroed by the host before the launch)
+static __global__ void msm_giant_enum_kernel(const uint32_t* __restrict__ tiers, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ counts,
+                                             uint32_t* __restrict__ ctl, uint2* __restrict__ items, uint4* __restrict__ gkeys) {
+  const uint32_t lo = tiers[0], hi = tiers[1];
+  for (uint32_t t = lo + blockIdx.x * blockDim.x + threadIdx.x; t < hi; t += gridDim.x * blockDim.x) {
+    const uint32_t key = perm[t], cnt = counts[key];
+    if (cnt <= GIANT_SEG) continue;
+    const uint32_t n_seg = (cnt + GIANT_SEG - 1) / GIANT_SEG;
+    const uint32_t base = atomicAdd(&ctl[0], n_seg), g = atomicAdd(&ctl[1], 1u);
+    gkeys[g] = make_uint4(key, base, n_seg, 0u);
+    for (uint32_t sgm = 0; sgm < n_seg; sgm++) items[base + sgm] = make_uint2(key, sgm);
+  }
+}
+
+// warp-wide sum of the lanes' points through shared memory; the total ends in lane 0's `acc`
+template <class C>
+__device__ __forceinline__ void msm_warp_tree(typename C::Ext& acc, uint32_t* sh, uint32_t tid, uint32_t lane) {
+  typename C::Ext* mine = reinterpret_cast<typename C::Ext*>(sh + tid * C::EXT_WORDS);
+  *mine = acc;
+  __syncwarp();
+  for (uint32_t s = 16; s > 0; s >>= 1) {
+    if (lane < s) {
+      typename C::Ext o = *reinterpret_cast<typename C::Ext*>(sh + (tid + s) * C::EXT_WORDS);
+      C::add(acc, o);
+      *mine = acc;
+    }
+    __syncwarp();
+  }
+}
+
+template <class C>
+__global__ void __launch_bounds__(128)
+msm_giant_accumulate_kernel(const uint32_t* __restrict__ ctl, const uint2* __restrict__ items, const uint32_t* __restrict__ offsets,
+                            const uint32_t* __restrict__ counts, const uint32_t* __restrict__ sorted, const uint32_t* __restrict__ wtab,
+                            uint32_t wtab_points, const uint32_t* __restrict__ dyn, uint32_t* __restrict__ partial) {
+  __shared__ uint32_t sh[128 * C::EXT_WORDS];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, n_items = ctl[0];
+  for (uint32_t it = blockIdx.x * 4 + tid / 32; it < n_items; it += gridDim.x * 4) {
+    const uint2 w = items[it];
+    const uint32_t beg = offsets[w.x] + w.y * GIANT_SEG, stop = offsets[w.x] + counts[w.x];
+    const uint32_t end = beg + GIANT_SEG < stop ? beg + GIANT_SEG : stop;
+    typename C::Ext acc;
+    uint32_t e = beg + lane;
+    if (e < end) {  // the last segment of a bucket may be shorter than a warp
+      uint32_t ref = __ldg(sorted + e);
+      C::init_from_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+      for (e += 32; e < end; e += 32) {
+        ref = __ldg(sorted + e);
+        C::madd_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+      }
+    } else {
+      C::set_identity(acc);
+    }
+    msm_warp_tree<C>(acc, sh, tid, lane);
+    if (lane == 0) store_words<C::EXT_WORDS>(partial + (size_t)it * C::EXT_WORDS, acc);
+    __syncwarp();
+  }
+}
+
+template <class C>
+__global__ void __launch_bounds__(128)
+msm_giant_merge_kernel(const uint32_t* __restrict__ ctl, const uint4* __restrict__ gkeys, const uint32_t* __restrict__ partial,
+                       uint32_t* __restrict__ buckets) {
+  __shared__ uint32_t sh[128 * C::EXT_WORDS];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, n_g = ctl[1];
+  for (uint32_t g = blockIdx.x * 4 + tid / 32; g < n_g; g += gridDim.x * 4) {
+    const uint4 k = gkeys[g];
+    typename C::Ext acc, p;
+    C::set_identity(acc);
+    for (uint32_t sgm = lane; sgm < k.z; sgm += 32) {
+      load_words<C::EXT_WORDS>(p, partial + (size_t)(k.y + sgm) * C::EXT_WORDS);
+      C::add(acc, p);
+    }
+    msm_warp_tree<C>(acc, sh, tid, lane);
+    if (lane == 0) store_words<C::EXT_WORDS>(buckets + (size_t)k.x * C::EXT_WORDS, acc);
     __syncwarp();
   }
 }

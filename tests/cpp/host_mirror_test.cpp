@@ -1,0 +1,120 @@
+// Exercises the C++ host mirror (include/bpp.hpp) the way the reference's own tests exercise the crate: small
+// known-answer group facts (point.rs:124-185), the README flow, tampering, and the panics. Prints "PASS name" / "FAIL name";
+// tests/test_gpu_cpp_host.py runs it on the GPU box and compares the printed encodings with the CPU oracle.
+#include <cstdio>
+#include <cstdlib>
+#include <functional>
+
+#include "bpp.hpp"
+
+using namespace bulletproofsplus;
+
+static int failures = 0;
+static void report(const char* name, bool ok) {
+  printf("%s %s\n", ok ? "PASS" : "FAIL", name);
+  if (!ok) failures++;
+}
+static bool panics(const std::function<void()>& f) {
+  try { f(); } catch (const Panic&) { return true; }
+  return false;
+}
+static void hex(const char* label, const std::vector<uint8_t>& b) {
+  printf("%s=", label);
+  for (uint8_t x : b) printf("%02x", x);
+  printf("\n");
+}
+
+int main(int argc, char** argv) {
+  const Curve curve = (Curve)(argc > 1 ? atoi(argv[1]) : 0);
+  Arith::init();
+  auto fe = [&](int32_t v) { return PrimeFieldElem::new_(v, curve); };
+
+  // generators: g, h = 2g, G_i = 3(i+1)g, H_i = 5(i+1)g (publickey.rs:21-48) => G_4 == H_2 and g + g == h
+  PublicKey pk8 = PublicKey::new_(8, curve);
+  report("G_4 == H_2 (both 15 g)", pk8.G_vec()[4] == pk8.H_vec()[2]);
+  {
+    MulVec mv(curve);
+    mv.add_scalar(fe(1)); mv.add_point(pk8.g());
+    mv.add_scalar(fe(1)); mv.add_point(pk8.g());
+    report("g + g == h (point.rs:131-139)", mv.calculate() == pk8.h());
+    MulVec three(curve);
+    three.add_scalars({fe(3)}); three.add_points({pk8.g()});
+    report("3 g == G_0", three.calculate() == pk8.G_vec()[0]);
+    MulVec cancel(curve);
+    cancel.add_scalars({fe(5), fe(-5)}); cancel.add_points({pk8.g(), pk8.g()});
+    MulVec empty(curve);
+    report("5 g + (-5) g == Point::zero()", cancel.calculate() == empty.calculate());
+    MulVec bad(curve);
+    bad.add_scalar(fe(1));
+    report("MulVec length mismatch panics (mulvec.rs:23-25)", panics([&] { bad.calculate(); }));
+  }
+  // commitment = v g + gamma h (publickey.rs:50-52): 2 g + 3 h = 8 g
+  {
+    MulVec mv(curve);
+    mv.add_scalar(fe(8)); mv.add_point(pk8.g());
+    report("commitment(2, 3) == 8 g", pk8.commitment(2, fe(3)) == mv.calculate());
+  }
+  // README / main.rs flow and its failure modes
+  for (auto nm : {std::pair<size_t, size_t>{64, 2}, {32, 1}, {8, 4}}) {
+    const size_t n = nm.first, m = nm.second;
+    PublicKey pk = PublicKey::new_(n * m, curve);
+    RangeProver prover = RangeProver::new_();
+    for (size_t j = 0; j < m; j++) prover.commit(pk, 2 + 3 * j, fe(3 + 4 * (int)j));
+    RangeProof proof = RangeProof::prove(pk, n, prover);
+    char label[64];
+    snprintf(label, sizeof label, "proof_n%zu_m%zu", n, m);
+    hex(label, proof.to_bytes());
+    snprintf(label, sizeof label, "verify n=%zu m=%zu == Ok(())", n, m);
+    report(label, proof.verify(pk, n, prover.commitment_vec) == Result::Ok());
+    RangeProof t = proof;
+    t.proof.r_prime.e[0] ^= 1;
+    snprintf(label, sizeof label, "tampered r' n=%zu m=%zu == Err(VerificationError)", n, m);
+    report(label, t.verify(pk, n, prover.commitment_vec) == Result::Err(ProofError::VerificationError));
+    t = proof;
+    t.proof.L_vec[0] = pk.g();
+    snprintf(label, sizeof label, "swapped L_0 n=%zu m=%zu == Err(VerificationError)", n, m);
+    report(label, t.verify(pk, n, prover.commitment_vec) == Result::Err(ProofError::VerificationError));
+    std::vector<Point> other = prover.commitment_vec;
+    other[0] = pk.commitment(3, fe(3));
+    snprintf(label, sizeof label, "other commitment n=%zu m=%zu == Err(VerificationError)", n, m);
+    report(label, proof.verify(pk, n, other) == Result::Err(ProofError::VerificationError));
+    // round trip through the wire format
+    auto bytes = proof.to_bytes();
+    RangeProof back = RangeProof::from_bytes(bytes.data(), bytes.size(), pk.point_bytes());
+    report("wire round trip", back.to_bytes() == bytes && back.verify(pk, n, prover.commitment_vec).is_ok());
+  }
+  {
+    PublicKey pk = PublicKey::new_(24, curve);  // not a power of two
+    RangeProver prover = RangeProver::new_();
+    for (int j = 0; j < 3; j++) prover.commit(pk, 1, fe(1));
+    report("n*m not a power of two panics (wip.rs:67)", panics([&] { RangeProof::prove(pk, 8, prover); }));
+    PublicKey pk16 = PublicKey::new_(16, curve);
+    report("generator count != n*m panics (range/mod.rs:252-253)", panics([&] { RangeProof::prove(pk16, 8, prover); }));
+  }
+  // standalone weighted inner product argument (wip.rs:36-43, :238-248; relation in the comment at :229-237)
+  {
+    const size_t N = 16;
+    PublicKey pk = PublicKey::new_(N, curve);
+    std::vector<PrimeFieldElem> a, b, ypow, zeros(N, fe(0));
+    int64_t y = 1, dl = 0;  // exponents stay small: P = dl * g is computed with one MulVec term
+    for (size_t i = 0; i < N; i++) {
+      y *= 2;  // y = 2: y^(i+1) = 2^(i+1)
+      a.push_back(fe((int)i + 1)); b.push_back(fe(2 * (int)i + 3)); ypow.push_back(fe((int32_t)y));
+      dl += (int64_t)(i + 1) * 3 * (i + 1) + (int64_t)(2 * i + 3) * 5 * (i + 1) + (int64_t)(i + 1) * (2 * i + 3) * y;
+    }
+    const int gamma = 9;
+    dl += 2 * gamma;
+    auto w = WeightedInnerProductProof::prove(pk, a, b, ypow, fe(gamma));
+    hex("wip_N16", w.to_bytes());
+    MulVec mv(curve);
+    // dl < 2^31 here
+    mv.add_scalar(fe((int32_t)dl)); mv.add_point(pk.g());
+    Point P = mv.calculate();
+    report("wip verify == Ok(())", w.verify(pk, ypow, zeros, zeros, fe(0), {}, P, {}) == Result::Ok());
+    report("wip verify, wrong P == Err", w.verify(pk, ypow, zeros, zeros, fe(0), {}, pk.g(), {}) == Result::Err(ProofError::VerificationError));
+    a.pop_back();
+    report("wip length mismatch panics (wip.rs:61-64)", panics([&] { WeightedInnerProductProof::prove(pk, a, b, ypow, fe(gamma)); }));
+  }
+  printf("%s\n", failures ? "SOME FAILED" : "ALL PASSED");
+  return failures ? 1 : 0;
+}
