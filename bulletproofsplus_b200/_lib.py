@@ -20,7 +20,8 @@ SYMBOLS = [
     "bpp_points_upload", "bpp_points_from_multipliers", "bpp_points_len", "bpp_points_precompute", "bpp_points_free", "bpp_msm_prepared",
     "bpp_msm_prepared_dev", "bpp_raw_point_bytes", "bpp_msm_prepared_raw", "bpp_points_sum_raw", "bpp_msm_prepared_raw_dev", "bpp_points_sum_raw_dev", "bpp_range_prove_batch",
     "bpp_range_verify_batch", "bpp_range_prove_batch_dev", "bpp_range_verify_batch_dev", "bpp_range_prove", "bpp_range_verify",
-    "bpp_wip_prove", "bpp_wip_verify", "bpp_int_peak_probe", "bpp_fe_mul_probe", "bpp_hot_kernel_stats", "bpp_debug_op",
+    "bpp_wip_prove", "bpp_wip_verify", "bpp_range_verify_batch_fs", "bpp_range_verify_batch_fs_dev", "bpp_range_prove_begin", "bpp_range_prove_step",
+    "bpp_range_prove_finish", "bpp_prove_session_rounds", "bpp_prove_session_free", "bpp_int_peak_probe", "bpp_fe_mul_probe", "bpp_hot_kernel_stats", "bpp_debug_op",
 ]
 
 
@@ -85,6 +86,13 @@ def load() -> C.CDLL:
     L.bpp_range_verify.argtypes = [vp, vp, sz, sz, u8p, u8p, sz, pp]
     L.bpp_wip_prove.argtypes = [vp, vp, u8p, u8p, u8p, u8p, pp, u8p, C.POINTER(sz)]
     L.bpp_wip_verify.argtypes = [vp, vp, u8p, u8p, u8p, u8p, sz, u8p, u8p, u8p, u8p, sz, pp]
+    L.bpp_range_verify_batch_fs.argtypes = [vp, vp, sz, sz, sz, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p]
+    L.bpp_range_verify_batch_fs_dev.argtypes = [vp, vp, sz, sz, sz, vp, vp, vp, vp]
+    L.bpp_range_prove_begin.argtypes = [vp, vp, sz, sz, sz, C.POINTER(C.c_uint64), C.c_char_p, C.c_char_p, C.POINTER(vp), C.c_char_p]
+    L.bpp_range_prove_step.argtypes = [vp, vp, C.c_char_p, C.c_char_p]
+    L.bpp_range_prove_finish.argtypes = [vp, vp, C.c_char_p, C.c_char_p]
+    L.bpp_prove_session_rounds.argtypes = [vp]
+    L.bpp_prove_session_free.argtypes = [vp]; L.bpp_prove_session_free.restype = None
     L.bpp_int_peak_probe.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.bpp_fe_mul_probe.argtypes = [vp, i, i, i, C.POINTER(C.c_double)]
     L.bpp_hot_kernel_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64), i]

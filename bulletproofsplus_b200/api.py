@@ -278,6 +278,79 @@ def verify_batch(pk: PublicKey, n: int, m: int, proofs, commitments, params: Bpp
     return list(out.raw[:count])
 
 
+class ProveSession:
+    """Interactive batch proving for a transcript-owning host (bpp_range_prove_begin / _step / _finish). Scalars are ints."""
+
+    def __init__(self, pk: PublicKey, n: int, m: int, values, gammas, nonces=None):
+        _shape_asserts(pk, n, m)
+        self.pk, self.n, self.m, self.count = pk, n, m, len(values) // m
+        self.q = ORDERS[pk.curve]
+        self.plen = pk.ctx.lib.bpp_range_proof_len(pk.curve, n, m)
+        arr = (C.c_uint64 * (self.count * m))(*[v & (2**64 - 1) for v in values])
+        nb = None
+        if nonces is not None:  # per proof: dict(alpha, r, s, delta, eta, d_L[L], d_R[L])
+            nb = b"".join(b"".join(_sc(x % self.q) for x in [d["alpha"], d["r"], d["s"], d["delta"], d["eta"], *d["d_L"], *d["d_R"]]) for d in nonces)
+        h = C.c_void_p()
+        out = C.create_string_buffer(self.count * pk.pb)
+        pk.ctx.check(pk.ctx.lib.bpp_range_prove_begin(pk.ctx.h, pk.handle, n, m, self.count, arr, b"".join(_sc(g % self.q) for g in gammas), nb,
+                                                      C.byref(h), out), "range_prove_begin")
+        self.h = h
+        self.rounds = pk.ctx.lib.bpp_prove_session_rounds(h)
+        self.A = [out.raw[i * pk.pb:(i + 1) * pk.pb] for i in range(self.count)]
+
+    def step(self, challenges) -> list:
+        """challenges: per proof (y, z) for the first call, then one scalar. Returns per proof the pair of points produced."""
+        flat = b"".join(b"".join(_sc(x) for x in (c if isinstance(c, (tuple, list)) else (c,))) for c in challenges)
+        out = C.create_string_buffer(self.count * 2 * self.pk.pb)
+        self.pk.ctx.check(self.pk.ctx.lib.bpp_range_prove_step(self.pk.ctx.h, self.h, flat, out), "range_prove_step")
+        pb = self.pk.pb
+        return [(out.raw[(2 * i) * pb:(2 * i + 1) * pb], out.raw[(2 * i + 1) * pb:(2 * i + 2) * pb]) for i in range(self.count)]
+
+    def finish(self, e_final) -> list:
+        out = C.create_string_buffer(self.count * self.plen)
+        self.pk.ctx.check(self.pk.ctx.lib.bpp_range_prove_finish(self.pk.ctx.h, self.h, b"".join(_sc(x) for x in e_final), out), "range_prove_finish")
+        return [out.raw[i * self.plen:(i + 1) * self.plen] for i in range(self.count)]
+
+    def __del__(self):
+        try:
+            self.pk.ctx.lib.bpp_prove_session_free(self.h)
+        except Exception:
+            pass
+
+
+def prove_batch_fs(pk: PublicKey, n: int, m: int, values, gammas, transcripts, nonces=None) -> list:
+    """Real Fiat-Shamir: `transcripts[i]` is proof i's merlin.Transcript (consumed). Returns the proofs."""
+    from . import merlin
+    count = len(values) // m
+    Vs = pk.commit_batch(values, gammas)
+    ses = ProveSession(pk, n, m, values, gammas, nonces)
+    rts = [merlin.RangeProofTranscript(transcripts[i], ORDERS[pk.curve], n, m, Vs[i * m:(i + 1) * m]) for i in range(count)]
+    ch = [rts[i].after_A(ses.A[i]) for i in range(count)]
+    for _ in range(ses.rounds):
+        LR = ses.step(ch)
+        ch = [rts[i].after_round(*LR[i]) for i in range(count)]
+    AB = ses.step(ch)
+    return ses.finish([rts[i].after_final(*AB[i]) for i in range(count)])
+
+
+def verify_batch_fs(pk: PublicKey, n: int, m: int, proofs, commitments, transcripts=None, challenges=None) -> list:
+    """Per-proof challenges, derived here from `transcripts` (one merlin.Transcript per proof) unless given explicitly as lists
+    [y, z, e, e_0..e_{L-1}]. Verdict code per proof."""
+    from . import merlin
+    _shape_asserts(pk, n, m)
+    count = len(proofs)
+    plen = pk.ctx.lib.bpp_range_proof_len(pk.curve, n, m)
+    if any(len(p) != plen for p in proofs):
+        raise FormatError("wrong proof length")
+    if challenges is None:
+        challenges = [merlin.verifier_challenges(transcripts[i], ORDERS[pk.curve], n, m, commitments[i], proofs[i], pk.pb) for i in range(count)]
+    out = C.create_string_buffer(max(1, count))
+    V = b"".join(b"".join(c) for c in commitments)
+    blob = b"".join(b"".join(_sc(x) for x in ch) for ch in challenges)
+    pk.ctx.check(pk.ctx.lib.bpp_range_verify_batch_fs(pk.ctx.h, pk.handle, n, m, count, V, b"".join(proofs), blob, out), "range_verify_batch_fs")
+    return list(out.raw[:count])
+
+
 class MulVec:
     """bls12_381/building_block/mulvec.rs:13-53 — accumulate (scalar, point) pairs, calculate() = sum s_i * P_i."""
 

@@ -294,7 +294,8 @@ struct Api {
   //         ext_* = the caller's commitment exponents (device, canonical).
   static int verify_core(bpp_ctx* ctx, const bpp_pk* pk, uint32_t mode, uint32_t n, uint32_t m, uint32_t count, const uint8_t* d_V,
                          const uint8_t* d_proofs, size_t proof_len, const uint32_t* ext_Gc, const uint32_t* ext_Hc,
-                         const uint32_t* ext_gc, const uint32_t* ext_Vc, const uint32_t* ext_y, uint8_t* d_verdicts) {
+                         const uint32_t* ext_gc, const uint32_t* ext_Vc, const uint32_t* ext_y, uint8_t* d_verdicts,
+                         const uint8_t* d_challenges = nullptr) {
     VerifyShape vs;
     vs.N = (uint32_t)pk->len; vs.L = ilog2(vs.N); vs.n = n; vs.m = m; vs.nV = m; vs.mode = mode; vs.n_proofs = count;
     vs.pk_G0 = 2; vs.pk_H0 = 2 + vs.N; vs.dyn0 = pk->n_points();
@@ -307,10 +308,13 @@ struct Api {
     BPP_CK(ctx->buf[B_FLAGS2].ensure(count));
     BPP_CK(ctx->buf[B_SCALARS].ensure((size_t)count * K * 32));
     BPP_CK(ctx->buf[B_PIDX].ensure((size_t)count * K * 4));
-    BPP_CK(ctx->buf[B_TAB0].ensure((size_t)K * 32));
-    BPP_CK(ctx->buf[B_TAB1].ensure((size_t)K * 32));
-    BPP_CK(ctx->buf[B_TAB2].ensure(((size_t)N + 64) * 32));
-    BPP_CK(ctx->buf[B_TAB3].ensure(((size_t)vs.m + 2) * 32));
+    // d_challenges: every proof has its own challenge set (count x (3 + L) scalars) and therefore its own tables
+    const size_t per = d_challenges ? count : 1;
+    BPP_CK(ctx->buf[B_TAB0].ensure(per * K * 32));
+    BPP_CK(ctx->buf[B_TAB1].ensure(per * K * 32));
+    BPP_CK(ctx->buf[B_TAB2].ensure(per * ((size_t)N + 64) * 32));
+    BPP_CK(ctx->buf[B_TAB3].ensure(per * ((size_t)vs.m + 2) * 32));
+    if (d_challenges) BPP_CK(ctx->buf[B_TAB5].ensure((size_t)count * (P_FIXED + 3 * L) * 32));
     BPP_CK(ctx->buf[B_TAB4].ensure((size_t)count * 128));
     // decode the per-proof points and the commitments into the dynamic table
     const uint32_t gb = count * ppp * (uint32_t)PB;
@@ -323,13 +327,22 @@ struct Api {
     VerifyTables T;
     T.Tmul = ctx->buf[B_TAB0].as<uint32_t>(); T.Tadd = ctx->buf[B_TAB1].as<uint32_t>(); T.tmp = ctx->buf[B_TAB2].as<uint32_t>();
     T.zpow = ctx->buf[B_TAB3].as<uint32_t>();
+    T.stride_T = T.stride_tmp = T.stride_zpow = T.stride_params = 0;
     uint32_t* xs = ctx->buf[B_TAB4].as<uint32_t>();
-    const size_t cap0 = ctx->buf[B_TAB0].cap + ctx->buf[B_TAB1].cap + ctx->buf[B_TAB2].cap + ctx->buf[B_TAB3].cap;
-    if (!tables_cached(ctx, 1, pk, N, n, m, mode) || cap0 != ctx->tab_caps)
-      BPP_LAUNCH(verify_tables_kernel<M>, 1, VT_THREADS, 0, vs, ctx->buf[B_PARAMS].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
-    ctx->tab_caps = cap0;
     BPP_LAUNCH(verify_proof_scalars_kernel<M>, ceil_div(count, 128), 128, 0, count, d_proofs, proof_len, (size_t)ppp * PB, xs,
                ctx->buf[B_FLAGS2].as<uint8_t>());
+    if (d_challenges) {
+      T.stride_T = K * 8; T.stride_tmp = (N + 64) * 8; T.stride_zpow = (vs.m + 2) * 8; T.stride_params = (P_FIXED + 3 * L) * 8;
+      ctx->tab_gen = 0;  // the shared tables of an earlier call are overwritten
+      BPP_LAUNCH(verify_expand_challenges_kernel<M>, ceil_div(count, 128), 128, 0, count, L, d_challenges, ctx->buf[B_TAB5].as<uint32_t>(),
+                 ctx->buf[B_FLAGS2].as<uint8_t>());
+      BPP_LAUNCH(verify_tables_kernel<M>, count, 128, 0, vs, ctx->buf[B_TAB5].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
+    } else {
+      const size_t cap0 = ctx->buf[B_TAB0].cap + ctx->buf[B_TAB1].cap + ctx->buf[B_TAB2].cap + ctx->buf[B_TAB3].cap;
+      if (!tables_cached(ctx, 1, pk, N, n, m, mode) || cap0 != ctx->tab_caps)
+        BPP_LAUNCH(verify_tables_kernel<M>, 1, VT_THREADS, 0, vs, ctx->buf[B_PARAMS].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
+      ctx->tab_caps = cap0;
+    }
     dim3 grid(ceil_div(K, 256), count);
     BPP_LAUNCH(verify_scalars_kernel<M>, grid, 256, 0, vs, T, xs, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>());
     BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), ppp + vs.nV));
@@ -365,6 +378,34 @@ struct Api {
     BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, V, count * m * PB, cudaMemcpyHostToDevice, ctx->stream));
     BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN2].p, proofs, count * plen, cudaMemcpyHostToDevice, ctx->stream));
     BPP_TRY(range_verify_batch_dev(ctx, pk, n, m, count, ctx->buf[B_IN1].p, ctx->buf[B_IN2].p, prm, ctx->buf[B_IN3].p, order_le));
+    BPP_CK(cudaMemcpyAsync(verdicts, ctx->buf[B_IN3].p, count, cudaMemcpyDeviceToHost, ctx->stream));
+    BPP_CK(cudaStreamSynchronize(ctx->stream));
+    return BPP_OK;
+  }
+
+  // per-proof Fiat-Shamir challenges: challenges = count x (3 + L) scalars [y, z, e_final, e_round[0..L)]
+  static int range_verify_batch_fs_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V, const void* d_proofs,
+                                       const void* d_challenges, void* d_verdicts) {
+    BPP_TRY(check_range_shape(ctx, pk, n, m, count));
+    if (!d_challenges) return BPP_ERR_LENGTH;
+    const size_t plen = (2 * (size_t)ilog2(n * m) + 3) * PB + 96;
+    return verify_core(ctx, pk, m == 1 ? 1 : 2, (uint32_t)n, (uint32_t)m, (uint32_t)count, reinterpret_cast<const uint8_t*>(d_V),
+                       reinterpret_cast<const uint8_t*>(d_proofs), plen, nullptr, nullptr, nullptr, nullptr, nullptr,
+                       reinterpret_cast<uint8_t*>(d_verdicts), reinterpret_cast<const uint8_t*>(d_challenges));
+  }
+  static int range_verify_batch_fs(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint8_t* V, const uint8_t* proofs,
+                                   const uint8_t* challenges, uint8_t* verdicts) {
+    BPP_TRY(check_range_shape(ctx, pk, n, m, count));
+    if (!challenges) return BPP_ERR_LENGTH;
+    const size_t L = ilog2(n * m), plen = (2 * L + 3) * PB + 96, clen = (3 + L) * 32;
+    BPP_CK(ctx->buf[B_IN1].ensure(count * m * PB));
+    BPP_CK(ctx->buf[B_IN2].ensure(count * plen));
+    BPP_CK(ctx->buf[B_IN3].ensure(count));
+    BPP_CK(ctx->buf[B_OUT0].ensure(count * clen));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, V, count * m * PB, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN2].p, proofs, count * plen, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_OUT0].p, challenges, count * clen, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_TRY(range_verify_batch_fs_dev(ctx, pk, n, m, count, ctx->buf[B_IN1].p, ctx->buf[B_IN2].p, ctx->buf[B_OUT0].p, ctx->buf[B_IN3].p));
     BPP_CK(cudaMemcpyAsync(verdicts, ctx->buf[B_IN3].p, count, cudaMemcpyDeviceToHost, ctx->stream));
     BPP_CK(cudaStreamSynchronize(ctx->stream));
     return BPP_OK;
@@ -453,6 +494,135 @@ struct Api {
     if (rc != BPP_OK) return rc;
     BPP_CK(cudaMemcpyAsync(proofs, ctx->buf[B_IN3].p, count * plen, cudaMemcpyDeviceToHost, ctx->stream));
     BPP_CK(cudaStreamSynchronize(ctx->stream));
+    return BPP_OK;
+  }
+
+  // ---- interactive proving for a transcript-owning host (proto_session.cuh) ----------------------------------
+  static FsState session_state(bpp_prove_session* s) {
+    FsState st;
+    st.params = s->params.as<uint32_t>(); st.a = s->a.as<uint32_t>(); st.b = s->b.as<uint32_t>(); st.alpha = s->alpha.as<uint32_t>();
+    st.ypow = s->ypow.as<uint32_t>(); st.gcoef = s->gcoef.as<uint32_t>(); st.hcoef = s->hcoef.as<uint32_t>(); st.rnd = s->rnd.as<uint32_t>();
+    st.PW = (P_FIXED + 3 * s->L) * 8;
+    return st;
+  }
+  static ProveShape session_shape(const bpp_prove_session* s) {
+    ProveShape ps;
+    memset(&ps, 0, sizeof(ps));
+    ps.N = s->N; ps.L = s->L; ps.n = s->n; ps.m = s->m; ps.mode = s->m == 1 ? 1 : 2; ps.n_proofs = s->count;
+    ps.pk_G0 = 2; ps.pk_H0 = 2 + s->N; ps.dyn0 = s->pk->n_points(); ps.has_A = 1;
+    return ps;
+  }
+  // runs the MSM over the terms in B_SCALARS / B_PIDX, encodes `jobs` points per proof into the proofs and into s->out, copies
+  // them to the host and reports a pending FORMAT flag
+  static int session_emit(bpp_ctx* ctx, bpp_prove_session* s, uint32_t n_terms, uint32_t jobs, uint32_t uniform, const uint32_t* d_job_start,
+                          const uint32_t* add_to_job0, uint32_t slot0, uint32_t slot1, uint8_t* host_out) {
+    const size_t plen = (2 * (size_t)s->L + 3) * PB + 96;
+    BPP_TRY(Msm<C>::run(ctx, n_terms, s->count * jobs, uniform, d_job_start, s->pk->wtab, s->pk->n_points(), s->pk->cA, s->pk->WA, nullptr, 0));
+    BPP_CK(s->out.ensure((size_t)s->count * jobs * PB));
+    BPP_LAUNCH(fs_encode_kernel<C>, ceil_div(s->count * jobs, 64), 64, 0, s->count, jobs, ctx->buf[B_RESULTS].as<uint32_t>(), add_to_job0, slot0, slot1,
+               s->proofs.as<uint8_t>(), plen, s->out.as<uint8_t>());
+    BPP_CK(cudaMemcpyAsync(host_out, s->out.p, (size_t)s->count * jobs * PB, cudaMemcpyDeviceToHost, ctx->stream));
+    uint8_t bad = 0;
+    BPP_TRY(read_flag(ctx, s->flag.as<uint8_t>(), &bad));
+    if (bad) { ctx->err = "prove session: a scalar supplied by the caller is not canonical, or a challenge is zero"; return BPP_ERR_FORMAT; }
+    return BPP_OK;
+  }
+  static int prove_begin(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint64_t* v, const uint8_t* gamma,
+                         const uint8_t* nonces, bpp_prove_session** out, uint8_t* out_A) {
+    BPP_TRY(check_range_shape(ctx, pk, n, m, count));
+    const uint32_t N = (uint32_t)(n * m), L = ilog2(N), cnt = (uint32_t)count;
+    if ((uint64_t)count * (2 * N + 4) > (1ull << 27)) { ctx->err = "prove session: batch too large"; return BPP_ERR_LENGTH; }
+    bpp_prove_session* s = new bpp_prove_session();
+    s->curve = C::CURVE_ID; s->pk = pk; s->n = (uint32_t)n; s->m = (uint32_t)m; s->count = cnt; s->N = N; s->L = L;
+    const size_t plen = (2 * (size_t)L + 3) * PB + 96, vec = (size_t)cnt * N * 32;
+    cudaError_t e = s->params.ensure((size_t)cnt * (P_FIXED + 3 * L) * 32);
+    for (DevBuf* d : {&s->a, &s->b, &s->ypow, &s->gcoef, &s->hcoef})
+      if (e == cudaSuccess) e = d->ensure(vec);
+    if (e == cudaSuccess) e = s->alpha.ensure((size_t)cnt * 32);
+    if (e == cudaSuccess) e = s->rnd.ensure((size_t)cnt * 64);
+    if (e == cudaSuccess) e = s->values.ensure((size_t)cnt * m * 8);
+    if (e == cudaSuccess) e = s->gammas.ensure((size_t)cnt * m * 32);
+    if (e == cudaSuccess) e = s->ext.ensure((size_t)cnt * C::EXT_WORDS * 4);
+    if (e == cudaSuccess) e = s->proofs.ensure((size_t)cnt * plen);
+    if (e == cudaSuccess) e = s->flag.ensure(16);
+    if (e == cudaSuccess && nonces) e = s->out.ensure((size_t)cnt * (5 + 2 * L) * 32);
+    auto fail = [&](int rc) { s->release(); delete s; return rc; };
+    if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return fail(BPP_ERR_CUDA); }
+    int rc = [&]() -> int {
+      BPP_CK(cudaMemsetAsync(s->flag.p, 0, 16, ctx->stream));
+      BPP_CK(cudaMemsetAsync(s->proofs.p, 0, (size_t)cnt * plen, ctx->stream));
+      BPP_CK(cudaMemcpyAsync(s->values.p, v, (size_t)cnt * m * 8, cudaMemcpyHostToDevice, ctx->stream));
+      BPP_CK(cudaMemcpyAsync(s->gammas.p, gamma, (size_t)cnt * m * 32, cudaMemcpyHostToDevice, ctx->stream));
+      if (nonces) BPP_CK(cudaMemcpyAsync(s->out.p, nonces, (size_t)cnt * (5 + 2 * L) * 32, cudaMemcpyHostToDevice, ctx->stream));
+      FsState st = session_state(s);
+      ProveShape ps = session_shape(s);
+      BPP_LAUNCH(fs_params_init_kernel<M>, ceil_div(cnt, 128), 128, 0, cnt, L, (uint32_t)(m == 1), nonces ? s->out.as<uint8_t>() : nullptr, st,
+                 s->flag.as<uint8_t>());
+      BPP_CK(ctx->buf[B_SCALARS].ensure((size_t)cnt * 32));
+      BPP_CK(ctx->buf[B_PIDX].ensure((size_t)cnt * 4));
+      BPP_LAUNCH(fs_alpha_terms_kernel<M>, ceil_div(cnt, 128), 128, 0, cnt, st, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>());
+      BPP_LAUNCH(range_bits_sum_kernel<C>, cnt, 128, 0, ps, s->values.as<uint64_t>(), pk->table, s->ext.as<uint32_t>());
+      ctx->tab_gen = 0;
+      return session_emit(ctx, s, cnt, 1, 1, nullptr, s->ext.as<uint32_t>(), 0, 0, out_A);
+    }();
+    if (rc != BPP_OK) return fail(rc);
+    *out = s;
+    return BPP_OK;
+  }
+  // step 0: challenges = count x [y, z]; step k in 1..L: count x e_{k-1}. out: count x [L_k, R_k] (steps < L) or count x [A, B] (step L)
+  static int prove_step(bpp_ctx* ctx, bpp_prove_session* s, const uint8_t* challenges, uint8_t* out_points) {
+    if (s->step > s->L) { ctx->err = "prove session: no step left, call finish"; return BPP_ERR_LENGTH; }
+    const uint32_t k = s->step, cnt = s->count, N = s->N, L = s->L;
+    FsState st = session_state(s);
+    ProveShape ps = session_shape(s);
+    const uint32_t n_ch = k == 0 ? 2 : 1;
+    BPP_CK(ctx->buf[B_IN0].ensure((size_t)cnt * n_ch * 32));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN0].p, challenges, (size_t)cnt * n_ch * 32, cudaMemcpyHostToDevice, ctx->stream));
+    if (k == 0) {
+      BPP_LAUNCH(fs_store_challenges_kernel<M>, ceil_div(cnt, 128), 128, 0, cnt, 2u, (uint32_t)P_Y, (uint32_t)P_Z, 1u, ctx->buf[B_IN0].as<uint8_t>(), st,
+                 s->flag.as<uint8_t>());
+      BPP_LAUNCH(fs_init_kernel<M>, cnt, 256, 0, ps, st, s->values.as<uint64_t>(), s->gammas.as<uint32_t>(), s->flag.as<uint8_t>());
+    } else {
+      BPP_LAUNCH(fs_store_challenges_kernel<M>, ceil_div(cnt, 128), 128, 0, cnt, 1u, (uint32_t)(P_FIXED + k - 1), 0u, 1u,
+                 ctx->buf[B_IN0].as<uint8_t>(), st, s->flag.as<uint8_t>());
+      BPP_LAUNCH(fs_fold_kernel<M>, cnt, 256, 0, ps, st, k - 1);
+    }
+    ctx->tab_gen = 0;
+    int rc;
+    if (k < L) {
+      const uint32_t T = cnt * 2 * (N + 2);
+      BPP_CK(ctx->buf[B_SCALARS].ensure((size_t)T * 32));
+      BPP_CK(ctx->buf[B_PIDX].ensure((size_t)T * 4));
+      BPP_LAUNCH(fs_round_kernel<M>, cnt, 256, 256 * 32, ps, st, k, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>());
+      rc = session_emit(ctx, s, T, 2, N + 2, nullptr, nullptr, 1 + k, 1 + L + k, out_points);
+    } else {
+      const uint32_t T = cnt * (2 * N + 4);
+      BPP_CK(ctx->buf[B_SCALARS].ensure((size_t)T * 32));
+      BPP_CK(ctx->buf[B_PIDX].ensure((size_t)T * 4));
+      BPP_CK(ctx->buf[B_JOBSTART].ensure(((size_t)cnt * 2 + 1) * 4));
+      BPP_LAUNCH(fs_final_points_kernel<M>, cnt, 256, 0, ps, st, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>(),
+                 ctx->buf[B_JOBSTART].as<uint32_t>());
+      rc = session_emit(ctx, s, T, 2, 0, ctx->buf[B_JOBSTART].as<uint32_t>(), nullptr, 1 + 2 * L, 2 + 2 * L, out_points);
+    }
+    if (rc == BPP_OK) s->step++;
+    return rc;
+  }
+  static int prove_finish(bpp_ctx* ctx, bpp_prove_session* s, const uint8_t* e_final, uint8_t* proofs) {
+    if (s->step != s->L + 1) { ctx->err = "prove session: finish comes after step L"; return BPP_ERR_LENGTH; }
+    const uint32_t cnt = s->count;
+    const size_t plen = (2 * (size_t)s->L + 3) * PB + 96;
+    FsState st = session_state(s);
+    ProveShape ps = session_shape(s);
+    BPP_CK(ctx->buf[B_IN0].ensure((size_t)cnt * 32));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN0].p, e_final, (size_t)cnt * 32, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_LAUNCH(fs_store_challenges_kernel<M>, ceil_div(cnt, 128), 128, 0, cnt, 1u, (uint32_t)P_EFINAL, 0u, 1u, ctx->buf[B_IN0].as<uint8_t>(), st,
+               s->flag.as<uint8_t>());
+    BPP_LAUNCH(fs_finish_kernel<M>, ceil_div(cnt, 128), 128, 0, ps, st, s->proofs.as<uint8_t>(), plen, (2 * (size_t)s->L + 3) * PB);
+    BPP_CK(cudaMemcpyAsync(proofs, s->proofs.p, (size_t)cnt * plen, cudaMemcpyDeviceToHost, ctx->stream));
+    uint8_t bad = 0;
+    BPP_TRY(read_flag(ctx, s->flag.as<uint8_t>(), &bad));
+    if (bad) { ctx->err = "prove session: a challenge is zero or not canonical"; return BPP_ERR_FORMAT; }
+    s->step++;
     return BPP_OK;
   }
 

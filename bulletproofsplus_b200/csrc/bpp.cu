@@ -236,6 +236,40 @@ int bpp_range_verify_batch_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t 
   if (!pk) return BPP_ERR_NOT_INIT;
   BPP_DISPATCH(pk->curve, range_verify_batch_dev(ctx, pk, n, m, count, d_V, d_proofs, params, d_verdicts));
 }
+int bpp_range_verify_batch_fs(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint8_t* V, const uint8_t* proofs,
+                              const uint8_t* challenges, uint8_t* verdicts) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, range_verify_batch_fs(ctx, pk, n, m, count, V, proofs, challenges, verdicts));
+}
+int bpp_range_verify_batch_fs_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V, const void* d_proofs,
+                                  const void* d_challenges, void* d_verdicts) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, range_verify_batch_fs_dev(ctx, pk, n, m, count, d_V, d_proofs, d_challenges, d_verdicts));
+}
+int bpp_range_prove_begin(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint64_t* v, const uint8_t* gamma,
+                          const uint8_t* nonces, bpp_prove_session** out, uint8_t* out_A) {
+  BPP_ENTER(ctx);
+  if (!pk || !out) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, prove_begin(ctx, pk, n, m, count, v, gamma, nonces, out, out_A));
+}
+int bpp_range_prove_step(bpp_ctx* ctx, bpp_prove_session* session, const uint8_t* challenges, uint8_t* out_points) {
+  BPP_ENTER(ctx);
+  if (!session) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(session->curve, prove_step(ctx, session, challenges, out_points));
+}
+int bpp_range_prove_finish(bpp_ctx* ctx, bpp_prove_session* session, const uint8_t* e_final, uint8_t* proofs) {
+  BPP_ENTER(ctx);
+  if (!session) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(session->curve, prove_finish(ctx, session, e_final, proofs));
+}
+int bpp_prove_session_rounds(const bpp_prove_session* session) { return session ? (int)session->L : -1; }
+void bpp_prove_session_free(bpp_prove_session* session) {
+  if (!session) return;
+  session->release();
+  delete session;
+}
 int bpp_range_prove(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, const uint64_t* v, const uint8_t* gamma, const bpp_params* params,
                     uint8_t* proof, size_t* proof_len) {
   if (!pk || !proof_len) return BPP_ERR_NOT_INIT;

@@ -23,6 +23,11 @@ struct CurveVtbl {
   int (*range_verify_batch)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const uint8_t*, const uint8_t*, const bpp_params*, uint8_t*);
   int (*range_prove_batch_dev)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const void*, const void*, const bpp_params*, void*);
   int (*range_verify_batch_dev)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const void*, const void*, const bpp_params*, void*);
+  int (*range_verify_batch_fs)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const uint8_t*, const uint8_t*, const uint8_t*, uint8_t*);
+  int (*range_verify_batch_fs_dev)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const void*, const void*, const void*, void*);
+  int (*prove_begin)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const uint64_t*, const uint8_t*, const uint8_t*, bpp_prove_session**, uint8_t*);
+  int (*prove_step)(bpp_ctx*, bpp_prove_session*, const uint8_t*, uint8_t*);
+  int (*prove_finish)(bpp_ctx*, bpp_prove_session*, const uint8_t*, uint8_t*);
   int (*wip_prove)(bpp_ctx*, const bpp_pk*, const uint8_t*, const uint8_t*, const uint8_t*, const uint8_t*, const bpp_params*, uint8_t*, size_t*);
   int (*wip_verify)(bpp_ctx*, const bpp_pk*, const uint8_t*, const uint8_t*, const uint8_t*, const uint8_t*, size_t, const uint8_t*,
                     const uint8_t*, const uint8_t*, const uint8_t*, size_t, const bpp_params*);
@@ -73,6 +78,11 @@ CurveVtbl make_vtbl() {
                                const bpp_params* p, void* o) { return A::range_prove_batch_dev(c, pk, n, m, cnt, vv, g, p, o, ORD::le()); };
   v.range_verify_batch_dev = [](bpp_ctx* c, const bpp_pk* pk, size_t n, size_t m, size_t cnt, const void* V, const void* pr,
                                 const bpp_params* p, void* o) { return A::range_verify_batch_dev(c, pk, n, m, cnt, V, pr, p, o, ORD::le()); };
+  v.range_verify_batch_fs = A::range_verify_batch_fs;
+  v.range_verify_batch_fs_dev = A::range_verify_batch_fs_dev;
+  v.prove_begin = A::prove_begin;
+  v.prove_step = A::prove_step;
+  v.prove_finish = A::prove_finish;
   v.wip_prove = [](bpp_ctx* c, const bpp_pk* pk, const uint8_t* a, const uint8_t* b, const uint8_t* y, const uint8_t* g,
                    const bpp_params* p, uint8_t* o, size_t* l) { return A::wip_prove(c, pk, a, b, y, g, p, o, l, ORD::le()); };
   v.wip_verify = [](bpp_ctx* c, const bpp_pk* pk, const uint8_t* y, const uint8_t* Gc, const uint8_t* Hc, const uint8_t* gc, size_t nV,

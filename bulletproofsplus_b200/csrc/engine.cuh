@@ -10,6 +10,7 @@
 #include "../../include/bpp.h"
 #include "msm.cuh"
 #include "proto_prove.cuh"
+#include "proto_session.cuh"
 
 namespace bpp {
 
@@ -80,6 +81,18 @@ struct bpp_points {
   uint32_t* table = nullptr;  // affine
   uint32_t* wtab = nullptr;   // optional window tables (bpp_points_precompute): wtab[w * len + i] = 2^(cA * w) * table[i]
   uint32_t cA = 0, WA = 0;
+};
+
+// interactive proving (bpp_range_prove_begin / _step / _finish): device state of a batch between the host's challenges
+struct bpp_prove_session {
+  int curve = 0;
+  const bpp_pk* pk = nullptr;
+  uint32_t n = 0, m = 0, count = 0, N = 0, L = 0;
+  uint32_t step = 0;  // next expected: 0..L = bpp_range_prove_step, L + 1 = bpp_range_prove_finish, L + 2 = done
+  bpp::DevBuf params, a, b, alpha, ypow, gcoef, hcoef, rnd, values, gammas, ext, proofs, out, flag;
+  void release() {
+    for (bpp::DevBuf* d : {&params, &a, &b, &alpha, &ypow, &gcoef, &hcoef, &rnd, &values, &gammas, &ext, &proofs, &out, &flag}) d->release();
+  }
 };
 
 namespace bpp {

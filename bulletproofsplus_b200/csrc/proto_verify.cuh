@@ -40,6 +40,9 @@ struct VerifyTables {
   uint32_t* Tadd;   // [K]  canonical
   uint32_t* tmp;    // [N + 64] scratch: s-vector (Montgomery), then small values
   uint32_t* zpow;   // [m + 1] scratch: z^(2(j+1)) (Montgomery)
+  // per-proof challenges (a transcript-owning host): block p of the tables kernel works on proof p's parameter block and its
+  // own table slices; all strides are in 32-bit words and are 0 when one challenge set serves the whole batch
+  uint32_t stride_T, stride_tmp, stride_zpow, stride_params;
 };
 
 template <class M>
@@ -82,6 +85,9 @@ verify_tables_kernel(VerifyShape vs, const uint32_t* __restrict__ params, const 
   typedef Sc<M> S;
   const uint32_t N = vs.N, L = vs.L, tid = threadIdx.x, nt = blockDim.x;
   const uint32_t K0 = 5 + 2 * L;  // first G term
+  params += (size_t)blockIdx.x * T.stride_params;
+  T.Tmul += (size_t)blockIdx.x * T.stride_T; T.Tadd += (size_t)blockIdx.x * T.stride_T;
+  T.tmp += (size_t)blockIdx.x * T.stride_tmp; T.zpow += (size_t)blockIdx.x * T.stride_zpow;
   // shared: inverses of e_0..e_{L-1}, y, e  (slots 0..L+1), scratch for the batch inversion, and a few broadcast values
   __shared__ uint32_t sh_inv[34 * 8];
   __shared__ uint32_t sh_scr[34 * 8];
@@ -191,6 +197,36 @@ verify_tables_kernel(VerifyShape vs, const uint32_t* __restrict__ params, const 
   }
 }
 
+// Per-proof challenges: thread per proof expands the caller's compact block [y, z, e_final, e_round[0..L)] into the packed
+// parameter layout the tables kernel reads. A non-canonical or zero challenge (not invertible) marks the proof FORMAT and is
+// replaced by 1 so that the arithmetic stays defined.
+template <class M>
+__global__ void verify_expand_challenges_kernel(uint32_t n_proofs, uint32_t L, const uint8_t* __restrict__ challenges,
+                                                uint32_t* __restrict__ params_all, uint8_t* __restrict__ bad) {
+  typedef Sc<M> S;
+  uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_proofs) return;
+  const uint8_t* src = challenges + (size_t)p * (3 + L) * 32;
+  uint32_t* dst = params_all + (size_t)p * (P_FIXED + 3 * L) * 8;
+  bool any_bad = false;
+  for (uint32_t j = 0; j < 3 + L; j++) {
+    uint32_t w[8], nz = 0;
+    for (int i = 0; i < 8; i++) {
+      const uint8_t* q = src + 32 * j + 4 * i;
+      w[i] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+      nz |= w[i];
+    }
+    const bool must_invert = j != 1;  // y, e_final, e_k are inverted; z is not
+    if (!S::canonical_ok(w) || (must_invert && !nz)) {
+      any_bad = true;
+      for (int i = 0; i < 8; i++) w[i] = i == 0;
+    }
+    const uint32_t slot = j == 0 ? P_Y : j == 1 ? P_Z : j == 2 ? P_EFINAL : P_FIXED + (j - 3);
+    for (int i = 0; i < 8; i++) dst[8 * slot + i] = w[i];
+  }
+  if (any_bad) bad[p] = 1;
+}
+
 // thread per proof: parse and check (r', s', delta'); per-proof scalars x = [r', s', delta', r'*s'] (canonical) -> xs[p][4][8]
 // proofs: wire layout A | L[L] | R[L] | wipA | wipB | r' | s' | d'   (include/bpp.h)
 template <class M>
@@ -236,6 +272,7 @@ __global__ void verify_scalars_kernel(VerifyShape vs, VerifyTables T, const uint
   if (k >= K) return;
   const uint32_t dyn = vs.dyn0 + p * (2 * L + 3);  // this proof's decoded points: A, L.., R.., wipA, wipB
   const uint32_t* x = xs + (size_t)p * 32;
+  T.Tadd += (size_t)p * T.stride_T; T.Tmul += (size_t)p * T.stride_T;
   S val = S::raw(T.Tadd + 8 * k);
   uint32_t idx;
   if (k == 0) idx = dyn + 2 * L + 2;                                                   // wipB

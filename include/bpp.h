@@ -28,6 +28,7 @@ extern "C" {
 typedef struct bpp_ctx bpp_ctx;       /* one per host thread / GPU: stream + scratch arena. Not thread-safe.     */
 typedef struct bpp_pk bpp_pk;         /* PublicKey (publickey.rs:13-18): device-resident generator table         */
 typedef struct bpp_points bpp_points; /* a decoded, device-resident point vector for repeated MSMs               */
+typedef struct bpp_prove_session bpp_prove_session; /* device state of an interactive batch prove (host-owned transcript) */
 
 enum { BPP_RISTRETTO255 = 0, BPP_SECP256K1 = 1, BPP_BLS12_381_G1 = 2 };
 
@@ -123,6 +124,32 @@ int bpp_range_prove(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, const ui
                     const bpp_params* params, uint8_t* proof, size_t* proof_len);
 int bpp_range_verify(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, const uint8_t* V, const uint8_t* proof,
                      size_t proof_len, const bpp_params* params);
+
+/* ---- real Fiat-Shamir: the host owns the transcript (task statement; the snapshot hard-codes every challenge) ---- */
+/* Batch verification with PER-PROOF challenges: challenges = count blocks of (3 + L) scalars [y, z, e, e_round[0..L)],
+ * L = log2(n*m), which the host derives from each proof's own transcript (A -> y, z; L_k, R_k -> e_k; wip A, B -> e). A zero
+ * or non-canonical challenge gives that proof the verdict BPP_ERR_FORMAT. Same checks, same MSM as bpp_range_verify_batch;
+ * with every block set to the reference's constants the verdicts are identical to it. */
+int bpp_range_verify_batch_fs(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint8_t* V,
+                              const uint8_t* proofs, const uint8_t* challenges, uint8_t* verdicts);
+int bpp_range_verify_batch_fs_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V,
+                                  const void* d_proofs, const void* d_challenges, void* d_verdicts);
+/* Interactive proving of a batch, cut where the challenges enter (range/mod.rs:31-55 and wip.rs:36-226 with the constants
+ * replaced by the host's answers). All scalars 32-byte canonical; every array is per proof, in batch order.
+ *   begin      nonces = NULL (the reference's constants) or count x (5 + 2L) scalars [alpha, r, s, delta, eta, d_L[L], d_R[L]];
+ *              writes A (count points): the host absorbs it and answers (y, z)
+ *   step 0     challenges = count x [y, z]        -> out_points = count x [L_0, R_0]
+ *   step k     challenges = count x e_{k-1}       -> out_points = count x [L_k, R_k]      (k = 1 .. L-1)
+ *   step L     challenges = count x e_{L-1}       -> out_points = count x [wip A, wip B]
+ *   finish     e_final    = count x e             -> proofs = count complete proofs (wire layout above)
+ * Calls must come in this order (BPP_ERR_LENGTH otherwise); a zero / non-canonical challenge or nonce is BPP_ERR_FORMAT.
+ * The session holds device memory until bpp_prove_session_free; `pk` must outlive it. */
+int bpp_range_prove_begin(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint64_t* v, const uint8_t* gamma,
+                          const uint8_t* nonces, bpp_prove_session** out, uint8_t* out_A);
+int bpp_range_prove_step(bpp_ctx* ctx, bpp_prove_session* session, const uint8_t* challenges, uint8_t* out_points);
+int bpp_range_prove_finish(bpp_ctx* ctx, bpp_prove_session* session, const uint8_t* e_final, uint8_t* proofs);
+int bpp_prove_session_rounds(const bpp_prove_session* session); /* L */
+void bpp_prove_session_free(bpp_prove_session* session);
 
 /* ---- WeightedInnerProductProof::prove / verify (weighted_inner_product_proof.rs:36-43, :238-248) -- */
 /* a, b, power_of_y: len scalars each (len = bpp_pk_len(pk)); gamma: one scalar. The reference's `commitment`

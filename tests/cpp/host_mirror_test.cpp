@@ -6,6 +6,7 @@
 #include <functional>
 
 #include "bpp.hpp"
+#include "bpp_merlin.hpp"
 
 using namespace bulletproofsplus;
 
@@ -114,6 +115,31 @@ int main(int argc, char** argv) {
     report("wip verify, wrong P == Err", w.verify(pk, ypow, zeros, zeros, fe(0), {}, pk.g(), {}) == Result::Err(ProofError::VerificationError));
     a.pop_back();
     report("wip length mismatch panics (wip.rs:61-64)", panics([&] { WeightedInnerProductProof::prove(pk, a, b, ypow, fe(gamma)); }));
+  }
+  // host-owned Fiat-Shamir: Merlin's published value, then the README flow with transcripts (README.md:39-52)
+  {
+    merlin::Transcript t("test protocol");
+    t.append_message("some label", std::string("some data"));
+    uint8_t c[32];
+    t.challenge_bytes("challenge", c, 32);
+    static const char* want = "d5a21972d0d5fe320c0d263fac7fffb8145aa640af6e9bca177c03c7efcf0615";
+    char got[65];
+    for (int i = 0; i < 32; i++) snprintf(got + 2 * i, 3, "%02x", c[i]);
+    report("merlin equivalence_simple value", std::string(got) == want);
+    const size_t n = 32, m = 4;
+    PublicKey pk = PublicKey::new_(n * m, curve);
+    RangeProver prover = RangeProver::new_();
+    for (size_t j = 0; j < m; j++) prover.commit(pk, 31 + j, fe(11 + (int)j));
+    RangeProof proof = prove_with_transcript(pk, n, prover, merlin::Transcript("RangeProof Test"));
+    hex("transcript_proof_n32_m4", proof.to_bytes());
+    report("transcript verify == Ok(())", verify_with_transcript(proof, pk, n, prover.commitment_vec, merlin::Transcript("RangeProof Test")) == Result::Ok());
+    report("other transcript label == Err(VerificationError)",
+           verify_with_transcript(proof, pk, n, prover.commitment_vec, merlin::Transcript("RangeProof Test 2")) == Result::Err(ProofError::VerificationError));
+    report("transcript proof under the fixed constants == Err", proof.verify(pk, n, prover.commitment_vec) == Result::Err(ProofError::VerificationError));
+    RangeProof t2 = proof;
+    t2.proof.R_vec[1] = pk.h();
+    report("tampered transcript proof == Err(VerificationError)",
+           verify_with_transcript(t2, pk, n, prover.commitment_vec, merlin::Transcript("RangeProof Test")) == Result::Err(ProofError::VerificationError));
   }
   printf("%s\n", failures ? "SOME FAILED" : "ALL PASSED");
   return failures ? 1 : 0;
