@@ -311,7 +311,9 @@ def main():
         pass
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     roofline = {
-        "bound": "int32-imad (no tensor/HBM bound applies: ~20k multiply-adds per 128 B term)", "kernel": "msm_accumulate_kernel<Ed25519> (+ its two long-bucket variants msm_accumulate_group_kernel<.,32|4>, timed together)",
+        "bound": "int-imad", "bound_note": "integer multiply pipe: ~20k multiply-adds per 128 B term, so neither the HBM nor the tensor roofline "
+                                               "applies (north_star asks for the integer-multiply roofline); HBM figures are in `hbm` below",
+        "kernel": "msm_accumulate_kernel<Ed25519> (+ its two long-bucket variants msm_accumulate_group_kernel<.,32|4>, timed together)",
         "achieved": ach_kernel / 1e12 if ach_kernel else None, "peak": int_peak / 1e12, "unit": "T 32x32+64 multiply-adds/s",
         "frac": (ach_kernel / int_peak) if ach_kernel else None, "traffic": None,
         "peak_source": "bpp_int_peak_probe: 32-bit IMAD chains with loop-produced operands on all SMs, measured in this run — the "
@@ -437,6 +439,78 @@ def run_extras(args, torch, api, _lib, ctx, pk, dev, stream, int_peak):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
     out["proves_per_sec_n64_m16"] = {"value": PB / (ms * 1e-3), "unit": "proofs/s", "batch": PB, "ms_per_batch": ms}
+    # real Fiat-Shamir, GPU side: per-proof challenges on the verifier, the interactive prover (12 host round trips per batch).
+    # The challenges are the constants, so the transcript hashing of the host (merlin.py is pure Python) is not in these numbers.
+    import ctypes as C
+    B = args.batch
+    vs2, gs2 = synth_inputs(B, seed=7)
+    proofs = []
+    for c0 in range(0, B, 256):
+        c1 = min(B, c0 + 256)
+        proofs += api.prove_batch(pk, N_BITS, M_AGG, vs2[c0 * M_AGG:c1 * M_AGG], gs2[c0 * M_AGG:c1 * M_AGG])
+    d_pr = torch.frombuffer(bytearray(b"".join(proofs)), dtype=torch.uint8).to(dev)
+    d_V = torch.frombuffer(bytearray(b"".join(pk.commit_batch(vs2, gs2))), dtype=torch.uint8).to(dev)
+    L = 10
+    block = b"".join(int(x).to_bytes(32, "little") for x in [12, 23, 99] + [7] * L)
+    d_ch = torch.frombuffer(bytearray(block * B), dtype=torch.uint8).to(dev)
+    d_vd = torch.full((B,), 255, dtype=torch.uint8, device=dev)
+
+    def verify_fs():
+        ctx.check(lib.bpp_range_verify_batch_fs_dev(ctx.h, pk.handle, N_BITS, M_AGG, B, d_V.data_ptr(), d_pr.data_ptr(), d_ch.data_ptr(), d_vd.data_ptr()),
+                  "verify_fs")
+
+    for _ in range(2):
+        verify_fs()
+    torch.cuda.synchronize()
+    assert bool((d_vd == 0).all())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(reps):
+        verify_fs()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    out["verifies_per_sec_per_proof_challenges"] = {"value": B / (ms * 1e-3), "unit": "proofs/s", "batch": B, "ms_per_batch": ms,
+                                                    "entry": "bpp_range_verify_batch_fs_dev"}
+
+    # random-linear-combination batch verification: same proofs, one combined MSM per batch (fallback to per-proof on failure)
+    import secrets
+    d_w = torch.frombuffer(bytearray(b"".join((secrets.randbits(128) | 1).to_bytes(32, "little") for _ in range(B))), dtype=torch.uint8).to(dev)
+    fb = C.c_int(0)
+
+    def verify_rlc():
+        ctx.check(lib.bpp_range_verify_batch_rlc_dev(ctx.h, pk.handle, N_BITS, M_AGG, B, d_V.data_ptr(), d_pr.data_ptr(), None, None, d_w.data_ptr(),
+                                                     d_vd.data_ptr(), C.byref(fb)), "verify_rlc")
+
+    for _ in range(2):
+        verify_rlc()
+    torch.cuda.synchronize()
+    assert bool((d_vd == 0).all()) and fb.value == 0
+    e0.record(stream)
+    for _ in range(reps):
+        verify_rlc()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    out["verifies_per_sec_rlc_batch"] = {"value": B / (ms * 1e-3), "unit": "proofs/s", "batch": B, "ms_per_batch": ms,
+                                         "entry": "bpp_range_verify_batch_rlc_dev (all proofs valid: no fallback; one host sync per batch inside)"}
+
+    def prove_fs():
+        ses = api.ProveSession(pk, N_BITS, M_AGG, vs[:PB * M_AGG], gs[:PB * M_AGG])
+        ch = [(12, 23)] * PB
+        for _ in range(ses.rounds + 1):
+            ses.step(ch)
+            ch = [7] * PB
+        return ses.finish([99] * PB)
+
+    prove_fs()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        got = prove_fs()
+    dt = (time.perf_counter() - t0) / 3
+    out["proves_per_sec_interactive"] = {"value": PB / dt, "unit": "proofs/s", "batch": PB, "ms_per_batch": dt * 1e3, "host_round_trips": 12,
+                                         "entry": "bpp_range_prove_begin/_step/_finish (host wall clock, host buffers)"}
     # MSM sweep, all three curves (field multiply = 72 IMAD for 2^255-19 and the secp256k1 prime, 300 for
     # BLS12-381; Edwards mixed/full/double = 7/8/8, short Weierstrass 11/16/7 field multiplies)
     curves = (("", _lib.RISTRETTO255, args.msm_max_log, 253, 72, (7, 8, 8)),

@@ -20,7 +20,7 @@ SYMBOLS = [
     "bpp_points_upload", "bpp_points_from_multipliers", "bpp_points_len", "bpp_points_precompute", "bpp_points_free", "bpp_msm_prepared",
     "bpp_msm_prepared_dev", "bpp_raw_point_bytes", "bpp_msm_prepared_raw", "bpp_points_sum_raw", "bpp_msm_prepared_raw_dev", "bpp_points_sum_raw_dev", "bpp_range_prove_batch",
     "bpp_range_verify_batch", "bpp_range_prove_batch_dev", "bpp_range_verify_batch_dev", "bpp_range_prove", "bpp_range_verify",
-    "bpp_wip_prove", "bpp_wip_verify", "bpp_range_verify_batch_fs", "bpp_range_verify_batch_fs_dev", "bpp_range_prove_begin", "bpp_range_prove_step",
+    "bpp_wip_prove", "bpp_wip_verify", "bpp_range_verify_batch_fs", "bpp_range_verify_batch_rlc", "bpp_range_verify_batch_rlc_dev", "bpp_range_verify_batch_fs_dev", "bpp_range_prove_begin", "bpp_range_prove_step",
     "bpp_range_prove_finish", "bpp_prove_session_rounds", "bpp_prove_session_free", "bpp_int_peak_probe", "bpp_fe_mul_probe", "bpp_hot_kernel_stats", "bpp_debug_op",
 ]
 
@@ -88,6 +88,8 @@ def load() -> C.CDLL:
     L.bpp_wip_verify.argtypes = [vp, vp, u8p, u8p, u8p, u8p, sz, u8p, u8p, u8p, u8p, sz, pp]
     L.bpp_range_verify_batch_fs.argtypes = [vp, vp, sz, sz, sz, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p]
     L.bpp_range_verify_batch_fs_dev.argtypes = [vp, vp, sz, sz, sz, vp, vp, vp, vp]
+    L.bpp_range_verify_batch_rlc.argtypes = [vp, vp, sz, sz, sz, C.c_char_p, C.c_char_p, pp, C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_int)]
+    L.bpp_range_verify_batch_rlc_dev.argtypes = [vp, vp, sz, sz, sz, vp, vp, pp, vp, vp, vp, C.POINTER(C.c_int)]
     L.bpp_range_prove_begin.argtypes = [vp, vp, sz, sz, sz, C.POINTER(C.c_uint64), C.c_char_p, C.c_char_p, C.POINTER(vp), C.c_char_p]
     L.bpp_range_prove_step.argtypes = [vp, vp, C.c_char_p, C.c_char_p]
     L.bpp_range_prove_finish.argtypes = [vp, vp, C.c_char_p, C.c_char_p]

@@ -351,6 +351,25 @@ def verify_batch_fs(pk: PublicKey, n: int, m: int, proofs, commitments, transcri
     return list(out.raw[:count])
 
 
+def verify_batch_rlc(pk: PublicKey, n: int, m: int, proofs, commitments, params: BppParams | None = None, challenges=None, weights=None):
+    """Random-linear-combination batch verification: (verdict per proof, used_fallback). weights default to 128 fresh random bits each."""
+    import secrets
+    _shape_asserts(pk, n, m)
+    count = len(proofs)
+    plen = pk.ctx.lib.bpp_range_proof_len(pk.curve, n, m)
+    if any(len(p) != plen for p in proofs):
+        raise FormatError("wrong proof length")
+    if weights is None:
+        weights = [secrets.randbits(128) | 1 for _ in range(count)]
+    out = C.create_string_buffer(max(1, count))
+    fb = C.c_int(0)
+    V = b"".join(b"".join(c) for c in commitments)
+    blob = b"".join(b"".join(_sc(x) for x in ch) for ch in challenges) if challenges is not None else None
+    pk.ctx.check(pk.ctx.lib.bpp_range_verify_batch_rlc(pk.ctx.h, pk.handle, n, m, count, V, b"".join(proofs), params, blob,
+                                                       b"".join(_sc(w) for w in weights), out, C.byref(fb)), "range_verify_batch_rlc")
+    return list(out.raw[:count]), bool(fb.value)
+
+
 class MulVec:
     """bls12_381/building_block/mulvec.rs:13-53 — accumulate (scalar, point) pairs, calculate() = sum s_i * P_i."""
 

@@ -295,7 +295,7 @@ struct Api {
   static int verify_core(bpp_ctx* ctx, const bpp_pk* pk, uint32_t mode, uint32_t n, uint32_t m, uint32_t count, const uint8_t* d_V,
                          const uint8_t* d_proofs, size_t proof_len, const uint32_t* ext_Gc, const uint32_t* ext_Hc,
                          const uint32_t* ext_gc, const uint32_t* ext_Vc, const uint32_t* ext_y, uint8_t* d_verdicts,
-                         const uint8_t* d_challenges = nullptr) {
+                         const uint8_t* d_challenges = nullptr, const uint8_t* d_weights = nullptr, uint8_t* rlc_pass = nullptr) {
     VerifyShape vs;
     vs.N = (uint32_t)pk->len; vs.L = ilog2(vs.N); vs.n = n; vs.m = m; vs.nV = m; vs.mode = mode; vs.n_proofs = count;
     vs.pk_G0 = 2; vs.pk_H0 = 2 + vs.N; vs.dyn0 = pk->n_points();
@@ -345,6 +345,36 @@ struct Api {
     }
     dim3 grid(ceil_div(K, 256), count);
     BPP_LAUNCH(verify_scalars_kernel<M>, grid, 256, 0, vs, T, xs, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>());
+    if (d_weights) {
+      // random linear combination: one MSM of 2 + 2N + count * (ppp + nV) terms for the whole batch
+      const uint32_t per = ppp + vs.nV, T2 = 2 + 2 * N + count * per;
+      BPP_CK(ctx->buf[B_WORK0].ensure((size_t)T2 * 32));
+      BPP_CK(ctx->buf[B_WORK1].ensure((size_t)T2 * 4));
+      BPP_CK(ctx->buf[B_WORK2].ensure((size_t)count * 32));
+      BPP_CK(ctx->buf[B_IN0].ensure((size_t)count * ppp * PB > count ? (size_t)count * ppp * PB : count));
+      BPP_CK(ctx->buf[B_FLAGS].ensure(16));
+      BPP_CK(cudaMemsetAsync(ctx->buf[B_FLAGS].p, 0, 16, ctx->stream));
+      uint32_t* w_eff = ctx->buf[B_WORK2].as<uint32_t>();
+      uint8_t* fmt = ctx->buf[B_IN0].as<uint8_t>();  // the gathered proof bytes are no longer needed
+      uint8_t* flags = ctx->buf[B_FLAGS].as<uint8_t>();
+      BPP_LAUNCH(rlc_weights_kernel<M>, ceil_div(count, 128), 128, 0, count, ppp, vs.nV, d_weights, ctx->buf[B_DYN_OK].as<uint8_t>(),
+                 ctx->buf[B_FLAGS2].as<uint8_t>(), w_eff, fmt, flags + 1);
+      BPP_LAUNCH(rlc_fold_fixed_kernel<M>, ceil_div(2 + 2 * N, 64), 64, 0, vs, w_eff, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_WORK0].as<uint32_t>(),
+                 ctx->buf[B_WORK1].as<uint32_t>());
+      BPP_LAUNCH(rlc_scale_dyn_kernel<M>, ceil_div(count * per, 256), 256, 0, vs, w_eff, ctx->buf[B_SCALARS].as<uint32_t>(),
+                 ctx->buf[B_PIDX].as<uint32_t>(), ctx->buf[B_WORK0].as<uint32_t>(), ctx->buf[B_WORK1].as<uint32_t>());
+      BPP_CK(cudaMemcpyAsync(ctx->buf[B_SCALARS].p, ctx->buf[B_WORK0].p, (size_t)T2 * 32, cudaMemcpyDeviceToDevice, ctx->stream));
+      BPP_CK(cudaMemcpyAsync(ctx->buf[B_PIDX].p, ctx->buf[B_WORK1].p, (size_t)T2 * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+      BPP_TRY(Msm<C>::run(ctx, T2, 1, T2, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), count * per));
+      BPP_LAUNCH(rlc_verdict_kernel<C>, ceil_div(count, 256) < 64 ? ceil_div(count, 256) : 64, 256, 0, count, ctx->buf[B_RESULTS].as<uint32_t>(), fmt,
+                 d_verdicts, flags);
+      uint8_t res[2] = {0, 0};
+      BPP_CK(cudaMemcpyAsync(res, flags, 2, cudaMemcpyDeviceToHost, ctx->stream));
+      BPP_CK(cudaStreamSynchronize(ctx->stream));
+      if (res[1]) { ctx->err = "rlc verify: a weight is zero or not canonical"; return BPP_ERR_FORMAT; }
+      *rlc_pass = res[0];
+      return BPP_OK;
+    }
     BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), ppp + vs.nV));
     BPP_LAUNCH(verdict_kernel<C>, ceil_div(count, 128), 128, 0, count, ppp, vs.nV, ctx->buf[B_RESULTS].as<uint32_t>(),
                ctx->buf[B_DYN_OK].as<uint8_t>(), ctx->buf[B_FLAGS2].as<uint8_t>(), d_verdicts);
@@ -406,6 +436,51 @@ struct Api {
     BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN2].p, proofs, count * plen, cudaMemcpyHostToDevice, ctx->stream));
     BPP_CK(cudaMemcpyAsync(ctx->buf[B_OUT0].p, challenges, count * clen, cudaMemcpyHostToDevice, ctx->stream));
     BPP_TRY(range_verify_batch_fs_dev(ctx, pk, n, m, count, ctx->buf[B_IN1].p, ctx->buf[B_IN2].p, ctx->buf[B_OUT0].p, ctx->buf[B_IN3].p));
+    BPP_CK(cudaMemcpyAsync(verdicts, ctx->buf[B_IN3].p, count, cudaMemcpyDeviceToHost, ctx->stream));
+    BPP_CK(cudaStreamSynchronize(ctx->stream));
+    return BPP_OK;
+  }
+
+  // Random-linear-combination batch verification. weights: count canonical non-zero scalars the prover could not predict (the
+  // host's CSPRNG). challenges: NULL (one challenge set from `prm`) or per-proof blocks as in range_verify_batch_fs. Verdicts are
+  // the per-proof ones: when the combined check fails the batch is re-verified proof by proof. Synchronises the stream.
+  static int range_verify_batch_rlc_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V, const void* d_proofs,
+                                        const bpp_params* prm, const void* d_challenges, const void* d_weights, void* d_verdicts,
+                                        const uint8_t* order_le, int* used_fallback) {
+    BPP_TRY(check_range_shape(ctx, pk, n, m, count));
+    if (!d_weights) return BPP_ERR_LENGTH;
+    const uint32_t L = ilog2(n * m);
+    if (!d_challenges) BPP_TRY(load_params(ctx, prm, m == 1, L, order_le));
+    const size_t plen = (2 * (size_t)L + 3) * PB + 96;
+    uint8_t pass = 0;
+    BPP_TRY(verify_core(ctx, pk, m == 1 ? 1 : 2, (uint32_t)n, (uint32_t)m, (uint32_t)count, reinterpret_cast<const uint8_t*>(d_V),
+                        reinterpret_cast<const uint8_t*>(d_proofs), plen, nullptr, nullptr, nullptr, nullptr, nullptr,
+                        reinterpret_cast<uint8_t*>(d_verdicts), reinterpret_cast<const uint8_t*>(d_challenges),
+                        reinterpret_cast<const uint8_t*>(d_weights), &pass));
+    if (used_fallback) *used_fallback = pass ? 0 : 1;
+    if (pass) return BPP_OK;
+    return verify_core(ctx, pk, m == 1 ? 1 : 2, (uint32_t)n, (uint32_t)m, (uint32_t)count, reinterpret_cast<const uint8_t*>(d_V),
+                       reinterpret_cast<const uint8_t*>(d_proofs), plen, nullptr, nullptr, nullptr, nullptr, nullptr,
+                       reinterpret_cast<uint8_t*>(d_verdicts), reinterpret_cast<const uint8_t*>(d_challenges));
+  }
+  static int range_verify_batch_rlc(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint8_t* V, const uint8_t* proofs,
+                                    const bpp_params* prm, const uint8_t* challenges, const uint8_t* weights, uint8_t* verdicts,
+                                    const uint8_t* order_le, int* used_fallback) {
+    BPP_TRY(check_range_shape(ctx, pk, n, m, count));
+    if (!weights) return BPP_ERR_LENGTH;
+    const size_t L = ilog2(n * m), plen = (2 * L + 3) * PB + 96, clen = (3 + L) * 32;
+    BPP_CK(ctx->buf[B_IN1].ensure(count * m * PB));
+    BPP_CK(ctx->buf[B_IN2].ensure(count * plen));
+    BPP_CK(ctx->buf[B_IN3].ensure(count));
+    BPP_CK(ctx->buf[B_OUT0].ensure(count * (clen + 32)));
+    uint8_t* d_w = ctx->buf[B_OUT0].as<uint8_t>();
+    uint8_t* d_c = d_w + count * 32;
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, V, count * m * PB, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN2].p, proofs, count * plen, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_CK(cudaMemcpyAsync(d_w, weights, count * 32, cudaMemcpyHostToDevice, ctx->stream));
+    if (challenges) BPP_CK(cudaMemcpyAsync(d_c, challenges, count * clen, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_TRY(range_verify_batch_rlc_dev(ctx, pk, n, m, count, ctx->buf[B_IN1].p, ctx->buf[B_IN2].p, prm, challenges ? d_c : nullptr, d_w,
+                                       ctx->buf[B_IN3].p, order_le, used_fallback));
     BPP_CK(cudaMemcpyAsync(verdicts, ctx->buf[B_IN3].p, count, cudaMemcpyDeviceToHost, ctx->stream));
     BPP_CK(cudaStreamSynchronize(ctx->stream));
     return BPP_OK;
@@ -532,7 +607,17 @@ struct Api {
     BPP_TRY(check_range_shape(ctx, pk, n, m, count));
     const uint32_t N = (uint32_t)(n * m), L = ilog2(N), cnt = (uint32_t)count;
     if ((uint64_t)count * (2 * N + 4) > (1ull << 27)) { ctx->err = "prove session: batch too large"; return BPP_ERR_LENGTH; }
-    bpp_prove_session* s = new bpp_prove_session();
+    bpp_prove_session* s = nullptr;
+    for (size_t i = 0; i < ctx->session_pool.size(); i++) {
+      bpp_prove_session* c = ctx->session_pool[i];
+      if (c->curve == C::CURVE_ID && c->n == n && c->m == m && c->count == cnt) {
+        s = c;
+        ctx->session_pool.erase(ctx->session_pool.begin() + i);
+        break;
+      }
+    }
+    if (!s) s = new bpp_prove_session();
+    s->owner = ctx; s->step = 0;
     s->curve = C::CURVE_ID; s->pk = pk; s->n = (uint32_t)n; s->m = (uint32_t)m; s->count = cnt; s->N = N; s->L = L;
     const size_t plen = (2 * (size_t)L + 3) * PB + 96, vec = (size_t)cnt * N * 32;
     cudaError_t e = s->params.ensure((size_t)cnt * (P_FIXED + 3 * L) * 32);

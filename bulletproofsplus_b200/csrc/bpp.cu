@@ -107,6 +107,8 @@ void bpp_destroy(bpp_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   drain_hot(ctx);
+  for (bpp_prove_session* ps : ctx->session_pool) { ps->release(); delete ps; }
+  ctx->session_pool.clear();
   for (auto& b : ctx->buf) b.release();
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -248,6 +250,19 @@ int bpp_range_verify_batch_fs_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size
   if (!pk) return BPP_ERR_NOT_INIT;
   BPP_DISPATCH(pk->curve, range_verify_batch_fs_dev(ctx, pk, n, m, count, d_V, d_proofs, d_challenges, d_verdicts));
 }
+int bpp_range_verify_batch_rlc(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint8_t* V, const uint8_t* proofs,
+                               const bpp_params* params, const uint8_t* challenges, const uint8_t* weights, uint8_t* verdicts, int* used_fallback) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, range_verify_batch_rlc(ctx, pk, n, m, count, V, proofs, params, challenges, weights, verdicts, used_fallback));
+}
+int bpp_range_verify_batch_rlc_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V, const void* d_proofs,
+                                   const bpp_params* params, const void* d_challenges, const void* d_weights, void* d_verdicts,
+                                   int* used_fallback) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, range_verify_batch_rlc_dev(ctx, pk, n, m, count, d_V, d_proofs, params, d_challenges, d_weights, d_verdicts, used_fallback));
+}
 int bpp_range_prove_begin(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint64_t* v, const uint8_t* gamma,
                           const uint8_t* nonces, bpp_prove_session** out, uint8_t* out_A) {
   BPP_ENTER(ctx);
@@ -267,6 +282,10 @@ int bpp_range_prove_finish(bpp_ctx* ctx, bpp_prove_session* session, const uint8
 int bpp_prove_session_rounds(const bpp_prove_session* session) { return session ? (int)session->L : -1; }
 void bpp_prove_session_free(bpp_prove_session* session) {
   if (!session) return;
+  if (session->owner && session->owner->session_pool.size() < 2) {
+    session->owner->session_pool.push_back(session);  // keeps its device memory for the next batch of the same shape
+    return;
+  }
   session->release();
   delete session;
 }

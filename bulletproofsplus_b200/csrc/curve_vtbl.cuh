@@ -25,6 +25,10 @@ struct CurveVtbl {
   int (*range_verify_batch_dev)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const void*, const void*, const bpp_params*, void*);
   int (*range_verify_batch_fs)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const uint8_t*, const uint8_t*, const uint8_t*, uint8_t*);
   int (*range_verify_batch_fs_dev)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const void*, const void*, const void*, void*);
+  int (*range_verify_batch_rlc)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const uint8_t*, const uint8_t*, const bpp_params*, const uint8_t*,
+                                const uint8_t*, uint8_t*, int*);
+  int (*range_verify_batch_rlc_dev)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const void*, const void*, const bpp_params*, const void*,
+                                    const void*, void*, int*);
   int (*prove_begin)(bpp_ctx*, const bpp_pk*, size_t, size_t, size_t, const uint64_t*, const uint8_t*, const uint8_t*, bpp_prove_session**, uint8_t*);
   int (*prove_step)(bpp_ctx*, bpp_prove_session*, const uint8_t*, uint8_t*);
   int (*prove_finish)(bpp_ctx*, bpp_prove_session*, const uint8_t*, uint8_t*);
@@ -80,6 +84,14 @@ CurveVtbl make_vtbl() {
                                 const bpp_params* p, void* o) { return A::range_verify_batch_dev(c, pk, n, m, cnt, V, pr, p, o, ORD::le()); };
   v.range_verify_batch_fs = A::range_verify_batch_fs;
   v.range_verify_batch_fs_dev = A::range_verify_batch_fs_dev;
+  v.range_verify_batch_rlc = [](bpp_ctx* c, const bpp_pk* pk, size_t n, size_t m, size_t cnt, const uint8_t* V, const uint8_t* pr, const bpp_params* p,
+                                const uint8_t* ch, const uint8_t* w, uint8_t* o, int* fb) {
+    return A::range_verify_batch_rlc(c, pk, n, m, cnt, V, pr, p, ch, w, o, ORD::le(), fb);
+  };
+  v.range_verify_batch_rlc_dev = [](bpp_ctx* c, const bpp_pk* pk, size_t n, size_t m, size_t cnt, const void* V, const void* pr, const bpp_params* p,
+                                    const void* ch, const void* w, void* o, int* fb) {
+    return A::range_verify_batch_rlc_dev(c, pk, n, m, cnt, V, pr, p, ch, w, o, ORD::le(), fb);
+  };
   v.prove_begin = A::prove_begin;
   v.prove_step = A::prove_step;
   v.prove_finish = A::prove_finish;

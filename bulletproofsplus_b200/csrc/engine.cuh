@@ -61,6 +61,7 @@ struct bpp_ctx {
   uint32_t tab_kind = 0;     // 1 verifier tables, 2 prover tables
   uint32_t tab_shape[5] = {0, 0, 0, 0, 0};  // N, n, m, mode, curve
   const void* tab_pk = nullptr;
+  std::vector<struct bpp_prove_session*> session_pool;  // at most two parked sessions (cudaMalloc/cudaFree cost milliseconds each)
   size_t tab_caps = 0;       // capacities of the table buffers when they were filled (a re-allocation invalidates them)
 };
 
@@ -89,6 +90,7 @@ struct bpp_prove_session {
   const bpp_pk* pk = nullptr;
   uint32_t n = 0, m = 0, count = 0, N = 0, L = 0;
   uint32_t step = 0;  // next expected: 0..L = bpp_range_prove_step, L + 1 = bpp_range_prove_finish, L + 2 = done
+  bpp_ctx* owner = nullptr;  // freed sessions are parked in the owner's pool: a same-shaped begin reuses the device memory
   bpp::DevBuf params, a, b, alpha, ypow, gcoef, hcoef, rnd, values, gammas, ext, proofs, out, flag;
   void release() {
     for (bpp::DevBuf* d : {&params, &a, &b, &alpha, &ypow, &gcoef, &hcoef, &rnd, &values, &gammas, &ext, &proofs, &out, &flag}) d->release();

@@ -121,6 +121,20 @@ __global__ void verdict_kernel(uint32_t n_proofs, uint32_t pts_per_proof, uint32
   verdicts[p] = fmt ? BPP_ERR_FORMAT : (C::is_identity(r) ? BPP_OK : BPP_ERR_VERIFICATION);
 }
 
+// random-linear-combination check: the one combined MSM result decides the whole batch. pass[0] = 1 and per-proof verdicts
+// (FORMAT for proofs that did not decode, OK for the rest) if it is the identity; pass[0] = 0 otherwise (verdicts untouched).
+template <class C>
+__global__ void rlc_verdict_kernel(uint32_t n_proofs, const uint32_t* __restrict__ result, const uint8_t* __restrict__ fmt,
+                                   uint8_t* __restrict__ verdicts, uint8_t* __restrict__ pass) {
+  typename C::Ext r;
+  load_words<C::EXT_WORDS>(r, result);
+  const bool ok = C::is_identity(r);
+  if (blockIdx.x == 0 && threadIdx.x == 0) pass[0] = ok ? 1 : 0;
+  if (!ok) return;
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n_proofs; p += gridDim.x * blockDim.x)
+    verdicts[p] = fmt[p] ? BPP_ERR_FORMAT : BPP_OK;
+}
+
 // proof assembly: job results (A, L.., R.., wipA, wipB per proof) -> encoded points inside each proof
 template <class C>
 __global__ void encode_into_proofs_kernel(uint32_t n_proofs, uint32_t jobs_per_proof, const uint32_t* __restrict__ results,

@@ -291,4 +291,65 @@ __global__ void verify_scalars_kernel(VerifyShape vs, VerifyTables T, const uint
   out_pidx[o] = idx;
 }
 
+// ---- random-linear-combination batch check ---------------------------------------------------------
+// sum_p w_p * (verification equation of proof p) = 0 for weights the prover could not predict: the generator terms of all
+// proofs collapse into ONE term per generator, sum_p w_p * exponent_{p,k}; only the 2L + 3 + nV per-proof points stay apart.
+// One MSM of 2 + 2N + count * (2L + 3 + nV) terms replaces `count` MSMs of K terms. A failing combination says only "some proof
+// is bad": the caller falls back to the per-proof path, so verdicts are always the per-proof ones.
+
+// thread per proof: effective weight (Montgomery; 0 for a proof that failed to decode) and its FORMAT flag
+template <class M>
+__global__ void rlc_weights_kernel(uint32_t n_proofs, uint32_t pts_per_proof, uint32_t nV, const uint8_t* __restrict__ weights,
+                                   const uint8_t* __restrict__ dyn_ok, const uint8_t* __restrict__ bad_scalar, uint32_t* __restrict__ w_eff,
+                                   uint8_t* __restrict__ fmt, uint8_t* __restrict__ bad_weight) {
+  typedef Sc<M> S;
+  uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_proofs) return;
+  bool f = bad_scalar[p] != 0;
+  for (uint32_t k = 0; k < pts_per_proof; k++) f = f || !dyn_ok[(size_t)p * pts_per_proof + k];
+  for (uint32_t k = 0; k < nV; k++) f = f || !dyn_ok[(size_t)n_proofs * pts_per_proof + (size_t)p * nV + k];
+  uint32_t w[8], nz = 0;
+  for (int i = 0; i < 8; i++) {
+    const uint8_t* q = weights + (size_t)p * 32 + 4 * i;
+    w[i] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+    nz |= w[i];
+  }
+  if (!S::canonical_ok(w) || !nz) { bad_weight[0] = 1; f = true; }
+  fmt[p] = f ? 1 : 0;
+  st_mont<M>(w_eff, p, f ? S::zero() : sc_load<M>(w));
+}
+
+// thread per generator term t in [0, 2 + 2N): g, h, G_i, H_i  ->  sum_p w_p * exponent_{p,k(t)}
+template <class M>
+__global__ void rlc_fold_fixed_kernel(VerifyShape vs, const uint32_t* __restrict__ w_eff, const uint32_t* __restrict__ in_scalars,
+                                      uint32_t* __restrict__ out_scalars, uint32_t* __restrict__ out_pidx) {
+  typedef Sc<M> S;
+  const uint32_t N = vs.N, L = vs.L, K = 5 + 2 * L + 2 * N + vs.nV;
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= 2 + 2 * N) return;
+  const uint32_t k = t < 2 ? 3 + t : 5 + 2 * L + (t - 2);
+  S acc = S::zero();
+  for (uint32_t p = 0; p < vs.n_proofs; p++) acc = acc + ld_mont<M>(w_eff, p) * S::raw(in_scalars + ((size_t)p * K + k) * 8);
+#pragma unroll
+  for (int i = 0; i < 8; i++) out_scalars[8 * (size_t)t + i] = acc.v[i];
+  out_pidx[t] = t;  // table order of the public key: g, h, G[N], H[N]
+}
+
+// thread per (proof, per-proof point): w_p * exponent; the point index is the one verify_scalars_kernel assigned
+template <class M>
+__global__ void rlc_scale_dyn_kernel(VerifyShape vs, const uint32_t* __restrict__ w_eff, const uint32_t* __restrict__ in_scalars,
+                                     const uint32_t* __restrict__ in_pidx, uint32_t* __restrict__ out_scalars, uint32_t* __restrict__ out_pidx) {
+  typedef Sc<M> S;
+  const uint32_t N = vs.N, L = vs.L, K = 5 + 2 * L + 2 * N + vs.nV, per = 2 * L + 3 + vs.nV;
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= vs.n_proofs * per) return;
+  const uint32_t p = t / per, j = t % per;
+  const uint32_t k = j < 3 ? j : j < 3 + 2 * L ? 5 + (j - 3) : 5 + 2 * L + 2 * N + (j - 3 - 2 * L);
+  const S v = ld_mont<M>(w_eff, p) * S::raw(in_scalars + ((size_t)p * K + k) * 8);
+  const size_t o = 2 + 2 * (size_t)N + t;
+#pragma unroll
+  for (int i = 0; i < 8; i++) out_scalars[8 * o + i] = v.v[i];
+  out_pidx[o] = in_pidx[(size_t)p * K + k];
+}
+
 }  // namespace bpp

@@ -134,6 +134,20 @@ int bpp_range_verify_batch_fs(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m
                               const uint8_t* proofs, const uint8_t* challenges, uint8_t* verdicts);
 int bpp_range_verify_batch_fs_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V,
                                   const void* d_proofs, const void* d_challenges, void* d_verdicts);
+/* Random-linear-combination batch verification: sum_p w_p * (equation of proof p) = 0 is checked with
+ * ONE MSM of 2 + 2*n*m + count*(2L + 3 + m) terms — the generator terms of all proofs collapse — instead of `count` MSMs.
+ * weights = count canonical, non-zero scalars the prover could not predict (the host's CSPRNG; BPP_ERR_FORMAT otherwise).
+ * challenges = NULL (one set: `params`, NULL = the reference's constants) or per-proof blocks as in bpp_range_verify_batch_fs.
+ * The verdicts are always the per-proof ones: proofs that do not decode get BPP_ERR_FORMAT and leave the combination; if the
+ * combination fails, the batch is verified again proof by proof (*used_fallback = 1) to name the bad ones. A wrong accept
+ * needs a bad proof whose error the random weights cancel: probability about 1 / group order per batch.
+ * Both forms synchronise the context's stream (the fallback decision is taken on the host). */
+int bpp_range_verify_batch_rlc(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint8_t* V, const uint8_t* proofs,
+                               const bpp_params* params, const uint8_t* challenges, const uint8_t* weights, uint8_t* verdicts,
+                               int* used_fallback);
+int bpp_range_verify_batch_rlc_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const void* d_V, const void* d_proofs,
+                                   const bpp_params* params, const void* d_challenges, const void* d_weights, void* d_verdicts,
+                                   int* used_fallback);
 /* Interactive proving of a batch, cut where the challenges enter (range/mod.rs:31-55 and wip.rs:36-226 with the constants
  * replaced by the host's answers). All scalars 32-byte canonical; every array is per proof, in batch order.
  *   begin      nonces = NULL (the reference's constants) or count x (5 + 2L) scalars [alpha, r, s, delta, eta, d_L[L], d_R[L]];
@@ -143,7 +157,8 @@ int bpp_range_verify_batch_fs_dev(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size
  *   step L     challenges = count x e_{L-1}       -> out_points = count x [wip A, wip B]
  *   finish     e_final    = count x e             -> proofs = count complete proofs (wire layout above)
  * Calls must come in this order (BPP_ERR_LENGTH otherwise); a zero / non-canonical challenge or nonce is BPP_ERR_FORMAT.
- * The session holds device memory until bpp_prove_session_free; `pk` must outlive it. */
+ * The session holds device memory until bpp_prove_session_free (which may park it in the context for the next batch of the
+ * same shape); `pk` and `ctx` must outlive it. */
 int bpp_range_prove_begin(bpp_ctx* ctx, const bpp_pk* pk, size_t n, size_t m, size_t count, const uint64_t* v, const uint8_t* gamma,
                           const uint8_t* nonces, bpp_prove_session** out, uint8_t* out_A);
 int bpp_range_prove_step(bpp_ctx* ctx, bpp_prove_session* session, const uint8_t* challenges, uint8_t* out_points);

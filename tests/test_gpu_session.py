@@ -55,6 +55,17 @@ def test_session_with_reference_constants_equals_one_shot(api, ctx, oracle, n, m
         assert proofs[i][:32] == pts[0][i] and proofs[i][32:64] == pts[1][i][0]  # what the host was shown is what the proof holds
     with pytest.raises(api.BppError):
         ses.step([7] * count)  # no step left
+    # a second batch of the same shape reuses the parked device state of the first: same bytes for the same inputs, fresh ones otherwise
+    del ses
+    vs2 = [v ^ 1 for v in vs]
+    for values in (vs, vs2):
+        ses = api.ProveSession(pk, n, m, values, gs)
+        ch = [(y, z)] * count
+        for _ in range(L + 1):
+            ses.step(ch)
+            ch = [7] * count
+        assert ses.finish([99] * count) == api.prove_batch(pk, n, m, values, gs)
+        del ses
 
 
 @pytest.mark.parametrize("curve,n,m,count", [(0, 8, 2, 5), (0, 64, 16, 4), (0, 32, 1, 6), (1, 8, 4, 2), (2, 8, 2, 2)])

@@ -25,12 +25,36 @@ def timeit(f, label):
     hot_ms, hot_n = ctx.hot_kernel_stats(reset=True)
     print(f"{label}: {dt*1e3:.3f} ms  ({size/dt:.1f} units/s)  accumulate {hot_ms/max(1,hot_n):.3f} ms x{hot_n//reps}", flush=True)
 
-if case in ("verify", "prove"):
+if case in ("verify", "prove", "verify_fs", "prove_fs", "verify_rlc"):
     pk = api.PublicKey.new(n * m, 0, ctx)
     vs = [rng.randrange(2**31) for _ in range(size * m)]
     gs = [rng.randrange(ELL) for _ in range(size * m)]
     if case == "prove":
         timeit(lambda: api.prove_batch(pk, n, m, vs, gs), f"prove_batch host-ABI B={size}")
+    elif case == "prove_fs":  # interactive prover, challenges = the constants (no transcript cost): the GPU side of real Fiat-Shamir
+        def run():
+            ses = api.ProveSession(pk, n, m, vs, gs)
+            ch = [(12, 23)] * size
+            for _ in range(ses.rounds + 1):
+                ses.step(ch)
+                ch = [7] * size
+            return ses.finish([99] * size)
+        assert run() == api.prove_batch(pk, n, m, vs, gs)
+        timeit(run, f"prove session (12 host round trips) B={size}")
+    elif case == "verify_rlc":
+        proofs = api.prove_batch(pk, n, m, vs, gs)
+        Vs = pk.commit_batch(vs, gs)
+        Vl = [Vs[i * m:(i + 1) * m] for i in range(size)]
+        ws = [rng.getrandbits(128) | 1 for _ in range(size)]
+        assert api.verify_batch_rlc(pk, n, m, proofs, Vl, weights=ws) == ([0] * size, False)
+        timeit(lambda: api.verify_batch_rlc(pk, n, m, proofs, Vl, weights=ws), f"verify_batch_rlc host-ABI B={size}")
+    elif case == "verify_fs":
+        proofs = api.prove_batch(pk, n, m, vs, gs)
+        Vs = pk.commit_batch(vs, gs)
+        Vl = [Vs[i * m:(i + 1) * m] for i in range(size)]
+        chal = [[12, 23, 99] + [7] * 10] * size
+        assert api.verify_batch_fs(pk, n, m, proofs, Vl, challenges=chal) == [0] * size
+        timeit(lambda: api.verify_batch_fs(pk, n, m, proofs, Vl, challenges=chal), f"verify_batch_fs host-ABI B={size}")
     else:
         proofs = api.prove_batch(pk, n, m, vs, gs)
         Vs = pk.commit_batch(vs, gs)
