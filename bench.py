@@ -315,7 +315,15 @@ def main():
                                                "applies (north_star asks for the integer-multiply roofline); HBM figures are in `hbm` below",
         "kernel": "msm_accumulate_kernel<Ed25519> (+ its two long-bucket variants msm_accumulate_group_kernel<.,32|4>, timed together)",
         "achieved": ach_kernel / 1e12 if ach_kernel else None, "peak": int_peak / 1e12, "unit": "T 32x32+64 multiply-adds/s",
-        "frac": (ach_kernel / int_peak) if ach_kernel else None, "traffic": None,
+        "frac": (ach_kernel / int_peak) if ach_kernel else None,
+        # dram__bytes_read.sum + dram__bytes_write.sum of ONE msm_accumulate_kernel launch at this batch size (B = 2048), from the ncu
+        # --set full capture profiles/r01d_msm_accumulate_verify_B2048_ncu_full_details.txt: 1.288 GB + 0.600 GB. Not measured live.
+        "traffic": 1.888e9 if B == 2048 else None, "traffic_unit": "bytes per launch",
+        "ncu": {"capture": "profiles/r01d_msm_accumulate_verify_B2048_ncu_full_details.txt", "gpu_time_ms": 5.82,
+                "sm__pipe_fmaheavy_cycles_active_pct": 87.6, "smsp__issue_active_pct": 43.5, "active_lanes_per_warp_inst": 32.0,
+                "registers_per_thread": 106, "dram_pct_of_peak": 5.0,
+                "note": "the pipe that executes IMAD.WIDE is busy 87.6 % of the kernel's cycles: the kernel sits at the integer-multiply roofline "
+                        "of sm_100a although only 0.4 of the 32-bit IMAD issue rate is reached (every wide multiply-add holds the pipe ~4.6 clk)"},
         "peak_source": "bpp_int_peak_probe: 32-bit IMAD chains with loop-produced operands on all SMs, measured in this run — the "
                        "issue peak of the integer multiply pipe, which every form of 32x32 multiply shares",
         "pipe_ceiling": {"wide_chain_T_per_s": probe["wide_chain_per_s"] / 1e12, "wide_fused_T_per_s": probe["wide_fused_per_s"] / 1e12,

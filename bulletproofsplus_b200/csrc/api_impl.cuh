@@ -359,8 +359,11 @@ struct Api {
       uint8_t* flags = ctx->buf[B_FLAGS].as<uint8_t>();
       BPP_LAUNCH(rlc_weights_kernel<M>, ceil_div(count, 128), 128, 0, count, ppp, vs.nV, d_weights, ctx->buf[B_DYN_OK].as<uint8_t>(),
                  ctx->buf[B_FLAGS2].as<uint8_t>(), w_eff, fmt, flags + 1);
-      BPP_LAUNCH(rlc_fold_fixed_kernel<M>, ceil_div(2 + 2 * N, 64), 64, 0, vs, w_eff, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_WORK0].as<uint32_t>(),
-                 ctx->buf[B_WORK1].as<uint32_t>());
+      BPP_CK(ctx->buf[B_EXT].ensure((size_t)RLC_GROUPS * (2 + 2 * N) * 32));
+      BPP_LAUNCH(rlc_fold_fixed_kernel<M>, dim3(ceil_div(2 + 2 * N, 32), RLC_GROUPS), 256, 0, vs, w_eff, ctx->buf[B_SCALARS].as<uint32_t>(),
+                 ctx->buf[B_EXT].as<uint32_t>());
+      BPP_LAUNCH(rlc_fold_finish_kernel<M>, ceil_div(2 + 2 * N, 128), 128, 0, 2 + 2 * N, RLC_GROUPS, ctx->buf[B_EXT].as<uint32_t>(),
+                 ctx->buf[B_WORK0].as<uint32_t>(), ctx->buf[B_WORK1].as<uint32_t>());
       BPP_LAUNCH(rlc_scale_dyn_kernel<M>, ceil_div(count * per, 256), 256, 0, vs, w_eff, ctx->buf[B_SCALARS].as<uint32_t>(),
                  ctx->buf[B_PIDX].as<uint32_t>(), ctx->buf[B_WORK0].as<uint32_t>(), ctx->buf[B_WORK1].as<uint32_t>());
       BPP_CK(cudaMemcpyAsync(ctx->buf[B_SCALARS].p, ctx->buf[B_WORK0].p, (size_t)T2 * 32, cudaMemcpyDeviceToDevice, ctx->stream));

@@ -319,17 +319,37 @@ __global__ void rlc_weights_kernel(uint32_t n_proofs, uint32_t pts_per_proof, ui
   st_mont<M>(w_eff, p, f ? S::zero() : sc_load<M>(w));
 }
 
-// thread per generator term t in [0, 2 + 2N): g, h, G_i, H_i  ->  sum_p w_p * exponent_{p,k(t)}
+// generator term t in [0, 2 + 2N) (g, h, G_i, H_i)  ->  sum_p w_p * exponent_{p,k(t)}. Block = 32 consecutive terms x 8 proof lanes,
+// gridDim.y proof groups: every thread adds up n_proofs / (8 * gridDim.y) products (1 KB contiguous per proof and warp), the
+// eight lanes meet in shared memory, the groups in rlc_fold_finish_kernel. partial: [gridDim.y][2 + 2N] canonical scalars.
+constexpr uint32_t RLC_GROUPS = 16;
 template <class M>
-__global__ void rlc_fold_fixed_kernel(VerifyShape vs, const uint32_t* __restrict__ w_eff, const uint32_t* __restrict__ in_scalars,
-                                      uint32_t* __restrict__ out_scalars, uint32_t* __restrict__ out_pidx) {
+__global__ void __launch_bounds__(256)
+rlc_fold_fixed_kernel(VerifyShape vs, const uint32_t* __restrict__ w_eff, const uint32_t* __restrict__ in_scalars, uint32_t* __restrict__ partial) {
   typedef Sc<M> S;
-  const uint32_t N = vs.N, L = vs.L, K = 5 + 2 * L + 2 * N + vs.nV;
-  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= 2 + 2 * N) return;
+  __shared__ uint32_t sh[256 * 8];
+  const uint32_t N = vs.N, L = vs.L, K = 5 + 2 * L + 2 * N + vs.nV, nT = 2 + 2 * N;
+  const uint32_t tx = threadIdx.x & 31, ly = threadIdx.x >> 5, t = blockIdx.x * 32 + tx;
   const uint32_t k = t < 2 ? 3 + t : 5 + 2 * L + (t - 2);
   S acc = S::zero();
-  for (uint32_t p = 0; p < vs.n_proofs; p++) acc = acc + ld_mont<M>(w_eff, p) * S::raw(in_scalars + ((size_t)p * K + k) * 8);
+  if (t < nT)
+    for (uint32_t p = blockIdx.y * 8 + ly; p < vs.n_proofs; p += 8 * gridDim.y)
+      acc = acc + ld_mont<M>(w_eff, p) * S::raw(in_scalars + ((size_t)p * K + k) * 8);
+  st_mont<M>(sh, threadIdx.x, acc);
+  __syncthreads();
+  if (ly == 0 && t < nT) {
+    for (uint32_t j = 1; j < 8; j++) acc = acc + ld_mont<M>(sh, j * 32 + tx);
+    st_mont<M>(partial, (size_t)blockIdx.y * nT + t, acc);
+  }
+}
+template <class M>
+__global__ void rlc_fold_finish_kernel(uint32_t nT, uint32_t groups, const uint32_t* __restrict__ partial, uint32_t* __restrict__ out_scalars,
+                                       uint32_t* __restrict__ out_pidx) {
+  typedef Sc<M> S;
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nT) return;
+  S acc = ld_mont<M>(partial, t);
+  for (uint32_t g = 1; g < groups; g++) acc = acc + ld_mont<M>(partial, (size_t)g * nT + t);
 #pragma unroll
   for (int i = 0; i < 8; i++) out_scalars[8 * (size_t)t + i] = acc.v[i];
   out_pidx[t] = t;  // table order of the public key: g, h, G[N], H[N]
