@@ -35,7 +35,7 @@ def build(force: bool = False) -> str:
     srcs = [os.path.join(HERE, "csrc", f) for f in os.listdir(os.path.join(HERE, "csrc"))]
     srcs.append(os.path.join(HERE, "..", "include", "bpp.h"))
     if force or not os.path.exists(SO) or any(os.path.getmtime(s) > os.path.getmtime(SO) for s in srcs):
-        subprocess.check_call(["make", "-j4", "-C", HERE, "libbpp_b200.so"])
+        subprocess.check_call(["make", f"-j{min(10, os.cpu_count() or 4)}", "-C", HERE, "libbpp_b200.so"])
     return SO
 
 

@@ -300,7 +300,7 @@ struct Api {
     vs.N = (uint32_t)pk->len; vs.L = ilog2(vs.N); vs.n = n; vs.m = m; vs.nV = m; vs.mode = mode; vs.n_proofs = count;
     vs.pk_G0 = 2; vs.pk_H0 = 2 + vs.N; vs.dyn0 = pk->n_points();
     const uint32_t N = vs.N, L = vs.L, ppp = 2 * L + 3, K = 5 + 2 * L + 2 * N + vs.nV;
-    if ((uint64_t)count * K > (1ull << 27)) { ctx->err = "verify: batch too large"; return BPP_ERR_LENGTH; }
+    if ((uint64_t)count * K > (1ull << 27) || (uint64_t)count * ppp * PB >= (1ull << 31)) { ctx->err = "verify: batch too large"; return BPP_ERR_LENGTH; }
     const uint32_t n_dyn = count * (ppp + vs.nV);
     BPP_CK(ctx->buf[B_IN0].ensure((size_t)count * ppp * PB));
     BPP_CK(ctx->buf[B_DYN].ensure((size_t)n_dyn * C::AFF_WORDS * 4));

@@ -11,8 +11,5 @@ struct OrderBlsR {
     return o;
   }
 };
-const CurveVtbl* vtbl_bls12_381_g1() {
-  static const CurveVtbl v = make_vtbl<Bls12381G1, ModBlsR, OrderBlsR>();
-  return &v;
-}
+BPP_CURVE_TU(vtbl_bls12_381_g1, bls, Bls12381G1, ModBlsR, OrderBlsR)
 }  // namespace bpp

@@ -57,11 +57,13 @@ int debug_op_host(bpp_ctx* ctx, int op, size_t n, const uint8_t* a, const uint8_
   return BPP_OK;
 }
 
-// ORD::le() = the group order, 32 bytes little-endian (host side canonicality checks of bpp_params)
+// ORD::le() = the group order, 32 bytes little-endian (host side canonicality checks of bpp_params).
+// The table is filled in three parts so that every curve compiles as three translation units in parallel (the prover, the
+// verifier and the key / MSM entry points instantiate disjoint sets of protocol kernels; the build is dominated by the 12-limb
+// BLS12-381 instantiation otherwise).
 template <class C, class M, class ORD>
-CurveVtbl make_vtbl() {
+void fill_vtbl_core(CurveVtbl& v) {
   typedef Api<C, M> A;
-  CurveVtbl v;
   v.curve = C::CURVE_ID; v.point_bytes = C::POINT_BYTES; v.raw_bytes = C::EXT_WORDS * 4; v.field_bytes = C::FIELD_BYTES;
   v.pk_new = A::pk_new;
   v.pk_export = A::pk_export;
@@ -74,12 +76,13 @@ CurveVtbl make_vtbl() {
   v.msm_prepared_raw_dev = A::msm_prepared_raw_dev;
   v.points_sum_raw = A::points_sum_raw;
   v.points_sum_raw_dev = A::points_sum_raw_dev;
-  v.range_prove_batch = [](bpp_ctx* c, const bpp_pk* pk, size_t n, size_t m, size_t cnt, const uint64_t* vv, const uint8_t* g,
-                           const bpp_params* p, uint8_t* o) { return A::range_prove_batch(c, pk, n, m, cnt, vv, g, p, o, ORD::le()); };
+  v.debug_op = debug_op_host<C, M>;
+}
+template <class C, class M, class ORD>
+void fill_vtbl_verify(CurveVtbl& v) {
+  typedef Api<C, M> A;
   v.range_verify_batch = [](bpp_ctx* c, const bpp_pk* pk, size_t n, size_t m, size_t cnt, const uint8_t* V, const uint8_t* pr,
                             const bpp_params* p, uint8_t* o) { return A::range_verify_batch(c, pk, n, m, cnt, V, pr, p, o, ORD::le()); };
-  v.range_prove_batch_dev = [](bpp_ctx* c, const bpp_pk* pk, size_t n, size_t m, size_t cnt, const void* vv, const void* g,
-                               const bpp_params* p, void* o) { return A::range_prove_batch_dev(c, pk, n, m, cnt, vv, g, p, o, ORD::le()); };
   v.range_verify_batch_dev = [](bpp_ctx* c, const bpp_pk* pk, size_t n, size_t m, size_t cnt, const void* V, const void* pr,
                                 const bpp_params* p, void* o) { return A::range_verify_batch_dev(c, pk, n, m, cnt, V, pr, p, o, ORD::le()); };
   v.range_verify_batch_fs = A::range_verify_batch_fs;
@@ -92,17 +95,50 @@ CurveVtbl make_vtbl() {
                                     const void* ch, const void* w, void* o, int* fb) {
     return A::range_verify_batch_rlc_dev(c, pk, n, m, cnt, V, pr, p, ch, w, o, ORD::le(), fb);
   };
+  v.wip_verify = [](bpp_ctx* c, const bpp_pk* pk, const uint8_t* y, const uint8_t* Gc, const uint8_t* Hc, const uint8_t* gc, size_t nV,
+                    const uint8_t* Vc, const uint8_t* Ap, const uint8_t* V, const uint8_t* pr, size_t l, const bpp_params* p) {
+    return A::wip_verify(c, pk, y, Gc, Hc, gc, nV, Vc, Ap, V, pr, l, p, ORD::le());
+  };
+}
+template <class C, class M, class ORD>
+void fill_vtbl_prove(CurveVtbl& v) {
+  typedef Api<C, M> A;
+  v.range_prove_batch = [](bpp_ctx* c, const bpp_pk* pk, size_t n, size_t m, size_t cnt, const uint64_t* vv, const uint8_t* g,
+                           const bpp_params* p, uint8_t* o) { return A::range_prove_batch(c, pk, n, m, cnt, vv, g, p, o, ORD::le()); };
+  v.range_prove_batch_dev = [](bpp_ctx* c, const bpp_pk* pk, size_t n, size_t m, size_t cnt, const void* vv, const void* g,
+                               const bpp_params* p, void* o) { return A::range_prove_batch_dev(c, pk, n, m, cnt, vv, g, p, o, ORD::le()); };
   v.prove_begin = A::prove_begin;
   v.prove_step = A::prove_step;
   v.prove_finish = A::prove_finish;
   v.wip_prove = [](bpp_ctx* c, const bpp_pk* pk, const uint8_t* a, const uint8_t* b, const uint8_t* y, const uint8_t* g,
                    const bpp_params* p, uint8_t* o, size_t* l) { return A::wip_prove(c, pk, a, b, y, g, p, o, l, ORD::le()); };
-  v.wip_verify = [](bpp_ctx* c, const bpp_pk* pk, const uint8_t* y, const uint8_t* Gc, const uint8_t* Hc, const uint8_t* gc, size_t nV,
-                    const uint8_t* Vc, const uint8_t* Ap, const uint8_t* V, const uint8_t* pr, size_t l, const bpp_params* p) {
-    return A::wip_verify(c, pk, y, Gc, Hc, gc, nV, Vc, Ap, V, pr, l, p, ORD::le());
-  };
-  v.debug_op = debug_op_host<C, M>;
-  return v;
 }
+
+// A curve's translation unit is compiled three times, with BPP_VTBL_PART = 0, 1, 2 (Makefile): part 0 defines the accessor
+// `ACCESSOR()` and fills the key / MSM entries, parts 1 and 2 define the two helpers it calls.
+#ifndef BPP_VTBL_PART
+#define BPP_VTBL_PART 0
+#endif
+#if BPP_VTBL_PART == 0
+#define BPP_CURVE_TU(ACCESSOR, TAG, C, M, ORD)                 \
+  void fill_verify_##TAG(CurveVtbl& v);                        \
+  void fill_prove_##TAG(CurveVtbl& v);                         \
+  const CurveVtbl* ACCESSOR() {                                \
+    static const CurveVtbl v = [] {                            \
+      CurveVtbl t{};                                           \
+      fill_vtbl_core<C, M, ORD>(t);                            \
+      fill_verify_##TAG(t);                                    \
+      fill_prove_##TAG(t);                                     \
+      return t;                                                \
+    }();                                                       \
+    return &v;                                                 \
+  }
+#elif BPP_VTBL_PART == 1
+#define BPP_CURVE_TU(ACCESSOR, TAG, C, M, ORD) \
+  void fill_verify_##TAG(CurveVtbl& v) { fill_vtbl_verify<C, M, ORD>(v); }
+#else
+#define BPP_CURVE_TU(ACCESSOR, TAG, C, M, ORD) \
+  void fill_prove_##TAG(CurveVtbl& v) { fill_vtbl_prove<C, M, ORD>(v); }
+#endif
 
 }  // namespace bpp
