@@ -206,6 +206,7 @@ struct Api {
   static void points_release(bpp_points* pts) {
     if (pts->table) cudaFree(pts->table);
     if (pts->wtab) cudaFree(pts->wtab);
+    if (pts->table_acc) cudaFree(pts->table_acc);
     delete pts;
   }
   // scalars already on device (n_jobs*k); result: n_jobs extended points in B_RESULTS
@@ -219,7 +220,16 @@ struct Api {
     BPP_LAUNCH(iota_kernel, ceil_div(T, 256), 256, 0, T, (uint32_t)k, ctx->buf[B_PIDX].as<uint32_t>());
     if (pts->wtab)  // point index i < len: fixed-base segment only
       return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, pts->wtab, (uint32_t)pts->len, pts->cA, pts->WA, nullptr, 0);
-    return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, nullptr, 0, 0, 0, pts->table, (uint32_t)k);
+    const uint32_t* table = pts->table;
+    if (C::F64_TABLES) {  // the same points in the accumulators' slot format, built once per point set
+      bpp_points* mp = const_cast<bpp_points*>(pts);
+      if (!mp->table_acc) {
+        BPP_CK(cudaMalloc(&mp->table_acc, pts->len * C::AFF_WORDS * 4));
+        BPP_LAUNCH(msm_table_format_kernel<C>, ceil_div(pts->len, 128), 128, 0, (uint32_t)pts->len, pts->table, mp->table_acc);
+      }
+      table = mp->table_acc;
+    }
+    return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, nullptr, 0, 0, 0, table, (uint32_t)k, true);
   }
   static int msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out, bool raw) {
     BPP_TRY(clear_flags(ctx));

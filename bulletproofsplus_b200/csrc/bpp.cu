@@ -110,6 +110,13 @@ void bpp_destroy(bpp_ctx* ctx) {
   for (bpp_prove_session* ps : ctx->session_pool) { ps->release(); delete ps; }
   ctx->session_pool.clear();
   for (auto& b : ctx->buf) b.release();
+  if (ctx->aux_stream) {
+    cudaStreamSynchronize(ctx->aux_stream);
+    cudaStreamDestroy(ctx->aux_stream);
+    cudaEventDestroy(ctx->aux_fork);
+    cudaEventDestroy(ctx->aux_join);
+  }
+  for (auto& b : ctx->buf2) b.release();
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -177,6 +184,7 @@ void bpp_points_free(bpp_points* pts) {
   if (!pts) return;
   cudaFree(pts->table);
   if (pts->wtab) cudaFree(pts->wtab);
+  if (pts->table_acc) cudaFree(pts->table_acc);
   delete pts;
 }
 int bpp_points_precompute(bpp_ctx* ctx, bpp_points* pts) {

@@ -10,6 +10,7 @@
 // Encoding/decoding: RFC 9496 §4.3.1 / §4.3.2.
 #pragma once
 #include "fe25519.cuh"
+#include "fe25519_f64.cuh"
 
 namespace bpp {
 
@@ -21,6 +22,11 @@ struct Ed25519 {
   static constexpr int FIELD_BYTES = 32;
   static constexpr int POINT_BYTES = 32;   // boundary encoding
   static constexpr int SCALAR_BITS = 253;  // group order ell < 2^253
+  // ell, little-endian 32-bit words: the table points (multiples of the Ristretto base point) have exactly this order
+  __host__ __device__ static constexpr uint32_t order_word(int i) {
+    constexpr uint32_t c[8] = {0x5cf5d3edu, 0x5812631au, 0xa2f79cd6u, 0x14def9deu, 0x00000000u, 0x00000000u, 0x00000000u, 0x10000000u};
+    return c[i];
+  }
   static constexpr int AFF_WORDS = 32;
   static constexpr int EXT_WORDS = 32;
   static constexpr const char* NAME = "ristretto255";
@@ -104,6 +110,76 @@ struct Ed25519 {
     fe_mul(p.T, e, h);
     fe_mul(p.Z, f, g);
   }
+  // ---- bucket accumulators on the FP64 pipe (fe25519_f64.cuh) ---------------------------------------------------------
+  // The MSM accumulation kernels keep their running sum as 4 x 5 doubles and read table points in the 128-byte slot
+  // format written by store_table_point: ((y+x)/2, (y-x)/2, d*x*y) as 3 x 5 balanced doubles (+ 8 bytes of padding).
+  // Halving the Niels form lets D = Z1 instead of 2*Z1, which keeps every operand of the second-level multiplies within
+  // the lazy bound; all four output coordinates come out divided by 4, i.e. the same projective point.
+#ifndef BPP_ED25519_INT_ACC
+  static constexpr bool F64_TABLES = true;
+  struct Acc { F5 X, Y, Z, T; };
+  BPP_DEV static void store_table_point(uint32_t* dst, const Aff& q) {
+    const uint32_t hc[8] = {0xfffffff7u, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0x3fffffffu};  // (p+1)/2
+    const F half = constant(hc);
+    double* d = reinterpret_cast<double*>(dst);
+    F t;
+    F5 f;
+    fe_mul(t, q.ypx, half); f5_from_fe(f, t);
+#pragma unroll
+    for (int i = 0; i < 5; i++) d[i] = f.v[i];
+    fe_mul(t, q.ymx, half); f5_from_fe(f, t);
+#pragma unroll
+    for (int i = 0; i < 5; i++) d[5 + i] = f.v[i];
+    fe_mul(t, q.t2d, half); f5_from_fe(f, t);
+#pragma unroll
+    for (int i = 0; i < 5; i++) d[10 + i] = f.v[i];
+    d[15] = 0.0;
+  }
+  BPP_DEV static void acc_init(Acc& p, const uint32_t* q, uint32_t neg) {
+    const double* d = reinterpret_cast<const double*>(q);
+    F5 q0, q1;
+    f5_load(q0, d + 5 * neg);
+    f5_load(q1, d + 5 * (1 - neg));
+    f5_sub(p.X, q0, q1);  // +/- x
+    f5_add(p.Y, q0, q1);  // y
+    f5_mul(p.T, p.X, p.Y);
+#pragma unroll
+    for (int i = 0; i < 5; i++) p.Z.v[i] = i ? 0.0 : 1.0;
+  }
+  // HOT: p +/-= the table point at q; 7 multiplies on the FP64 pipe
+  BPP_DEV static void acc_madd(Acc& p, const uint32_t* q, uint32_t neg) {
+    const double* d = reinterpret_cast<const double*>(q);
+    F5 q0, q1, q2, t0, a, b, c, e, f, g, h;
+    f5_load(q0, d + 5 * neg);
+    f5_load(q1, d + 5 * (1 - neg));
+    f5_load(q2, d + 10);
+    f5_sub(t0, p.Y, p.X);
+    f5_mul(a, t0, q1);
+    f5_add(t0, p.Y, p.X);
+    f5_mul(b, t0, q0);
+    f5_mul(c, p.T, q2);
+    f5_cneg(c, c, neg);
+    f5_sub(e, b, a);
+    f5_add(h, b, a);
+    f5_sub(f, p.Z, c);
+    f5_add(g, p.Z, c);
+    f5_mul(p.X, e, f);
+    f5_mul(p.Y, g, h);
+    f5_mul(p.T, e, h);
+    f5_mul(p.Z, f, g);
+  }
+  BPP_DEV static void acc_to_ext(Ext& o, const Acc& p) {
+    f5_to_fe(o.X, p.X); f5_to_fe(o.Y, p.Y); f5_to_fe(o.Z, p.Z); f5_to_fe(o.T, p.T);
+  }
+#else
+  static constexpr bool F64_TABLES = false;
+  typedef Ext Acc;
+  BPP_DEV static void store_table_point(uint32_t* dst, const Aff& q) { store_words<AFF_WORDS>(dst, q); }
+  BPP_DEV static void acc_init(Acc& p, const uint32_t* q, uint32_t neg) { init_from_ptr(p, q, neg); }
+  BPP_DEV static void acc_madd(Acc& p, const uint32_t* q, uint32_t neg) { madd_ptr(p, q, neg); }
+  BPP_DEV static void acc_to_ext(Ext& o, const Acc& p) { o = p; }
+#endif
+
   // p = +/- the table point at q, as (4x : 4y : 4 : 4xy) — one multiply instead of a madd onto the identity
   BPP_DEV static void init_from_ptr(Ext& p, const uint32_t* q, uint32_t neg) {
     F m_minus, m_plus, dx, sy;

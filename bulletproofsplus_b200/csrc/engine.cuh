@@ -33,7 +33,7 @@ struct DevBuf {
 enum BufId {
   B_SCALARS, B_PIDX, B_JOBSTART, B_COUNTS, B_OFFSETS, B_CURSOR, B_TILES, B_SORTED, B_PERM, B_BINS, B_BUCKETS, B_CHUNK_S, B_CHUNK_T,
   B_WINDOWS, B_FIXEDRES, B_RESULTS, B_DYN, B_DYN_OK, B_IN0, B_IN1, B_IN2, B_IN3, B_OUT0, B_PARAMS, B_TAB0, B_TAB1, B_TAB2, B_TAB3, B_TAB4,
-  B_TAB5, B_TAB6, B_WORK0, B_WORK1, B_WORK2, B_FLAGS, B_FLAGS2, B_EXT, B_GIANT_CTL, B_GIANT_ITEMS, B_GIANT_KEYS, B_GIANT_PART, B_COUNT_
+  B_TAB5, B_TAB6, B_WORK0, B_WORK1, B_WORK2, B_FLAGS, B_FLAGS2, B_EXT, B_GIANT_CTL, B_GIANT_ITEMS, B_GIANT_KEYS, B_GIANT_PART, B_DYNF, B_COUNT_
 };
 
 }  // namespace bpp
@@ -43,6 +43,11 @@ struct bpp_ctx {
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   bpp::DevBuf buf[bpp::B_COUNT_];
+  // second scratch set + stream for the generic segment of a two-segment MSM, which runs beside the fixed-base segment
+  // (Msm::run): its Horner pass is a chain of ~SCALAR_BITS dependent doublings per job, latency-bound on a few warps
+  bpp::DevBuf buf2[bpp::B_COUNT_];
+  cudaStream_t aux_stream = nullptr;
+  cudaEvent_t aux_fork = nullptr, aux_join = nullptr;
   std::string err;
   uint64_t launches = 0;
   // hot-kernel timing (bucket accumulation)
@@ -81,6 +86,7 @@ struct bpp_points {
   size_t len = 0;
   uint32_t* table = nullptr;  // affine
   uint32_t* wtab = nullptr;   // optional window tables (bpp_points_precompute): wtab[w * len + i] = 2^(cA * w) * table[i]
+  uint32_t* table_acc = nullptr;  // `table` in the accumulators' slot format (curves with F64_TABLES; built on first use)
   uint32_t cA = 0, WA = 0;
 };
 
@@ -154,15 +160,56 @@ struct Msm {
   // number about `dyn_per_job` per job (0 = none). job_start: device array (n_jobs+1) or nullptr when `uniform` > 0.
   // Leaves n_jobs extended points in ctx->buf[B_RESULTS].
   static int run(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start,
-                 const uint32_t* wtab, uint32_t n_fixed, uint32_t cA, uint32_t WA, const uint32_t* dyn, uint32_t dyn_per_job) {
+                 const uint32_t* wtab, uint32_t n_fixed, uint32_t cA, uint32_t WA, const uint32_t* dyn, uint32_t dyn_per_job,
+                 bool dyn_formatted = false) {
     if (n_jobs == 0) return BPP_OK;
+    const bool two = n_fixed && wtab && dyn_per_job && n_jobs >= 16 && getenv("BPP_NO_OVERLAP") == nullptr;
+    if (!two) return run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 3, dyn_formatted);
+    // Two segments, many jobs: the generic segment (sort, buckets, reduction, Horner) goes to the auxiliary stream with its
+    // own scratch and overlaps the fixed-base segment on the main stream; one addition per job joins them.
+    if (!ctx->aux_stream) {
+      BPP_CK(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
+      BPP_CK(cudaEventCreateWithFlags(&ctx->aux_fork, cudaEventDisableTiming));
+      BPP_CK(cudaEventCreateWithFlags(&ctx->aux_join, cudaEventDisableTiming));
+    }
+    BPP_CK(ctx->buf[B_RESULTS].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
+    BPP_CK(cudaEventRecord(ctx->aux_fork, ctx->stream));
+    BPP_CK(cudaStreamWaitEvent(ctx->aux_stream, ctx->aux_fork, 0));
+    static const BufId scratch[] = {B_COUNTS, B_OFFSETS, B_CURSOR, B_TILES, B_SORTED, B_PERM, B_BINS, B_BUCKETS, B_CHUNK_S, B_CHUNK_T, B_WINDOWS,
+                                    B_FIXEDRES, B_RESULTS, B_GIANT_CTL, B_GIANT_ITEMS, B_GIANT_KEYS, B_GIANT_PART, B_DYNF};
+    auto swap_scratch = [&]() {
+      for (BufId id : scratch) std::swap(ctx->buf[id], ctx->buf2[id]);
+      std::swap(ctx->stream, ctx->aux_stream);
+    };
+    swap_scratch();
+    const bool timing = ctx->hot_timing;
+    ctx->hot_timing = false;  // the hot-kernel bracket stays on the main stream
+    int rc = run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 2, dyn_formatted);
+    ctx->hot_timing = timing;
+    const uint32_t* part_b = ctx->buf[B_RESULTS].as<uint32_t>();
+    if (rc == BPP_OK && cudaEventRecord(ctx->aux_join, ctx->stream) != cudaSuccess) { ctx->err = "cudaEventRecord(aux_join)"; rc = BPP_ERR_CUDA; }
+    swap_scratch();
+    BPP_TRY(rc);
+    BPP_TRY(run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, 0, 1, dyn_formatted));
+    BPP_CK(cudaStreamWaitEvent(ctx->stream, ctx->aux_join, 0));
+    BPP_LAUNCH(msm_join_kernel<C>, ceil_div(n_jobs, 128), 128, 0, n_jobs, ctx->buf[B_RESULTS].as<uint32_t>(), part_b);
+    return BPP_OK;
+  }
+
+  // seg: bit 0 = fixed-base segment, bit 1 = generic segment; terms of a segment that is left out are skipped by the sort
+  // (their window count is zero).
+  static int run_seg(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start,
+                     const uint32_t* wtab, uint32_t n_fixed, uint32_t cA, uint32_t WA, const uint32_t* dyn, uint32_t dyn_per_job, int seg,
+                     bool dyn_formatted) {
     MsmPlan pl;
     memset(&pl, 0, sizeof(pl));
     pl.n_terms = n_terms; pl.n_jobs = n_jobs; pl.uniform = uniform;
-    if (n_fixed && wtab) {
-      pl.n_fixed = n_fixed; pl.cA = cA; pl.WA = WA; pl.NBA = 1u << (cA - 1);
+    if (n_fixed && wtab) pl.n_fixed = n_fixed;
+    if (n_fixed && wtab && (seg & 1)) {
+      pl.cA = cA; pl.WA = WA; pl.NBA = 1u << (cA - 1);
       pl.qA = pl.NBA < 16 ? pl.NBA : 16;
     }
+    if (!(seg & 2)) dyn_per_job = 0;
     if (dyn_per_job) {
       pl.cB = choose_window_generic(dyn_per_job, C::SCALAR_BITS, n_jobs);
       pl.WB = (C::SCALAR_BITS + 1 + pl.cB - 1) / pl.cB;
@@ -170,6 +217,20 @@ struct Msm {
       pl.qB = pl.NBB < 16 ? pl.NBB : 16;
     }
     pl.wtab_points = pl.WA * pl.n_fixed;
+    const uint32_t KPJ = pl.NBA + pl.WB * pl.NBB;
+    pl.sort_mult = 1;
+    if (pl.NBA) {
+      for (int i = 0; i < 8; i++) pl.order[i] = C::order_word(i);
+      // split digits (msm.cuh): only on the per-job shared-memory sort, and only where some job can be small enough
+      if (KPJ <= 12288 && pl.cA >= 8 && getenv("BPP_NO_SPLIT") == nullptr) {
+        const uint32_t k2 = pl.NBA / 9, k3 = pl.NBA / 64;
+        if (!uniform || uniform <= k2) {
+          pl.k2 = k2; pl.k3 = k3;
+          pl.sub2 = (pl.cA + 1) / 2; pl.sub3 = (pl.cA + 2) / 3;
+          pl.sort_mult = (!uniform || uniform <= k3) ? 3 : 2;
+        }
+      }
+    }
     const uint64_t keysA64 = (uint64_t)n_jobs * pl.NBA, keysB64 = (uint64_t)n_jobs * pl.WB * pl.NBB;
     if (keysA64 + keysB64 >= (1ull << 30) || keysA64 + keysB64 == 0) { ctx->err = "msm: key space out of range"; return BPP_ERR_LENGTH; }
     pl.keysA = (uint32_t)keysA64;
@@ -178,7 +239,8 @@ struct Msm {
     const uint32_t chunksB = pl.WB ? (uint32_t)(keysB64 / pl.qB) : 0;
     pl.n_chunks = pl.chunksA + chunksB;
     const uint32_t n_keys = pl.n_keys;
-    const uint64_t n_entries = pl.WA ? (uint64_t)n_terms * pl.WA + (uint64_t)n_jobs * dyn_per_job * (pl.WB > pl.WA ? pl.WB - pl.WA : 0)
+    const uint64_t n_entries = pl.WA ? (uint64_t)n_terms * pl.WA * pl.sort_mult + (uint64_t)n_jobs * dyn_per_job * (pl.WB > pl.WA ? pl.WB - pl.WA : 0)
+                                      : pl.n_fixed ? (uint64_t)n_jobs * dyn_per_job * pl.WB  // generic segment alone: fixed-base terms are skipped
                                       : (uint64_t)n_terms * pl.WB;  // upper bound; the per-job slices of the shared-memory sort
     const uint32_t n_setsB = n_jobs * pl.WB;
     BPP_CK(ctx->buf[B_COUNTS].ensure((size_t)n_keys * 4));
@@ -220,9 +282,15 @@ struct Msm {
     uint32_t* results = ctx->buf[B_RESULTS].as<uint32_t>();
     const uint32_t* scalars = ctx->buf[B_SCALARS].as<uint32_t>();
     const uint32_t* pidx = ctx->buf[B_PIDX].as<uint32_t>();
+    if (C::F64_TABLES && dyn && dyn_per_job && !dyn_formatted) {  // per-call points in the accumulators' table format
+      const uint32_t n_dyn = n_jobs * dyn_per_job;
+      BPP_CK(ctx->buf[B_DYNF].ensure((size_t)n_dyn * C::AFF_WORDS * 4));
+      BPP_LAUNCH(msm_table_format_kernel<C>, ceil_div(n_dyn, 128), 128, 0, n_dyn, dyn, ctx->buf[B_DYNF].as<uint32_t>());
+      dyn = ctx->buf[B_DYNF].as<uint32_t>();
+    }
     BPP_CK(cudaMemsetAsync(bins, 0, 256 * 4, ctx->stream));
     BPP_CK(cudaMemsetAsync(gctl, 0, 16, ctx->stream));
-    const uint32_t KPJ = pl.NBA + pl.WB * pl.NBB;
+    if (n_entries >= (1ull << 32)) { ctx->err = "msm: too many bucket entries for one call"; return BPP_ERR_LENGTH; }
     if (KPJ <= 12288) {
       // small key space per job: one block sorts a whole job in shared memory
       auto k = msm_sort_job_kernel<0>;
@@ -268,8 +336,11 @@ struct Msm {
     }
     BPP_LAUNCH(msm_reduce_chunks_kernel<C>, ceil_div(pl.n_chunks, 128), 128, 0, pl, counts, buckets, chunk_S, chunk_T);
     auto sets = [&](uint32_t n_sets, uint32_t first_chunk, uint32_t q, uint32_t NB, uint32_t* out) -> int {
-      const uint32_t cps = NB / q;                 // chunks per set
-      const uint32_t tps = cps < 128 ? cps : 128;  // threads per set
+      const uint32_t cps = NB / q;  // chunks per set
+      // threads per set: the group's suffix scan costs log2(tps) additions in EVERY thread, so many sets get few threads
+      // each (serial running sums over `per` chunks, work-efficient) and few sets get many (latency); ~32 K threads in all
+      uint32_t tps = 1;
+      while (tps < 128 && tps < cps && (uint64_t)tps * n_sets < 32768) tps <<= 1;
       const uint32_t per = cps / tps;
       BPP_LAUNCH(msm_reduce_sets_kernel<C>, ceil_div(n_sets, 128 / tps), 128, 0, n_sets, first_chunk, q, per, tps, chunk_S, chunk_T, out);
       return BPP_OK;

@@ -47,7 +47,53 @@ struct MsmPlan {
   uint32_t qA, qB;       // reduce chunk sizes (powers of two dividing NBA / NBB)
   uint32_t chunksA;      // keysA / qA
   uint32_t n_chunks;     // chunksA + n_jobs * WB * NBB / qB
+  // fixed-base scalars above order/2 are replaced by order - s with every digit sign flipped (the table points are
+  // torsion-free multiples of the base point): the top partial window, which would otherwise collect ~K/2 carries per job
+  // in ONE bucket, stays empty. order[0] == 0 && order[7] == 0 disables it.
+  uint32_t order[8];
+  // small jobs split every cA-bit digit into 2 or 3 signed sub-digits of `sub2` / `sub3` bits that reference the SAME
+  // table point from buckets of weight d * 2^(i*sub): 2-3x the entries, but only ~2^(sub-1) * levels distinct buckets per
+  // job to reduce instead of 2^(cA-1). Jobs with <= k3 terms use 3 levels, <= k2 terms 2 levels. sort_mult = capacity
+  // multiplier of the per-job slices of `sorted` (1 when no job can split).
+  uint32_t k2, k3, sub2, sub3, sort_mult;
 };
+
+// s (canonical, < order) -> min(s, order - s); returns 1 when negated
+__device__ __forceinline__ uint32_t msm_fold_half(const MsmPlan& pl, uint32_t* s) {
+  uint32_t t[8], bw = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const uint64_t d = (uint64_t)pl.order[i] - s[i] - bw;
+    t[i] = (uint32_t)d;
+    bw = (uint32_t)(d >> 63);
+  }
+  if (bw) return 0;  // s > order: not canonical, left alone (the callers reject such scalars before they get here)
+  bool lt = false, decided = false;
+#pragma unroll
+  for (int i = 7; i >= 0; i--)
+    if (!decided && t[i] != s[i]) { lt = t[i] < s[i]; decided = true; }
+  if (!lt) return 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) s[i] = t[i];
+  return 1;
+}
+
+// Calls emit(bucket weight - 1, negative) for the entries of one window digit of magnitude mag (1..2^(cA-1)).
+// levels == 1: one entry of weight mag. levels 2/3: signed base-2^sub digits d_i of mag, entry i has weight |d_i| * 2^(i*sub).
+template <class F>
+__device__ __forceinline__ void msm_split_digit(uint32_t mag, uint32_t neg, uint32_t levels, uint32_t sub, F emit) {
+  if (levels == 1) { emit(mag - 1, neg); return; }
+  const uint32_t base = 1u << sub, hb = base >> 1;
+  uint32_t rest = mag;
+  for (uint32_t i = 0; i + 1 < levels; i++) {
+    uint32_t d = rest & (base - 1);
+    rest >>= sub;
+    uint32_t dn = d > hb;
+    if (dn) { d = base - d; rest += 1; }
+    if (d) emit((d << (i * sub)) - 1, neg ^ dn);
+  }
+  if (rest) emit((rest << ((levels - 1) * sub)) - 1, neg);
+}
 
 __device__ __forceinline__ uint32_t msm_find_job(const uint32_t* __restrict__ job_start, uint32_t n_jobs, uint32_t uniform, uint32_t t) {
   if (uniform) return t / uniform;
@@ -85,6 +131,7 @@ __global__ void msm_digits_kernel(MsmPlan pl, const uint32_t* __restrict__ scala
     const uint32_t half = 1u << (c - 1);
     const uint32_t keybase = fixed ? job * pl.NBA : pl.keysA + job * pl.WB * pl.NBB;
     const uint32_t refbase = fixed ? p : pl.wtab_points + (p - pl.n_fixed);
+    const uint32_t flip = (fixed && (pl.order[0] | pl.order[7])) ? msm_fold_half(pl, s) : 0u;
     uint32_t carry = 0;
     for (uint32_t w = 0; w < W; w++) {
       uint32_t raw = msm_bits(s, w * c, c) + carry;
@@ -94,7 +141,7 @@ __global__ void msm_digits_kernel(MsmPlan pl, const uint32_t* __restrict__ scala
       if (mag) {
         uint32_t key = keybase + (fixed ? 0u : w * pl.NBB) + (mag - 1);
         if (MODE == 0) atomicAdd(&counts_or_cursor[key], 1u);
-        else sorted[atomicAdd(&counts_or_cursor[key], 1u)] = (refbase + (fixed ? w * pl.n_fixed : 0u)) | (neg << 31);
+        else sorted[atomicAdd(&counts_or_cursor[key], 1u)] = (refbase + (fixed ? w * pl.n_fixed : 0u)) | ((neg ^ flip) << 31);
       }
     }
   }
@@ -104,7 +151,7 @@ __global__ void msm_digits_kernel(MsmPlan pl, const uint32_t* __restrict__ scala
 // One block per job, for jobs whose key space (NBA + WB * NBB counters) fits in shared memory: histogram with shared
 // atomics, block scan, scatter with shared cursors. Only the sorted references and the per-key (offset, count) leave
 // the SM; the global histogram, its memset and the three scan kernels are not needed on this path. Job j owns the
-// slice [ebase_j, ebase_j + cap_j) of `sorted`, cap_j = K_j * WA + dyn_per_job * max(WB - WA, 0).
+// slice [ebase_j, ebase_j + cap_j) of `sorted`, cap_j = sort_mult * K_j * WA + dyn_per_job * max(WB - WA, 0).
 constexpr int SJ_THREADS = 512;
 __device__ __forceinline__ void msm_job_digits(const MsmPlan& pl, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
                                                uint32_t t, uint32_t* s, uint32_t& p) {
@@ -125,7 +172,10 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
   const uint32_t t0 = pl.uniform ? job * pl.uniform : job_start[job];
   const uint32_t t1 = pl.uniform ? t0 + pl.uniform : job_start[job + 1];
   const uint32_t extraW = pl.WB > pl.WA ? pl.WB - pl.WA : 0;
-  const uint32_t ebase = t0 * pl.WA + job * dyn_per_job * extraW;
+  const uint32_t ebase = t0 * pl.WA * pl.sort_mult + job * dyn_per_job * extraW;
+  const uint32_t K = t1 - t0;
+  const uint32_t levels = K <= pl.k3 ? 3u : K <= pl.k2 ? 2u : 1u, sub = levels == 3 ? pl.sub3 : pl.sub2;
+  const bool fold = (pl.order[0] | pl.order[7]) != 0;
   for (uint32_t k = tid; k < KPJ; k += SJ_THREADS) sm[k] = 0;
   __syncthreads();
   // pass 1: histogram
@@ -134,13 +184,16 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
     msm_job_digits(pl, scalars, pidx, t, s, p);
     const bool fixed = p < pl.n_fixed;
     const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
+    if (fixed && fold) msm_fold_half(pl, s);
     uint32_t carry = 0;
     for (uint32_t w = 0; w < W; w++) {
       uint32_t raw = msm_bits(s, w * c, c) + carry;
       uint32_t neg = raw > half;
       uint32_t mag = neg ? (1u << c) - raw : raw;
       carry = neg;
-      if (mag) atomicAdd(&sm[fixed ? mag - 1 : pl.NBA + w * pl.NBB + mag - 1], 1u);
+      if (!mag) continue;
+      if (fixed) msm_split_digit(mag, 0u, levels, sub, [&](uint32_t k, uint32_t) { atomicAdd(&sm[k], 1u); });
+      else atomicAdd(&sm[pl.NBA + w * pl.NBB + mag - 1], 1u);
     }
   }
   __syncthreads();
@@ -186,15 +239,23 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
     const bool fixed = p < pl.n_fixed;
     const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
     const uint32_t refbase = fixed ? p : pl.wtab_points + (p - pl.n_fixed);
+    const uint32_t flip = (fixed && fold) ? msm_fold_half(pl, s) : 0u;
     uint32_t carry = 0;
     for (uint32_t w = 0; w < W; w++) {
       uint32_t raw = msm_bits(s, w * c, c) + carry;
       uint32_t neg = raw > half;
       uint32_t mag = neg ? (1u << c) - raw : raw;
       carry = neg;
-      if (mag) {
-        uint32_t pos = atomicAdd(&sm[fixed ? mag - 1 : pl.NBA + w * pl.NBB + mag - 1], 1u);
-        sorted[ebase + pos] = (refbase + (fixed ? w * pl.n_fixed : 0u)) | (neg << 31);
+      if (!mag) continue;
+      if (fixed) {
+        const uint32_t ref = refbase + w * pl.n_fixed;
+        msm_split_digit(mag, neg ^ flip, levels, sub, [&](uint32_t k, uint32_t ng) {
+          const uint32_t pos = atomicAdd(&sm[k], 1u);
+          sorted[ebase + pos] = ref | (ng << 31);
+        });
+      } else {
+        const uint32_t pos = atomicAdd(&sm[pl.NBA + w * pl.NBB + mag - 1], 1u);
+        sorted[ebase + pos] = refbase | (neg << 31);
       }
     }
   }
@@ -350,14 +411,16 @@ msm_accumulate_kernel(uint32_t n_keys, const uint32_t* __restrict__ perm, const 
   const uint32_t key = perm[t];
   const uint32_t beg = offsets[key], cnt = counts[key], end = beg + cnt;
   if (cnt == 0 || cnt > ACC_CAP) return;
-  typename C::Ext acc;
+  typename C::Acc acc;
   uint32_t ref = __ldg(sorted + beg);
-  C::init_from_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+  C::acc_init(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
   for (uint32_t e = beg + 1; e < end; e++) {
     ref = __ldg(sorted + e);
-    C::madd_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+    C::acc_madd(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
   }
-  store_words<C::EXT_WORDS>(buckets + (size_t)key * C::EXT_WORDS, acc);
+  typename C::Ext out;
+  C::acc_to_ext(out, acc);
+  store_words<C::EXT_WORDS>(buckets + (size_t)key * C::EXT_WORDS, out);
 }
 
 // Buckets longer than ACC_CAP (the first entries of `perm`): G lanes per bucket — lane-strided walk, then a log2(G)-level
@@ -378,12 +441,16 @@ msm_accumulate_group_kernel(const uint32_t* __restrict__ tiers, uint32_t tier, c
     if (counts[key] > GIANT_SEG) continue;  // split over several warps by the msm_giant_* kernels (warp-uniform test)
     const uint32_t beg = offsets[key], end = beg + counts[key];  // count > ACC_CAP >= G: every lane has an entry
     typename C::Ext acc;
-    uint32_t e = beg + lane;
-    uint32_t ref = __ldg(sorted + e);
-    C::init_from_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
-    for (e += G; e < end; e += G) {
-      ref = __ldg(sorted + e);
-      C::madd_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+    {
+      typename C::Acc run;
+      uint32_t e = beg + lane;
+      uint32_t ref = __ldg(sorted + e);
+      C::acc_init(run, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+      for (e += G; e < end; e += G) {
+        ref = __ldg(sorted + e);
+        C::acc_madd(run, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+      }
+      C::acc_to_ext(acc, run);
     }
     *mine = acc;
     __syncwarp();
@@ -445,12 +512,14 @@ msm_giant_accumulate_kernel(const uint32_t* __restrict__ ctl, const uint2* __res
     typename C::Ext acc;
     uint32_t e = beg + lane;
     if (e < end) {  // the last segment of a bucket may be shorter than a warp
+      typename C::Acc run;
       uint32_t ref = __ldg(sorted + e);
-      C::init_from_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+      C::acc_init(run, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
       for (e += 32; e < end; e += 32) {
         ref = __ldg(sorted + e);
-        C::madd_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+        C::acc_madd(run, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
       }
+      C::acc_to_ext(acc, run);
     } else {
       C::set_identity(acc);
     }
@@ -493,7 +562,24 @@ msm_reduce_chunks_kernel(MsmPlan pl, const uint32_t* __restrict__ counts, const 
   else { q = pl.qB; lo = pl.keysA + (id - pl.chunksA) * q; }
   typename C::Ext run, sum, b;
   bool have_run = false, have_sum = false;
-  for (int k = (int)q - 1; k >= 0; k--) {
+  // sparse chunks (the split digits of small jobs leave one bucket per chunk, at weight |d| * 2^(i*sub)): S = B, T = (k+1) * B
+  // by double-and-add instead of k+1 running-sum additions
+  uint32_t n_live = 0, last = 0;
+  for (uint32_t k = 0; k < q; k++)
+    if (counts[lo + k]) { n_live++; last = k; }
+  if (n_live == 1) {
+    load_words<C::EXT_WORDS>(b, buckets + (size_t)(lo + last) * C::EXT_WORDS);
+    store_words<C::EXT_WORDS>(chunk_S + (size_t)id * C::EXT_WORDS, b);
+    const uint32_t wgt = last + 1;
+    sum = b;
+    for (int bit = 30 - (int)__clz(wgt); bit >= 0; bit--) {
+      C::dbl(sum);
+      if ((wgt >> bit) & 1u) C::add(sum, b);
+    }
+    store_words<C::EXT_WORDS>(chunk_T + (size_t)id * C::EXT_WORDS, sum);
+    return;
+  }
+  for (int k = (int)q - 1; k >= 0 && n_live; k--) {
     uint32_t key = lo + k;
     if (counts[key]) {
       load_words<C::EXT_WORDS>(b, buckets + (size_t)key * C::EXT_WORDS);
@@ -594,7 +680,19 @@ msm_combine_kernel(MsmPlan pl, const uint32_t* __restrict__ windows, const uint3
   store_words<C::EXT_WORDS>(results + (size_t)job * C::EXT_WORDS, acc);
 }
 
-// ---- window tables of a public key: wtab[w * n + i] = 2^(c*w) * P_i ------------------------------------------
+// thread per job: results[job] += part[job] (joins the two segments of Msm::run)
+template <class C>
+__global__ void __launch_bounds__(128) msm_join_kernel(uint32_t n_jobs, uint32_t* __restrict__ results, const uint32_t* __restrict__ part) {
+  uint32_t job = blockIdx.x * blockDim.x + threadIdx.x;
+  if (job >= n_jobs) return;
+  typename C::Ext a, b;
+  load_words<C::EXT_WORDS>(a, results + (size_t)job * C::EXT_WORDS);
+  load_words<C::EXT_WORDS>(b, part + (size_t)job * C::EXT_WORDS);
+  C::add(a, b);
+  store_words<C::EXT_WORDS>(results + (size_t)job * C::EXT_WORDS, a);
+}
+
+// ---- window tables of a public key: wtab[w * n + i] = 2^(c*w) * P_i, in the accumulators' slot format ------------------------------------------
 template <class C>
 __global__ void wtab_build_kernel(uint32_t n, uint32_t c, uint32_t W, const uint32_t* __restrict__ aff, uint32_t* __restrict__ wtab) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -602,13 +700,23 @@ __global__ void wtab_build_kernel(uint32_t n, uint32_t c, uint32_t W, const uint
   typename C::Aff q;
   typename C::Ext p;
   load_words<C::AFF_WORDS>(q, aff + (size_t)i * C::AFF_WORDS);
-  store_words<C::AFF_WORDS>(wtab + (size_t)i * C::AFF_WORDS, q);
+  C::store_table_point(wtab + (size_t)i * C::AFF_WORDS, q);
   C::aff_to_ext(p, q);
   for (uint32_t w = 1; w < W; w++) {
     for (uint32_t k = 0; k < c; k++) C::dbl(p);
     C::to_aff(q, p);
-    store_words<C::AFF_WORDS>(wtab + ((size_t)w * n + i) * C::AFF_WORDS, q);
+    C::store_table_point(wtab + ((size_t)w * n + i) * C::AFF_WORDS, q);
   }
+}
+
+// per-call points (affine) -> the slot format the accumulation kernels read (identical unless C::F64_TABLES)
+template <class C>
+__global__ void __launch_bounds__(128) msm_table_format_kernel(uint32_t n, const uint32_t* __restrict__ aff, uint32_t* __restrict__ out) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  typename C::Aff q;
+  load_words<C::AFF_WORDS>(q, aff + (size_t)i * C::AFF_WORDS);
+  C::store_table_point(out + (size_t)i * C::AFF_WORDS, q);
 }
 
 // ---- K5: comb tables for the two commitment bases: comb[(p * CW + w) * 128 + d - 1] = d * 2^(8w) * P_p -------
