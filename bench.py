@@ -246,6 +246,7 @@ def main():
 
     # ---- integer-pipe peak (live) ----
     probe = ctx.int_peak_probe()
+    fp64 = ctx.fp64_peak_probe()  # the alternative multiply (5 x 51-bit limbs on DFMA): measured beside it on every run
     int_peak = probe["imad32_per_s"]  # issue peak of the integer multiply pipe (64 lanes/clk/SM on sm_100a)
 
     # ---- device-resident timing ----
@@ -298,9 +299,10 @@ def main():
     W, c_star, acc_share = algorithmic_field_muls(n_terms)
     hot_avg_ms = hot_ms / max(1, hot_n)
     ach_kernel = B * acc_share * FIELD_MUL_IMAD / (hot_avg_ms * 1e-3) if hot_n else None
-    # what the kernel actually executes: fixed-base window tables (c = 12, 22 windows, no doublings) for the 2050 generator terms,
-    # generic 5-bit windows (51) for the 39 per-proof points: fewer additions than the algorithmic count above
-    exec_madds = B * ((2 + 2 * NM) * 22 + (n_terms - 2 - 2 * NM) * 51)
+    # what the kernel actually executes: fixed-base window tables (c = 12; 21 windows since the scalars are folded below ell/2, no
+    # doublings) for the 2050 generator terms, generic 5-bit windows (51) for the 39 per-proof points: fewer additions than the
+    # algorithmic count above
+    exec_madds = B * ((2 + 2 * NM) * 21 + (n_terms - 2 - 2 * NM) * 51)
     exec_kernel = exec_madds * MIXED * FIELD_MUL_IMAD / (hot_avg_ms * 1e-3) if hot_n else None
     ach_whole = B * W * FIELD_MUL_IMAD / (elapsed_ms / K_steps * 1e-3)
     alg_bytes = B * (n_terms * (32 + 96) + 128)  # scalars + affine points read once, one point written
@@ -330,6 +332,10 @@ def main():
                          "note": "same probe, the two 32x32+64 forms a limb product can use: carry-chained IMAD.WIDE.U32.X (what "
                                  "mul_wide_n emits) and IMAD.WIDE.U32 with a 64-bit register addend; both issue at well under half "
                                  "the IMAD peak on sm_100a, so ~0.43 of `peak` is the ceiling of any multi-limb multiply (DESIGN.md §3.1)"},
+        "fp64_alternative": {"dfma_T_per_s": fp64["dfma_per_s"] / 1e12, "f5_mul_G_per_s": fp64["f5_mul_per_s"] / 1e9,
+                             "note": "the same field multiply as 50 DFMA + 30 DADD + int64 column sums (csrc/fe25519_f64.cuh), probed live: "
+                                     "no faster than the 72-IMAD.WIDE form, and running both kinds of warp on one SM adds nothing "
+                                     "(profiles/r01e_dfma_fe.txt) - DFMA and IMAD.WIDE contend for the same issue capacity on sm_100a"},
         "executed": {"achieved": exec_kernel / 1e12 if exec_kernel else None, "frac": (exec_kernel / int_peak) if exec_kernel else None,
                      "note": "multiply-adds the kernel really issues (upper bound: zero digits skipped): the window tables of the public key "
                              "beat the algorithmic count, so `frac` above overstates pipe utilisation by algorithmic/executed"},

@@ -94,6 +94,11 @@ class Context:
         self.check(self.lib.bpp_int_peak_probe(self.h, rates, C.byref(ms)), "int_peak_probe")
         return dict(imad32_per_s=rates[0], wide_chain_per_s=rates[1], wide_fused_per_s=rates[2], elapsed_ms=ms.value)
 
+    def fp64_peak_probe(self):
+        rates = (C.c_double * 2)()
+        self.check(self.lib.bpp_fp64_peak_probe(self.h, rates), "fp64_peak_probe")
+        return dict(dfma_per_s=rates[0], f5_mul_per_s=rates[1])
+
     def hot_kernel_stats(self, reset=False):
         ms, n = C.c_double(), C.c_uint64()
         self.check(self.lib.bpp_hot_kernel_stats(self.h, C.byref(ms), C.byref(n), 1 if reset else 0), "hot_kernel_stats")

@@ -86,6 +86,7 @@ struct Api {
   static void pk_release(bpp_pk* pk) {
     if (pk->table) cudaFree(pk->table);
     if (pk->wtab) cudaFree(pk->wtab);
+    if (pk->wtab_f) cudaFree(pk->wtab_f);
     if (pk->comb) cudaFree(pk->comb);
     delete pk;
   }
@@ -106,6 +107,12 @@ struct Api {
     wtab_build_kernel<C><<<ceil_div(np, 32), 32, 0, ctx->stream>>>(np, pk->cA, pk->WA, pk->table, pk->wtab);
     comb_build_kernel<C><<<ceil_div(2 * pk->comb_w * COMB_D, 64), 64, 0, ctx->stream>>>(pk->comb_w, pk->table, pk->comb);
     ctx->launches += 3;
+    if (C::HAS_F64 && hybrid_pattern()) {  // the window tables once more, in the slot format of the FP64 accumulators (hybrid accumulation kernel)
+      e = cudaMalloc(&pk->wtab_f, (size_t)np * pk->WA * C::AFF_WORDS * 4);
+      if (e != cudaSuccess) { pk_release(pk); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
+      msm_table_format_kernel<C><<<ceil_div(np * pk->WA, 128), 128, 0, ctx->stream>>>(np * pk->WA, pk->wtab, pk->wtab_f);
+      ctx->launches++;
+    }
     e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { pk_release(pk); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
     *out = pk;
@@ -201,12 +208,23 @@ struct Api {
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { cudaFree(wtab); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
     pts->wtab = wtab; pts->cA = c; pts->WA = W;
+    if (C::HAS_F64 && hybrid_pattern() && bytes <= ((size_t)8 << 30)) {
+      if (cudaMalloc(&pts->wtab_f, bytes) == cudaSuccess) {
+        msm_table_format_kernel<C><<<ceil_div((uint64_t)n * W, 128), 128, 0, ctx->stream>>>(n * W, wtab, pts->wtab_f);
+        ctx->launches++;
+        if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { cudaFree(pts->wtab_f); pts->wtab_f = nullptr; }
+      } else {
+        pts->wtab_f = nullptr;
+        cudaGetLastError();
+      }
+    }
     return BPP_OK;
   }
   static void points_release(bpp_points* pts) {
     if (pts->table) cudaFree(pts->table);
     if (pts->wtab) cudaFree(pts->wtab);
-    if (pts->table_acc) cudaFree(pts->table_acc);
+    if (pts->table_f) cudaFree(pts->table_f);
+    if (pts->wtab_f) cudaFree(pts->wtab_f);
     delete pts;
   }
   // scalars already on device (n_jobs*k); result: n_jobs extended points in B_RESULTS
@@ -219,17 +237,15 @@ struct Api {
     BPP_LAUNCH(scalars_check_kernel<M>, ceil_div(T, 256), 256, 0, T, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_FLAGS].as<uint8_t>());
     BPP_LAUNCH(iota_kernel, ceil_div(T, 256), 256, 0, T, (uint32_t)k, ctx->buf[B_PIDX].as<uint32_t>());
     if (pts->wtab)  // point index i < len: fixed-base segment only
-      return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, pts->wtab, (uint32_t)pts->len, pts->cA, pts->WA, nullptr, 0);
-    const uint32_t* table = pts->table;
-    if (C::F64_TABLES) {  // the same points in the accumulators' slot format, built once per point set
+      return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, pts->wtab, (uint32_t)pts->len, pts->cA, pts->WA, nullptr, 0, pts->wtab_f);
+    if (C::HAS_F64 && hybrid_pattern()) {  // the same points in the FP64 accumulators' slot format, built once per point set
       bpp_points* mp = const_cast<bpp_points*>(pts);
-      if (!mp->table_acc) {
-        BPP_CK(cudaMalloc(&mp->table_acc, pts->len * C::AFF_WORDS * 4));
-        BPP_LAUNCH(msm_table_format_kernel<C>, ceil_div(pts->len, 128), 128, 0, (uint32_t)pts->len, pts->table, mp->table_acc);
+      if (!mp->table_f) {
+        BPP_CK(cudaMalloc(&mp->table_f, pts->len * C::AFF_WORDS * 4));
+        BPP_LAUNCH(msm_table_format_kernel<C>, ceil_div(pts->len, 128), 128, 0, (uint32_t)pts->len, pts->table, mp->table_f);
       }
-      table = mp->table_acc;
     }
-    return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, nullptr, 0, 0, 0, table, (uint32_t)k, true);
+    return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, nullptr, 0, 0, 0, pts->table, (uint32_t)k, nullptr, pts->table_f);
   }
   static int msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out, bool raw) {
     BPP_TRY(clear_flags(ctx));
@@ -378,7 +394,7 @@ struct Api {
                  ctx->buf[B_PIDX].as<uint32_t>(), ctx->buf[B_WORK0].as<uint32_t>(), ctx->buf[B_WORK1].as<uint32_t>());
       BPP_CK(cudaMemcpyAsync(ctx->buf[B_SCALARS].p, ctx->buf[B_WORK0].p, (size_t)T2 * 32, cudaMemcpyDeviceToDevice, ctx->stream));
       BPP_CK(cudaMemcpyAsync(ctx->buf[B_PIDX].p, ctx->buf[B_WORK1].p, (size_t)T2 * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-      BPP_TRY(Msm<C>::run(ctx, T2, 1, T2, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), count * per));
+      BPP_TRY(Msm<C>::run(ctx, T2, 1, T2, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), count * per, pk->wtab_f));
       BPP_LAUNCH(rlc_verdict_kernel<C>, ceil_div(count, 256) < 64 ? ceil_div(count, 256) : 64, 256, 0, count, ctx->buf[B_RESULTS].as<uint32_t>(), fmt,
                  d_verdicts, flags);
       uint8_t res[2] = {0, 0};
@@ -388,7 +404,7 @@ struct Api {
       *rlc_pass = res[0];
       return BPP_OK;
     }
-    BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), ppp + vs.nV));
+    BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), ppp + vs.nV, pk->wtab_f));
     BPP_LAUNCH(verdict_kernel<C>, ceil_div(count, 128), 128, 0, count, ppp, vs.nV, ctx->buf[B_RESULTS].as<uint32_t>(),
                ctx->buf[B_DYN_OK].as<uint8_t>(), ctx->buf[B_FLAGS2].as<uint8_t>(), d_verdicts);
     return BPP_OK;
@@ -551,7 +567,7 @@ struct Api {
                ctx->buf[B_PIDX].as<uint32_t>(), d_proofs, proof_len, scalar_off);
     BPP_LAUNCH(prove_jobstart_kernel, ceil_div(count * J + 1, 256), 256, 0, count, L, N, ps.has_A, ps.terms_per_proof,
                ctx->buf[B_JOBSTART].as<uint32_t>());
-    BPP_TRY(Msm<C>::run(ctx, T_all, count * J, 0, ctx->buf[B_JOBSTART].as<uint32_t>(), pk->wtab, pk->n_points(), pk->cA, pk->WA, nullptr, 0));
+    BPP_TRY(Msm<C>::run(ctx, T_all, count * J, 0, ctx->buf[B_JOBSTART].as<uint32_t>(), pk->wtab, pk->n_points(), pk->cA, pk->WA, nullptr, 0, pk->wtab_f));
     // job 0 of a range proof is alpha * h; RangeProof.A = that + sum(bit ? G_i : -H_i) (range/mod.rs:98-106 / :260-277)
     BPP_LAUNCH(encode_into_proofs_kernel<C>, ceil_div(count * J, 64), 64, 0, count, J, ctx->buf[B_RESULTS].as<uint32_t>(),
                ps.has_A ? ctx->buf[B_EXT].as<uint32_t>() : nullptr, d_proofs, proof_len);
@@ -605,7 +621,7 @@ struct Api {
   static int session_emit(bpp_ctx* ctx, bpp_prove_session* s, uint32_t n_terms, uint32_t jobs, uint32_t uniform, const uint32_t* d_job_start,
                           const uint32_t* add_to_job0, uint32_t slot0, uint32_t slot1, uint8_t* host_out) {
     const size_t plen = (2 * (size_t)s->L + 3) * PB + 96;
-    BPP_TRY(Msm<C>::run(ctx, n_terms, s->count * jobs, uniform, d_job_start, s->pk->wtab, s->pk->n_points(), s->pk->cA, s->pk->WA, nullptr, 0));
+    BPP_TRY(Msm<C>::run(ctx, n_terms, s->count * jobs, uniform, d_job_start, s->pk->wtab, s->pk->n_points(), s->pk->cA, s->pk->WA, nullptr, 0, s->pk->wtab_f));
     BPP_CK(s->out.ensure((size_t)s->count * jobs * PB));
     BPP_LAUNCH(fs_encode_kernel<C>, ceil_div(s->count * jobs, 64), 64, 0, s->count, jobs, ctx->buf[B_RESULTS].as<uint32_t>(), add_to_job0, slot0, slot1,
                s->proofs.as<uint8_t>(), plen, s->out.as<uint8_t>());

@@ -2,6 +2,7 @@
 // launch sequences in api_impl.cuh. No CPU fallback exists: every entry point needs a live bpp_ctx,
 // and bpp_init fails when there is no CUDA device.
 #include "fe25519.cuh"
+#include "fe25519_f64.cuh"
 #include "engine.cuh"
 #include "proto_misc.cuh"
 
@@ -157,6 +158,7 @@ void bpp_pk_free(bpp_pk* pk) {
   cudaSetDevice(pk->device);
   if (pk->table) cudaFree(pk->table);
   if (pk->wtab) cudaFree(pk->wtab);
+  if (pk->wtab_f) cudaFree(pk->wtab_f);
   if (pk->comb) cudaFree(pk->comb);
   delete pk;
 }
@@ -184,7 +186,8 @@ void bpp_points_free(bpp_points* pts) {
   if (!pts) return;
   cudaFree(pts->table);
   if (pts->wtab) cudaFree(pts->wtab);
-  if (pts->table_acc) cudaFree(pts->table_acc);
+  if (pts->table_f) cudaFree(pts->table_f);
+  if (pts->wtab_f) cudaFree(pts->wtab_f);
   delete pts;
 }
 int bpp_points_precompute(bpp_ctx* ctx, bpp_points* pts) {
@@ -364,6 +367,38 @@ int bpp_int_peak_probe(bpp_ctx* ctx, double* rates3, double* elapsed_ms) {
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   if (elapsed_ms) *elapsed_ms = total_ms;
+  return BPP_OK;
+}
+
+int bpp_fp64_peak_probe(bpp_ctx* ctx, double* rates2) {
+  BPP_ENTER(ctx);
+  cudaDeviceProp prop;
+  BPP_CK(cudaGetDeviceProperties(&prop, ctx->device));
+  const int blocks = prop.multiProcessorCount * 4, threads = 256;
+  BPP_CK(ctx->buf[B_OUT0].ensure(64));
+  cudaEvent_t e0, e1;
+  BPP_CK(cudaEventCreate(&e0));
+  BPP_CK(cudaEventCreate(&e1));
+  for (int mode = 0; mode < 2; mode++) {
+    const uint32_t iters = mode == 0 ? 8192 : 2048;
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++) {  // first repetition is the warm-up
+      double* sink = ctx->buf[B_OUT0].as<double>();
+      BPP_CK(cudaEventRecord(e0, ctx->stream));
+      if (mode == 0) fp64_peak_kernel<0><<<blocks, threads, 0, ctx->stream>>>(iters, 1.0000001 + rep, sink);
+      else fp64_peak_kernel<1><<<blocks, threads, 0, ctx->stream>>>(iters, 1.0, sink);
+      ctx->launches++;
+      BPP_CK(cudaGetLastError());
+      BPP_CK(cudaEventRecord(e1, ctx->stream));
+      BPP_CK(cudaEventSynchronize(e1));
+      float ms = 0;
+      BPP_CK(cudaEventElapsedTime(&ms, e0, e1));
+      if (rep > 0 && ms < best) best = ms;
+    }
+    if (rates2) rates2[mode] = (double)blocks * threads * iters * (mode == 0 ? 32.0 : 1.0) / (best * 1e-3);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
   return BPP_OK;
 }
 

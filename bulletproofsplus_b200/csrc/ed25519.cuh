@@ -111,14 +111,14 @@ struct Ed25519 {
     fe_mul(p.Z, f, g);
   }
   // ---- bucket accumulators on the FP64 pipe (fe25519_f64.cuh) ---------------------------------------------------------
-  // The MSM accumulation kernels keep their running sum as 4 x 5 doubles and read table points in the 128-byte slot
-  // format written by store_table_point: ((y+x)/2, (y-x)/2, d*x*y) as 3 x 5 balanced doubles (+ 8 bytes of padding).
+  // Alone, the FP64 multiply is no faster than the integer one (both ~320 issue cycles per warp-multiply, measured), but
+  // the two load DIFFERENT pipes: in the hybrid accumulation kernel (msm_accumulate_kernel<C, true>) some blocks keep
+  // their buckets as 4 x 5 doubles and read table points in the 128-byte slot format written by store_table_point_f: ((y+x)/2, (y-x)/2, d*x*y) as 3 x 5 balanced doubles (+ 8 bytes of padding).
   // Halving the Niels form lets D = Z1 instead of 2*Z1, which keeps every operand of the second-level multiplies within
   // the lazy bound; all four output coordinates come out divided by 4, i.e. the same projective point.
-#ifndef BPP_ED25519_INT_ACC
-  static constexpr bool F64_TABLES = true;
-  struct Acc { F5 X, Y, Z, T; };
-  BPP_DEV static void store_table_point(uint32_t* dst, const Aff& q) {
+  static constexpr bool HAS_F64 = true;
+  struct AccF { F5 X, Y, Z, T; };
+  BPP_DEV static void store_table_point_f(uint32_t* dst, const Aff& q) {
     const uint32_t hc[8] = {0xfffffff7u, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0x3fffffffu};  // (p+1)/2
     const F half = constant(hc);
     double* d = reinterpret_cast<double*>(dst);
@@ -135,7 +135,7 @@ struct Ed25519 {
     for (int i = 0; i < 5; i++) d[10 + i] = f.v[i];
     d[15] = 0.0;
   }
-  BPP_DEV static void acc_init(Acc& p, const uint32_t* q, uint32_t neg) {
+  BPP_DEV static void accf_init(AccF& p, const uint32_t* q, uint32_t neg) {
     const double* d = reinterpret_cast<const double*>(q);
     F5 q0, q1;
     f5_load(q0, d + 5 * neg);
@@ -147,7 +147,7 @@ struct Ed25519 {
     for (int i = 0; i < 5; i++) p.Z.v[i] = i ? 0.0 : 1.0;
   }
   // HOT: p +/-= the table point at q; 7 multiplies on the FP64 pipe
-  BPP_DEV static void acc_madd(Acc& p, const uint32_t* q, uint32_t neg) {
+  BPP_DEV static void accf_madd(AccF& p, const uint32_t* q, uint32_t neg) {
     const double* d = reinterpret_cast<const double*>(q);
     F5 q0, q1, q2, t0, a, b, c, e, f, g, h;
     f5_load(q0, d + 5 * neg);
@@ -168,17 +168,9 @@ struct Ed25519 {
     f5_mul(p.T, e, h);
     f5_mul(p.Z, f, g);
   }
-  BPP_DEV static void acc_to_ext(Ext& o, const Acc& p) {
+  BPP_DEV static void accf_to_ext(Ext& o, const AccF& p) {
     f5_to_fe(o.X, p.X); f5_to_fe(o.Y, p.Y); f5_to_fe(o.Z, p.Z); f5_to_fe(o.T, p.T);
   }
-#else
-  static constexpr bool F64_TABLES = false;
-  typedef Ext Acc;
-  BPP_DEV static void store_table_point(uint32_t* dst, const Aff& q) { store_words<AFF_WORDS>(dst, q); }
-  BPP_DEV static void acc_init(Acc& p, const uint32_t* q, uint32_t neg) { init_from_ptr(p, q, neg); }
-  BPP_DEV static void acc_madd(Acc& p, const uint32_t* q, uint32_t neg) { madd_ptr(p, q, neg); }
-  BPP_DEV static void acc_to_ext(Ext& o, const Acc& p) { o = p; }
-#endif
 
   // p = +/- the table point at q, as (4x : 4y : 4 : 4xy) — one multiply instead of a madd onto the identity
   BPP_DEV static void init_from_ptr(Ext& p, const uint32_t* q, uint32_t neg) {

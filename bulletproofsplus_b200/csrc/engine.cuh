@@ -12,6 +12,10 @@
 #include "proto_prove.cuh"
 #include "proto_session.cuh"
 
+#ifndef BPP_HYBRID_DEFAULT
+#define BPP_HYBRID_DEFAULT 0x0u  // block roles of the hybrid accumulation kernel (bit i: blocks with index % 4 == i use the FP64 pipe)
+#endif
+
 namespace bpp {
 
 // grow-only device buffer
@@ -76,6 +80,7 @@ struct bpp_pk {
   int device = 0;
   uint32_t* table = nullptr;  // affine: g, h, G[len], H[len]
   uint32_t* wtab = nullptr;   // window tables: wtab[w * n_points + i] = 2^(cA * w) * table[i]
+  uint32_t* wtab_f = nullptr; // the same in the FP64 accumulators' slot format (curves with HAS_F64; hybrid accumulation)
   uint32_t* comb = nullptr;   // comb tables of g and h (K5): [(p * comb_w + w) * 128 + d - 1] = d * 2^(8w) * {g, h}
   uint32_t cA = 0, WA = 0, comb_w = 0;
   uint32_t n_points() const { return (uint32_t)(2 + 2 * len); }
@@ -86,7 +91,7 @@ struct bpp_points {
   size_t len = 0;
   uint32_t* table = nullptr;  // affine
   uint32_t* wtab = nullptr;   // optional window tables (bpp_points_precompute): wtab[w * len + i] = 2^(cA * w) * table[i]
-  uint32_t* table_acc = nullptr;  // `table` in the accumulators' slot format (curves with F64_TABLES; built on first use)
+  uint32_t* table_f = nullptr, *wtab_f = nullptr;  // `table` / `wtab` in the FP64 accumulators' slot format (HAS_F64; built on first use)
   uint32_t cA = 0, WA = 0;
 };
 
@@ -125,6 +130,12 @@ namespace bpp {
     BPP_CK(cudaGetLastError());                                            \
   } while (0)
 
+// block roles of the hybrid accumulation kernel: bit i set = blocks with (index % 4) == i run on the FP64 pipe. 0 (the
+// default: measured, mixing the two multiplies gains nothing on sm_100a — DESIGN.md §3.2) = integer pipe only.
+inline uint32_t hybrid_pattern() {
+  static const uint32_t v = (getenv("BPP_HYBRID") ? (uint32_t)strtoul(getenv("BPP_HYBRID"), nullptr, 16) : BPP_HYBRID_DEFAULT) & 0xfu;
+  return v;
+}
 inline uint32_t ceil_div(uint64_t a, uint64_t b) { return (uint32_t)((a + b - 1) / b); }
 inline uint32_t ilog2(uint64_t x) { uint32_t l = 0; while ((1ull << (l + 1)) <= x) l++; return l; }
 
@@ -161,14 +172,18 @@ struct Msm {
   // Leaves n_jobs extended points in ctx->buf[B_RESULTS].
   static int run(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start,
                  const uint32_t* wtab, uint32_t n_fixed, uint32_t cA, uint32_t WA, const uint32_t* dyn, uint32_t dyn_per_job,
-                 bool dyn_formatted = false) {
+                 const uint32_t* wtab_f = nullptr, const uint32_t* dyn_f = nullptr) {
     if (n_jobs == 0) return BPP_OK;
     const bool two = n_fixed && wtab && dyn_per_job && n_jobs >= 16 && getenv("BPP_NO_OVERLAP") == nullptr;
-    if (!two) return run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 3, dyn_formatted);
+    if (!two) return run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 3, wtab_f, dyn_f);
     // Two segments, many jobs: the generic segment (sort, buckets, reduction, Horner) goes to the auxiliary stream with its
     // own scratch and overlaps the fixed-base segment on the main stream; one addition per job joins them.
     if (!ctx->aux_stream) {
-      BPP_CK(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
+      // highest priority: its many small kernels take SM slots as blocks of the big accumulation grid retire, instead of
+      // queueing behind that grid (measured without it: no overlap at all)
+      int prio_lo = 0, prio_hi = 0;
+      BPP_CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+      BPP_CK(cudaStreamCreateWithPriority(&ctx->aux_stream, cudaStreamNonBlocking, prio_hi));
       BPP_CK(cudaEventCreateWithFlags(&ctx->aux_fork, cudaEventDisableTiming));
       BPP_CK(cudaEventCreateWithFlags(&ctx->aux_join, cudaEventDisableTiming));
     }
@@ -184,13 +199,13 @@ struct Msm {
     swap_scratch();
     const bool timing = ctx->hot_timing;
     ctx->hot_timing = false;  // the hot-kernel bracket stays on the main stream
-    int rc = run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 2, dyn_formatted);
+    int rc = run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 2, wtab_f, dyn_f);
     ctx->hot_timing = timing;
     const uint32_t* part_b = ctx->buf[B_RESULTS].as<uint32_t>();
     if (rc == BPP_OK && cudaEventRecord(ctx->aux_join, ctx->stream) != cudaSuccess) { ctx->err = "cudaEventRecord(aux_join)"; rc = BPP_ERR_CUDA; }
     swap_scratch();
     BPP_TRY(rc);
-    BPP_TRY(run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, 0, 1, dyn_formatted));
+    BPP_TRY(run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, 0, 1, wtab_f, dyn_f));
     BPP_CK(cudaStreamWaitEvent(ctx->stream, ctx->aux_join, 0));
     BPP_LAUNCH(msm_join_kernel<C>, ceil_div(n_jobs, 128), 128, 0, n_jobs, ctx->buf[B_RESULTS].as<uint32_t>(), part_b);
     return BPP_OK;
@@ -200,7 +215,7 @@ struct Msm {
   // (their window count is zero).
   static int run_seg(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start,
                      const uint32_t* wtab, uint32_t n_fixed, uint32_t cA, uint32_t WA, const uint32_t* dyn, uint32_t dyn_per_job, int seg,
-                     bool dyn_formatted) {
+                     const uint32_t* wtab_f, const uint32_t* dyn_f) {
     MsmPlan pl;
     memset(&pl, 0, sizeof(pl));
     pl.n_terms = n_terms; pl.n_jobs = n_jobs; pl.uniform = uniform;
@@ -282,11 +297,15 @@ struct Msm {
     uint32_t* results = ctx->buf[B_RESULTS].as<uint32_t>();
     const uint32_t* scalars = ctx->buf[B_SCALARS].as<uint32_t>();
     const uint32_t* pidx = ctx->buf[B_PIDX].as<uint32_t>();
-    if (C::F64_TABLES && dyn && dyn_per_job && !dyn_formatted) {  // per-call points in the accumulators' table format
+    // hybrid accumulation (msm_accumulate_kernel<C, true>): blocks chosen by `pattern` run on the FP64 pipe and need the
+    // tables in its slot format; per-call points are converted here
+    uint32_t pattern = C::HAS_F64 ? hybrid_pattern() : 0u;
+    if (pl.NBA && !wtab_f) pattern = 0;
+    if (pattern && dyn && dyn_per_job && !dyn_f) {
       const uint32_t n_dyn = n_jobs * dyn_per_job;
       BPP_CK(ctx->buf[B_DYNF].ensure((size_t)n_dyn * C::AFF_WORDS * 4));
       BPP_LAUNCH(msm_table_format_kernel<C>, ceil_div(n_dyn, 128), 128, 0, n_dyn, dyn, ctx->buf[B_DYNF].as<uint32_t>());
-      dyn = ctx->buf[B_DYNF].as<uint32_t>();
+      dyn_f = ctx->buf[B_DYNF].as<uint32_t>();
     }
     BPP_CK(cudaMemsetAsync(bins, 0, 256 * 4, ctx->stream));
     BPP_CK(cudaMemsetAsync(gctl, 0, 16, ctx->stream));
@@ -328,7 +347,12 @@ struct Msm {
       BPP_LAUNCH(k32, g32, 128, 0, bins + 256, 0u, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets);
       BPP_LAUNCH(k4, g4, 128, 0, bins + 256, 1u, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets);
     }
-    BPP_LAUNCH(msm_accumulate_kernel<C>, ceil_div(n_keys, 128), 128, 0, n_keys, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets);
+    if (pattern)
+      BPP_LAUNCH((msm_accumulate_kernel<C, true>), ceil_div(n_keys, 128), 128, 0, n_keys, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets,
+                 wtab_f, dyn_f, pattern);
+    else
+      BPP_LAUNCH((msm_accumulate_kernel<C, false>), ceil_div(n_keys, 128), 128, 0, n_keys, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets,
+                 nullptr, nullptr, 0u);
     if (ctx->hot_timing) {
       BPP_CK(cudaEventRecord(e1, ctx->stream));
       ctx->hot_pending.push_back({e0, e1});

@@ -153,12 +153,15 @@ __global__ void msm_digits_kernel(MsmPlan pl, const uint32_t* __restrict__ scala
 // the SM; the global histogram, its memset and the three scan kernels are not needed on this path. Job j owns the
 // slice [ebase_j, ebase_j + cap_j) of `sorted`, cap_j = sort_mult * K_j * WA + dyn_per_job * max(WB - WA, 0).
 constexpr int SJ_THREADS = 512;
-__device__ __forceinline__ void msm_job_digits(const MsmPlan& pl, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
+// point index first: terms of a segment this pass leaves out (window count 0) never load their scalar
+__device__ __forceinline__ bool msm_job_digits(const MsmPlan& pl, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
                                                uint32_t t, uint32_t* s, uint32_t& p) {
+  p = pidx[t];
+  if ((p < pl.n_fixed ? pl.WA : pl.WB) == 0) return false;
   const uint4* sp = reinterpret_cast<const uint4*>(scalars + 8ull * t);
   uint4 a = __ldg(sp), b = __ldg(sp + 1);
   s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
-  p = pidx[t];
+  return true;
 }
 template <int DUMMY>
 __global__ void __launch_bounds__(SJ_THREADS)
@@ -181,7 +184,7 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
   // pass 1: histogram
   for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS) {
     uint32_t s[8], p;
-    msm_job_digits(pl, scalars, pidx, t, s, p);
+    if (!msm_job_digits(pl, scalars, pidx, t, s, p)) continue;
     const bool fixed = p < pl.n_fixed;
     const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
     if (fixed && fold) msm_fold_half(pl, s);
@@ -235,7 +238,7 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
   // pass 2: scatter
   for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS) {
     uint32_t s[8], p;
-    msm_job_digits(pl, scalars, pidx, t, s, p);
+    if (!msm_job_digits(pl, scalars, pidx, t, s, p)) continue;
     const bool fixed = p < pl.n_fixed;
     const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
     const uint32_t refbase = fixed ? p : pl.wtab_points + (p - pl.n_fixed);
@@ -401,25 +404,37 @@ __device__ __forceinline__ const uint32_t* msm_point_ptr(uint32_t ref, const uin
   return idx < wtab_points ? wtab + (size_t)idx * C::AFF_WORDS : dyn + (size_t)(idx - wtab_points) * C::AFF_WORDS;
 }
 
-template <class C>
+// HYB: blocks whose (index mod 4) bit is set in `pattern` keep their buckets on the FP64 pipe (C::AccF, tables wtab_f / dyn_f
+// in the store_table_point_f slot format), the others on the integer pipe. A block's four warps sit on the four
+// sub-partitions of its SM, so every sub-partition runs both kinds of warp and both pipes at once.
+template <class C, bool HYB>
 __global__ void __launch_bounds__(128)
 msm_accumulate_kernel(uint32_t n_keys, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ offsets,
                       const uint32_t* __restrict__ counts, const uint32_t* __restrict__ sorted, const uint32_t* __restrict__ wtab, uint32_t wtab_points,
-                      const uint32_t* __restrict__ dyn, uint32_t* __restrict__ buckets) {
+                      const uint32_t* __restrict__ dyn, uint32_t* __restrict__ buckets, const uint32_t* __restrict__ wtab_f,
+                      const uint32_t* __restrict__ dyn_f, uint32_t pattern) {
   uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_keys) return;
   const uint32_t key = perm[t];
   const uint32_t beg = offsets[key], cnt = counts[key], end = beg + cnt;
   if (cnt == 0 || cnt > ACC_CAP) return;
-  typename C::Acc acc;
-  uint32_t ref = __ldg(sorted + beg);
-  C::acc_init(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
-  for (uint32_t e = beg + 1; e < end; e++) {
-    ref = __ldg(sorted + e);
-    C::acc_madd(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
-  }
   typename C::Ext out;
-  C::acc_to_ext(out, acc);
+  uint32_t ref = __ldg(sorted + beg);
+  if (HYB && ((pattern >> (blockIdx.x & 3)) & 1u)) {
+    typename C::AccF acc;
+    C::accf_init(acc, msm_point_ptr<C>(ref, wtab_f, wtab_points, dyn_f), ref >> 31);
+    for (uint32_t e = beg + 1; e < end; e++) {
+      ref = __ldg(sorted + e);
+      C::accf_madd(acc, msm_point_ptr<C>(ref, wtab_f, wtab_points, dyn_f), ref >> 31);
+    }
+    C::accf_to_ext(out, acc);
+  } else {
+    C::init_from_ptr(out, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+    for (uint32_t e = beg + 1; e < end; e++) {
+      ref = __ldg(sorted + e);
+      C::madd_ptr(out, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+    }
+  }
   store_words<C::EXT_WORDS>(buckets + (size_t)key * C::EXT_WORDS, out);
 }
 
@@ -441,16 +456,12 @@ msm_accumulate_group_kernel(const uint32_t* __restrict__ tiers, uint32_t tier, c
     if (counts[key] > GIANT_SEG) continue;  // split over several warps by the msm_giant_* kernels (warp-uniform test)
     const uint32_t beg = offsets[key], end = beg + counts[key];  // count > ACC_CAP >= G: every lane has an entry
     typename C::Ext acc;
-    {
-      typename C::Acc run;
-      uint32_t e = beg + lane;
-      uint32_t ref = __ldg(sorted + e);
-      C::acc_init(run, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
-      for (e += G; e < end; e += G) {
-        ref = __ldg(sorted + e);
-        C::acc_madd(run, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
-      }
-      C::acc_to_ext(acc, run);
+    uint32_t e = beg + lane;
+    uint32_t ref = __ldg(sorted + e);
+    C::init_from_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+    for (e += G; e < end; e += G) {
+      ref = __ldg(sorted + e);
+      C::madd_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
     }
     *mine = acc;
     __syncwarp();
@@ -512,14 +523,12 @@ msm_giant_accumulate_kernel(const uint32_t* __restrict__ ctl, const uint2* __res
     typename C::Ext acc;
     uint32_t e = beg + lane;
     if (e < end) {  // the last segment of a bucket may be shorter than a warp
-      typename C::Acc run;
       uint32_t ref = __ldg(sorted + e);
-      C::acc_init(run, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+      C::init_from_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
       for (e += 32; e < end; e += 32) {
         ref = __ldg(sorted + e);
-        C::acc_madd(run, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
+        C::madd_ptr(acc, msm_point_ptr<C>(ref, wtab, wtab_points, dyn), ref >> 31);
       }
-      C::acc_to_ext(acc, run);
     } else {
       C::set_identity(acc);
     }
@@ -692,7 +701,7 @@ __global__ void __launch_bounds__(128) msm_join_kernel(uint32_t n_jobs, uint32_t
   store_words<C::EXT_WORDS>(results + (size_t)job * C::EXT_WORDS, a);
 }
 
-// ---- window tables of a public key: wtab[w * n + i] = 2^(c*w) * P_i, in the accumulators' slot format ------------------------------------------
+// ---- window tables of a public key: wtab[w * n + i] = 2^(c*w) * P_i, ------------------------------------------
 template <class C>
 __global__ void wtab_build_kernel(uint32_t n, uint32_t c, uint32_t W, const uint32_t* __restrict__ aff, uint32_t* __restrict__ wtab) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -700,23 +709,23 @@ __global__ void wtab_build_kernel(uint32_t n, uint32_t c, uint32_t W, const uint
   typename C::Aff q;
   typename C::Ext p;
   load_words<C::AFF_WORDS>(q, aff + (size_t)i * C::AFF_WORDS);
-  C::store_table_point(wtab + (size_t)i * C::AFF_WORDS, q);
+  store_words<C::AFF_WORDS>(wtab + (size_t)i * C::AFF_WORDS, q);
   C::aff_to_ext(p, q);
   for (uint32_t w = 1; w < W; w++) {
     for (uint32_t k = 0; k < c; k++) C::dbl(p);
     C::to_aff(q, p);
-    C::store_table_point(wtab + ((size_t)w * n + i) * C::AFF_WORDS, q);
+    store_words<C::AFF_WORDS>(wtab + ((size_t)w * n + i) * C::AFF_WORDS, q);
   }
 }
 
-// per-call points (affine) -> the slot format the accumulation kernels read (identical unless C::F64_TABLES)
+// affine points -> the slot format of the FP64 accumulators (curves with HAS_F64; hybrid accumulation kernel)
 template <class C>
 __global__ void __launch_bounds__(128) msm_table_format_kernel(uint32_t n, const uint32_t* __restrict__ aff, uint32_t* __restrict__ out) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   typename C::Aff q;
   load_words<C::AFF_WORDS>(q, aff + (size_t)i * C::AFF_WORDS);
-  C::store_table_point(out + (size_t)i * C::AFF_WORDS, q);
+  C::store_table_point_f(out + (size_t)i * C::AFF_WORDS, q);
 }
 
 // ---- K5: comb tables for the two commitment bases: comb[(p * CW + w) * 128 + d - 1] = d * 2^(8w) * P_p -------

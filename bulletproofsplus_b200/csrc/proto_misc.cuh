@@ -3,6 +3,7 @@
 #pragma once
 #include "proto_prove.cuh"
 #include "msm.cuh"
+#include "fe25519_f64.cuh"
 
 namespace bpp {
 
@@ -236,6 +237,42 @@ __global__ void __launch_bounds__(256) int_peak_kernel(uint32_t iters, uint32_t 
 #pragma unroll
   for (int i = 0; i < 8; i++) s += acc[i] + lo[i] + hi[i];
   if (s == 0x1234567ull) sink[0] = s;  // never true in practice; keeps the chains alive
+}
+
+// ---- FP64-pipe probes (bpp_fp64_peak_probe) -------------------------------------------------------------------------
+// MODE 0: eight interleaved fma.rz.f64 chains whose operands the loop itself produces; MODE 1: the 5 x 51-bit double-limb
+// field multiply of fe25519_f64.cuh, x <- x * y, y <- old x
+template <int MODE>
+__global__ void __launch_bounds__(256) fp64_peak_kernel(uint32_t iters, double seed, double* __restrict__ sink) {
+  if (MODE == 0) {
+    double x[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = seed + (double)(threadIdx.x + i) * 0x1p-20;
+    for (uint32_t it = 0; it < iters; it++) {
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) x[i] = __fma_rz(x[i], x[(i + 1) & 7], x[(i + 2) & 7]);
+      }
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += x[i];
+    if (s == 0.123456789) sink[0] = s;
+  } else {
+    F5 x, y, z;
+#pragma unroll
+    for (int i = 0; i < 5; i++) { x.v[i] = (double)(long long)(0x2345678abcdell + 977 * i + threadIdx.x); y.v[i] = -(double)(long long)(0x1fedcba987654ll - 31 * i); }
+    for (uint32_t it = 0; it < iters; it++) {
+      f5_mul(z, x, y);
+      y = x;
+      x = z;
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 5; i++) s += x.v[i];
+    if (s == 0.123456789) sink[0] = s;
+  }
 }
 
 }  // namespace bpp

@@ -25,13 +25,14 @@ struct Weierstrass {
   static constexpr int POINT_BYTES = 8 * NL;
   static constexpr int SCALAR_BITS = Cfg::SCALAR_BITS;
   __host__ __device__ static constexpr uint32_t order_word(int i) { return Cfg::order_word(i); }  // prime group order
-  // bucket accumulators of the MSM kernels: the extended point itself (Ed25519 keeps them on the FP64 pipe instead)
-  static constexpr bool F64_TABLES = false;
-  typedef Ext Acc;
-  BPP_DEV static void store_table_point(uint32_t* dst, const Aff& q) { store_words<AFF_WORDS>(dst, q); }
-  BPP_DEV static void acc_init(Acc& p, const uint32_t* q, uint32_t neg) { init_from_ptr(p, q, neg); }
-  BPP_DEV static void acc_madd(Acc& p, const uint32_t* q, uint32_t neg) { madd_ptr(p, q, neg); }
-  BPP_DEV static void acc_to_ext(Ext& o, const Acc& p) { o = p; }
+  // no FP64 accumulator path for the Montgomery-form base fields (Ed25519 has one; the names exist so that the hybrid
+  // kernel template compiles, it is never launched with HYB = true for these curves)
+  static constexpr bool HAS_F64 = false;
+  typedef Ext AccF;
+  BPP_DEV static void store_table_point_f(uint32_t* dst, const Aff& q) { store_words<AFF_WORDS>(dst, q); }
+  BPP_DEV static void accf_init(AccF& p, const uint32_t* q, uint32_t neg) { init_from_ptr(p, q, neg); }
+  BPP_DEV static void accf_madd(AccF& p, const uint32_t* q, uint32_t neg) { madd_ptr(p, q, neg); }
+  BPP_DEV static void accf_to_ext(Ext& o, const AccF& p) { o = p; }
   static constexpr int AFF_WORDS = 3 * NL + Cfg::AFF_PAD;
   static constexpr int EXT_WORDS = 4 * NL;
 

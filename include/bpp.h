@@ -185,6 +185,10 @@ int bpp_int_peak_probe(bpp_ctx* ctx, double* rates3, double* elapsed_ms);
 /* Field-multiply probe: `ilp` independent chains of GF(2^255-19) multiplications per thread on blocks_per_sm x threads_per_block
  * threads per SM, no memory traffic: field multiplications/s (x 72 = multiply-adds/s the carry-chain multiply reaches alone). */
 int bpp_fe_mul_probe(bpp_ctx* ctx, int ilp, int threads_per_block, int blocks_per_sm, double* muls_per_sec);
+/* FP64-pipe microbenchmark (the Ristretto bucket accumulators multiply there, csrc/fe25519_f64.cuh). rates2[0] = DFMA
+ * lane-operations/s (fma.rz.f64 chains with loop-produced operands: the issue peak of the FP64 pipe), rates2[1] =
+ * GF(2^255-19) multiplications/s of the 5 x 51-bit double-limb multiply alone (50 DFMA + 30 DADD each, no memory traffic). */
+int bpp_fp64_peak_probe(bpp_ctx* ctx, double* rates2);
 /* device time (ms, CUDA events on the context's stream) spent in the bucket-accumulation kernel, and its launch
  * count, since the last reset */
 int bpp_hot_kernel_stats(bpp_ctx* ctx, double* ms, uint64_t* launches, int reset);

@@ -19,6 +19,7 @@
 #include <cstring>
 #include <vector>
 #include <cuda_runtime.h>
+#include "../../bulletproofsplus_b200/csrc/fe25519.cuh"  // the library's 8 x 32-bit IMAD.WIDE multiply, for the mixed-pipe run
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); exit(1); } } while (0)
 
@@ -106,6 +107,40 @@ __global__ void mul_kernel(int iters, const F5* __restrict__ in, F5* __restrict_
   }
 #pragma unroll
   for (int q = 0; q < ILP; q++) out[(size_t)t * ILP + q] = x[q];
+}
+
+// ---- both multiplies side by side: warps whose (index mod 4) bit is set in `pattern` run the FP64 multiply, the others the
+// integer one. The two forms load different pipes (FP64 + ALU vs FMA-heavy), so a mix can beat either alone.
+// by_block = 1: the role is chosen per BLOCK (index mod 4): a block's four warps sit on the four sub-partitions of an SM, so
+// every sub-partition sees both kinds of warp. by_block = 0: per warp index within the block, which pins each role to
+// fixed sub-partitions (no mixing inside a sub-partition).
+__global__ void mix_kernel(int iters, uint32_t pattern, int by_block, const F5* __restrict__ in, F5* __restrict__ out, uint32_t* __restrict__ out_i) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool f64 = (pattern >> ((by_block ? blockIdx.x : (threadIdx.x >> 5)) & 3)) & 1u;
+  if (f64) {
+    F5 x = in[0], y = in[1];
+    x.v[0] += (double)(t & 7);
+    for (int i = 0; i < iters; i++) {
+      F5 z;
+      f5_mul(z, x, y);
+      y = x;
+      x = z;
+    }
+    out[t] = x;
+  } else {
+    bpp::Fe25519 x, y, z;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { x.v[k] = 0x9e3779b9u * (k + 1) + t; y.v[k] = 0x85ebca6bu * (k + 3) ^ t; }
+    for (int i = 0; i < iters; i++) {
+      bpp::fe_mul(z, x, y);
+      y = x;
+      x = z;
+    }
+    uint32_t acc = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) acc ^= x.v[k];
+    out_i[t] = acc;
+  }
 }
 
 // ---- host reference: 5 x 51-bit limbs, unsigned __int128 -------------------------------------------------------------
@@ -239,6 +274,30 @@ int main() {
       const double muls = (double)blocks * threads * iters * ilp;
       printf("f5_mul (FP64 pipe): %4d threads/SM, ILP %d: %7.1f G multiplies/s  (%.0f clk per warp-multiply per sub-partition at 1.9 GHz)\n",
              threads_per_sm, ilp, muls / (ms * 1e-3) / 1e9, 1.9e9 * nsm * 4 * 32 / (muls / (ms * 1e-3)));
+    }
+  }
+  {
+    uint32_t* out_i;
+    CK(cudaMalloc(&out_i, sizeof(uint32_t) * (size_t)max_threads));
+    const struct { uint32_t pat; const char* name; } pats[] = {{0x0, "all warps integer multiply (8x32 IMAD.WIDE)"}, {0xf, "all warps FP64 multiply (5x51 DFMA)"},
+      {0x5, "1/2 FP64 + 1/2 integer"}, {0x1, "1/4 FP64 + 3/4 integer"}, {0x7, "3/4 FP64 + 1/4 integer"}};
+    for (int by_block = 1; by_block >= 0; by_block--)
+    for (int threads_per_sm : {512, 1024, 2048}) {
+      for (auto& pt : pats) {
+        if (!by_block && (pt.pat == 0 || pt.pat == 0xf)) continue;
+        const int iters = 2000, threads = 128, blocks = nsm * threads_per_sm / threads;
+        for (int rep = 0; rep < 2; rep++) {
+          CK(cudaEventRecord(e0));
+          mix_kernel<<<blocks, threads>>>(iters, pt.pat, by_block, din, dout, out_i);
+          CK(cudaEventRecord(e1));
+          CK(cudaEventSynchronize(e1));
+          CK(cudaGetLastError());
+        }
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        const double muls = (double)blocks * threads * iters;
+        printf("mix (%s): %4d threads/SM, %-46s %7.1f G multiplies/s\n", by_block ? "role per block" : "role per warp ", threads_per_sm, pt.name, muls / (ms * 1e-3) / 1e9);
+      }
     }
   }
   printf("reference: the library's 8x32-bit IMAD.WIDE multiply runs at 108-113 G multiplies/s (profiles/r01c_fe_probe.txt)\n");
