@@ -343,6 +343,14 @@ struct Api {
     if (d_challenges) BPP_CK(ctx->buf[B_TAB5].ensure((size_t)count * (P_FIXED + 3 * L) * 32));
     BPP_CK(ctx->buf[B_TAB4].ensure((size_t)count * 128));
     // decode the per-proof points and the commitments into the dynamic table
+    // Only the generic MSM segment reads the decoded points: when that segment will run on the auxiliary stream (per-proof
+    // MSMs, >= 16 proofs) the decoding starts there too, beside the exponent kernels and the fixed-base sort on the main stream.
+    const bool aux_decode = !d_weights && Msm<C>::overlaps(count);
+    struct AuxGuard {
+      bpp_ctx* c; bool on;
+      ~AuxGuard() { if (on) Msm<C>::aux_leave(c); }
+    } aux_guard{ctx, false};
+    if (aux_decode) { BPP_TRY(Msm<C>::aux_enter(ctx)); aux_guard.on = true; }
     const uint32_t gb = count * ppp * (uint32_t)PB;
     BPP_LAUNCH(gather_proof_points_kernel, ceil_div(gb, 256), 256, 0, count, ppp * (uint32_t)PB, d_proofs, proof_len, ctx->buf[B_IN0].as<uint8_t>());
     BPP_LAUNCH(points_decode_kernel<C>, ceil_div(count * ppp, 64), 64, 0, count * ppp, ctx->buf[B_IN0].as<uint8_t>(),
@@ -350,6 +358,7 @@ struct Api {
     if (vs.nV)
       BPP_LAUNCH(points_decode_kernel<C>, ceil_div(count * vs.nV, 64), 64, 0, count * vs.nV, d_V,
                  ctx->buf[B_DYN].as<uint32_t>() + (size_t)count * ppp * C::AFF_WORDS, ctx->buf[B_DYN_OK].as<uint8_t>() + (size_t)count * ppp);
+    if (aux_guard.on) { Msm<C>::aux_leave(ctx); aux_guard.on = false; }
     VerifyTables T;
     T.Tmul = ctx->buf[B_TAB0].as<uint32_t>(); T.Tadd = ctx->buf[B_TAB1].as<uint32_t>(); T.tmp = ctx->buf[B_TAB2].as<uint32_t>();
     T.zpow = ctx->buf[B_TAB3].as<uint32_t>();

@@ -166,18 +166,12 @@ inline uint32_t choose_window_generic(uint64_t terms_per_job, uint32_t scalar_bi
 
 template <class C>
 struct Msm {
-  // Runs the segmented MSM over terms already in ctx->buf[B_SCALARS] / [B_PIDX]. Terms with point index < n_fixed use the
-  // window tables `wtab` (cA, WA from the public key); the others index `dyn` (per-call affine table) at idx - n_fixed and
-  // number about `dyn_per_job` per job (0 = none). job_start: device array (n_jobs+1) or nullptr when `uniform` > 0.
-  // Leaves n_jobs extended points in ctx->buf[B_RESULTS].
-  static int run(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start,
-                 const uint32_t* wtab, uint32_t n_fixed, uint32_t cA, uint32_t WA, const uint32_t* dyn, uint32_t dyn_per_job,
-                 const uint32_t* wtab_f = nullptr, const uint32_t* dyn_f = nullptr) {
-    if (n_jobs == 0) return BPP_OK;
-    const bool two = n_fixed && wtab && dyn_per_job && n_jobs >= 16 && getenv("BPP_NO_OVERLAP") == nullptr;
-    if (!two) return run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 3, wtab_f, dyn_f);
-    // Two segments, many jobs: the generic segment (sort, buckets, reduction, Horner) goes to the auxiliary stream with its
-    // own scratch and overlaps the fixed-base segment on the main stream; one addition per job joins them.
+  // a two-segment MSM over this many jobs runs its generic segment on the auxiliary stream (run() below)
+  static bool overlaps(uint32_t n_jobs) {
+    static const bool off = getenv("BPP_NO_OVERLAP") != nullptr;
+    return n_jobs >= 16 && !off;
+  }
+  static int aux_ensure(bpp_ctx* ctx) {
     if (!ctx->aux_stream) {
       // highest priority: its many small kernels take SM slots as blocks of the big accumulation grid retire, instead of
       // queueing behind that grid (measured without it: no overlap at all)
@@ -187,6 +181,33 @@ struct Msm {
       BPP_CK(cudaEventCreateWithFlags(&ctx->aux_fork, cudaEventDisableTiming));
       BPP_CK(cudaEventCreateWithFlags(&ctx->aux_join, cudaEventDisableTiming));
     }
+    return BPP_OK;
+  }
+  // Work that only the generic segment needs (decoding the per-call points) can start on the auxiliary stream before run():
+  // aux_enter forks from the caller's stream and redirects launches until aux_leave. The caller must go on to a run() for
+  // which overlaps() holds — that run joins the auxiliary stream back.
+  static int aux_enter(bpp_ctx* ctx) {
+    BPP_TRY(aux_ensure(ctx));
+    BPP_CK(cudaEventRecord(ctx->aux_fork, ctx->stream));
+    BPP_CK(cudaStreamWaitEvent(ctx->aux_stream, ctx->aux_fork, 0));
+    std::swap(ctx->stream, ctx->aux_stream);
+    return BPP_OK;
+  }
+  static void aux_leave(bpp_ctx* ctx) { std::swap(ctx->stream, ctx->aux_stream); }
+
+  // Runs the segmented MSM over terms already in ctx->buf[B_SCALARS] / [B_PIDX]. Terms with point index < n_fixed use the
+  // window tables `wtab` (cA, WA from the public key); the others index `dyn` (per-call affine table) at idx - n_fixed and
+  // number about `dyn_per_job` per job (0 = none). job_start: device array (n_jobs+1) or nullptr when `uniform` > 0.
+  // Leaves n_jobs extended points in ctx->buf[B_RESULTS].
+  static int run(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start,
+                 const uint32_t* wtab, uint32_t n_fixed, uint32_t cA, uint32_t WA, const uint32_t* dyn, uint32_t dyn_per_job,
+                 const uint32_t* wtab_f = nullptr, const uint32_t* dyn_f = nullptr) {
+    if (n_jobs == 0) return BPP_OK;
+    const bool two = n_fixed && wtab && dyn_per_job && overlaps(n_jobs);
+    if (!two) return run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 3, wtab_f, dyn_f);
+    // Two segments, many jobs: the generic segment (sort, buckets, reduction, Horner) goes to the auxiliary stream with its
+    // own scratch and overlaps the fixed-base segment on the main stream; one addition per job joins them.
+    BPP_TRY(aux_ensure(ctx));
     BPP_CK(ctx->buf[B_RESULTS].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
     BPP_CK(cudaEventRecord(ctx->aux_fork, ctx->stream));
     BPP_CK(cudaStreamWaitEvent(ctx->aux_stream, ctx->aux_fork, 0));

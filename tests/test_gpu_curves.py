@@ -134,6 +134,14 @@ def test_msm(api, ctx, oracle, R):
     want = oracle.scalar_mul(R, sum(a * b for a, b in zip(mult, sc)) % q)
     assert pts.msm(b"".join(le32(x) for x in sc))[0] == want
     assert pts.precompute().msm(b"".join(le32(x) for x in sc))[0] == want  # window tables: same point, no doublings
+    # short jobs against the 4096-point window tables: the engine splits every window digit into 3 (k <= N_B/64) or 2
+    # (k <= N_B/9) signed sub-digits that share the table point (msm.cuh, msm_split_digit); scalars above order/2 are folded
+    for k, jobs in ((5, 3), (40, 2), (200, 3), (450, 1), (700, 2)):
+        ss = [rng.randrange(q) for _ in range(k * jobs)]
+        ss[0], ss[k - 1] = q - 1, (q + 1) // 2
+        got = pts.msm(b"".join(le32(x) for x in ss), k=k, n_jobs=jobs)
+        for j in range(jobs):
+            assert got[j] == oracle.scalar_mul(R, sum(a * b for a, b in zip(mult[:k], ss[j * k:(j + 1) * k])) % q), (k, j)
     dup = api.Points.from_multipliers(b"".join(le32(mult[i // 2] if i % 2 == 0 else (q - mult[i // 2])) for i in range(256)), R, ctx).precompute()
     s256 = sc[:256]
     want = sum(s * (mult[i // 2] if i % 2 == 0 else q - mult[i // 2]) for i, s in enumerate(s256)) % q
