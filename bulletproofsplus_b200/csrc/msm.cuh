@@ -163,6 +163,30 @@ __device__ __forceinline__ bool msm_job_digits(const MsmPlan& pl, const uint32_t
   s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
   return true;
 }
+// Four consecutive window digits of one term: shared-memory keys (0xffffffff = no entry) and sorted references. The kernel
+// issues the four shared atomics back to back and only then uses their results: a warp otherwise spends most of its time
+// waiting for ONE atomic's return at a time (short-scoreboard stalls were 56 % of the issue cycles, r01g capture).
+__device__ __forceinline__ void msm_digits4(const MsmPlan& pl, const uint32_t* s, bool fixed, uint32_t c, uint32_t W, uint32_t w0,
+                                            uint32_t refbase, uint32_t flip, uint32_t& carry, uint32_t* key, uint32_t* ref) {
+  const uint32_t half = 1u << (c - 1);
+#pragma unroll
+  for (int u = 0; u < 4; u++) {
+    const uint32_t w = w0 + u;
+    key[u] = 0xffffffffu;
+    ref[u] = 0;
+    if (w < W) {
+      const uint32_t raw = msm_bits(s, w * c, c) + carry;
+      const uint32_t neg = raw > half;
+      const uint32_t mag = neg ? (1u << c) - raw : raw;
+      carry = neg;
+      if (mag) {
+        key[u] = fixed ? mag - 1 : pl.NBA + w * pl.NBB + mag - 1;
+        ref[u] = (fixed ? refbase + w * pl.n_fixed : refbase) | ((neg ^ flip) << 31);
+      }
+    }
+  }
+}
+
 template <int DUMMY>
 __global__ void __launch_bounds__(SJ_THREADS)
 msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
@@ -189,6 +213,16 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
     const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
     if (fixed && fold) msm_fold_half(pl, s);
     uint32_t carry = 0;
+    if (levels == 1 || !fixed) {
+      for (uint32_t w0 = 0; w0 < W; w0 += 4) {
+        uint32_t key[4], ref[4];
+        msm_digits4(pl, s, fixed, c, W, w0, 0u, 0u, carry, key, ref);
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (key[u] != 0xffffffffu) atomicAdd(&sm[key[u]], 1u);
+      }
+      continue;
+    }
     for (uint32_t w = 0; w < W; w++) {
       uint32_t raw = msm_bits(s, w * c, c) + carry;
       uint32_t neg = raw > half;
@@ -244,6 +278,19 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
     const uint32_t refbase = fixed ? p : pl.wtab_points + (p - pl.n_fixed);
     const uint32_t flip = (fixed && fold) ? msm_fold_half(pl, s) : 0u;
     uint32_t carry = 0;
+    if (levels == 1 || !fixed) {
+      for (uint32_t w0 = 0; w0 < W; w0 += 4) {
+        uint32_t key[4], ref[4], pos[4];
+        msm_digits4(pl, s, fixed, c, W, w0, refbase, flip, carry, key, ref);
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (key[u] != 0xffffffffu) pos[u] = atomicAdd(&sm[key[u]], 1u);
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (key[u] != 0xffffffffu) sorted[ebase + pos[u]] = ref[u];
+      }
+      continue;
+    }
     for (uint32_t w = 0; w < W; w++) {
       uint32_t raw = msm_bits(s, w * c, c) + carry;
       uint32_t neg = raw > half;
