@@ -153,6 +153,7 @@ __global__ void msm_digits_kernel(MsmPlan pl, const uint32_t* __restrict__ scala
 // the SM; the global histogram, its memset and the three scan kernels are not needed on this path. Job j owns the
 // slice [ebase_j, ebase_j + cap_j) of `sorted`, cap_j = sort_mult * K_j * WA + dyn_per_job * max(WB - WA, 0).
 constexpr int SJ_THREADS = 512;
+constexpr uint32_t SJ_RANK_TERMS = 5, SJ_RANK_WINDOWS = 32;  // ranks kept per thread: 5 terms x 32 windows x 8 bits = 160 bytes
 // point index first: terms of a segment this pass leaves out (window count 0) never load their scalar
 __device__ __forceinline__ bool msm_job_digits(const MsmPlan& pl, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
                                                uint32_t t, uint32_t* s, uint32_t& p) {
@@ -205,8 +206,15 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
   const bool fold = (pl.order[0] | pl.order[7]) != 0;
   for (uint32_t k = tid; k < KPJ; k += SJ_THREADS) sm[k] = 0;
   __syncthreads();
+  // The shared atomics bound this kernel (~10 cycles per wavefront per SM, r01h capture), so the histogram pass keeps the
+  // rank every atomic returns — 8 bits each, four per word — and the scatter pass needs none: position = bucket start +
+  // rank. Only for unsplit jobs of at most SJ_RANK_TERMS terms per thread and SJ_RANK_WINDOWS windows; a rank above 254
+  // (a bucket that long) sends the whole job back to the two-pass form.
+  uint32_t ranks[SJ_RANK_TERMS * (SJ_RANK_WINDOWS / 4)];
+  const bool keep_ranks = levels == 1 && K <= SJ_RANK_TERMS * SJ_THREADS && pl.WA <= SJ_RANK_WINDOWS && pl.WB <= SJ_RANK_WINDOWS;
+  uint32_t rank_overflow = 0, term_i = 0;
   // pass 1: histogram
-  for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS) {
+  for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS, term_i++) {
     uint32_t s[8], p;
     if (!msm_job_digits(pl, scalars, pidx, t, s, p)) continue;
     const bool fixed = p < pl.n_fixed;
@@ -217,9 +225,14 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
       for (uint32_t w0 = 0; w0 < W; w0 += 4) {
         uint32_t key[4], ref[4];
         msm_digits4(pl, s, fixed, c, W, w0, 0u, 0u, carry, key, ref);
+        uint32_t r[4] = {0, 0, 0, 0};
 #pragma unroll
         for (int u = 0; u < 4; u++)
-          if (key[u] != 0xffffffffu) atomicAdd(&sm[key[u]], 1u);
+          if (key[u] != 0xffffffffu) r[u] = atomicAdd(&sm[key[u]], 1u);
+        if (keep_ranks) {
+          rank_overflow |= (r[0] | r[1] | r[2] | r[3]) > 254u;
+          ranks[term_i * (SJ_RANK_WINDOWS / 4) + (w0 >> 2)] = (r[0] & 255u) | ((r[1] & 255u) << 8) | ((r[2] & 255u) << 16) | (r[3] << 24);
+        }
       }
       continue;
     }
@@ -233,6 +246,7 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
       else atomicAdd(&sm[pl.NBA + w * pl.NBB + mag - 1], 1u);
     }
   }
+  const bool use_ranks = keep_ranks && !__syncthreads_or((int)rank_overflow);
   __syncthreads();
   // exclusive scan of cnt[0..KPJ): contiguous chunk per thread
   const uint32_t ch = (KPJ + SJ_THREADS - 1) / SJ_THREADS;
@@ -270,7 +284,8 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
   }
   __syncthreads();
   // pass 2: scatter
-  for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS) {
+  term_i = 0;
+  for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS, term_i++) {
     uint32_t s[8], p;
     if (!msm_job_digits(pl, scalars, pidx, t, s, p)) continue;
     const bool fixed = p < pl.n_fixed;
@@ -282,9 +297,16 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
       for (uint32_t w0 = 0; w0 < W; w0 += 4) {
         uint32_t key[4], ref[4], pos[4];
         msm_digits4(pl, s, fixed, c, W, w0, refbase, flip, carry, key, ref);
+        if (use_ranks) {  // sm[] still holds the bucket starts: nothing in this pass modifies it
+          const uint32_t rk = ranks[term_i * (SJ_RANK_WINDOWS / 4) + (w0 >> 2)];
 #pragma unroll
-        for (int u = 0; u < 4; u++)
-          if (key[u] != 0xffffffffu) pos[u] = atomicAdd(&sm[key[u]], 1u);
+          for (int u = 0; u < 4; u++)
+            if (key[u] != 0xffffffffu) pos[u] = sm[key[u]] + ((rk >> (8 * u)) & 255u);
+        } else {
+#pragma unroll
+          for (int u = 0; u < 4; u++)
+            if (key[u] != 0xffffffffu) pos[u] = atomicAdd(&sm[key[u]], 1u);
+        }
 #pragma unroll
         for (int u = 0; u < 4; u++)
           if (key[u] != 0xffffffffu) sorted[ebase + pos[u]] = ref[u];
