@@ -304,7 +304,7 @@ def main():
     ach_kernel = B * acc_share * (n_fixed_terms / n_terms) * FIELD_MUL_IMAD / (hot_avg_ms * 1e-3) if hot_n else None
     # what the kernel actually executes: fixed-base window tables (c = 12; 21 windows since the scalars are folded below ell/2, no
     # doublings) for the 2050 generator terms: fewer additions than the algorithmic count above (the 39 per-proof points take
-    # 51 generic 5-bit windows each, outside the timed bracket)
+    # 64 generic 4-bit windows each, outside the timed bracket)
     exec_madds = B * (2 + 2 * NM) * 21
     exec_kernel = exec_madds * MIXED * FIELD_MUL_IMAD / (hot_avg_ms * 1e-3) if hot_n else None
     ach_whole = B * W * FIELD_MUL_IMAD / (elapsed_ms / K_steps * 1e-3)

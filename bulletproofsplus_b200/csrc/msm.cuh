@@ -153,7 +153,6 @@ __global__ void msm_digits_kernel(MsmPlan pl, const uint32_t* __restrict__ scala
 // the SM; the global histogram, its memset and the three scan kernels are not needed on this path. Job j owns the
 // slice [ebase_j, ebase_j + cap_j) of `sorted`, cap_j = sort_mult * K_j * WA + dyn_per_job * max(WB - WA, 0).
 constexpr int SJ_THREADS = 512;
-constexpr uint32_t SJ_RANK_TERMS = 5, SJ_RANK_WINDOWS = 32;  // ranks kept per thread: 5 terms x 32 windows x 8 bits = 160 bytes
 // point index first: terms of a segment this pass leaves out (window count 0) never load their scalar
 __device__ __forceinline__ bool msm_job_digits(const MsmPlan& pl, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
                                                uint32_t t, uint32_t* s, uint32_t& p) {
@@ -188,8 +187,36 @@ __device__ __forceinline__ void msm_digits4(const MsmPlan& pl, const uint32_t* s
   }
 }
 
-template <int DUMMY>
-__global__ void __launch_bounds__(SJ_THREADS)
+// The same for a fixed-base term when the window width is a compile-time constant: every bit offset is static, so the
+// scalar stays in registers (the generic form indexes s[] dynamically = local memory) and a digit costs ~12 instructions
+// instead of ~65 (r01h/r01i captures: the kernel was bound by instruction issue and local-memory latency, not by atomics).
+template <int CA>
+__device__ __forceinline__ void msm_digits4_static(const MsmPlan& pl, const uint32_t* s, uint32_t W, int w0, uint32_t refbase, uint32_t flip,
+                                                   uint32_t& carry, uint32_t* key, uint32_t* ref) {
+  constexpr uint32_t half = 1u << (CA - 1), mask = (1u << CA) - 1u;
+#pragma unroll
+  for (int u = 0; u < 4; u++) {
+    const int w = w0 + u, off = w * CA, word = off >> 5, sh = off & 31;
+    key[u] = 0xffffffffu;
+    ref[u] = 0;
+    if ((uint32_t)w < W && word < 8) {
+      const uint32_t lo = s[word], hi = word + 1 < 8 ? s[word + 1] : 0u;
+      const uint32_t raw = (__funnelshift_r(lo, hi, sh) & mask) + carry;
+      const uint32_t neg = raw > half;
+      const uint32_t mag = neg ? (1u << CA) - raw : raw;
+      carry = neg;
+      if (mag) {
+        key[u] = mag - 1;
+        ref[u] = (refbase + (uint32_t)w * pl.n_fixed) | ((neg ^ flip) << 31);
+      }
+    }
+  }
+}
+
+// CA > 0: pl.cA == CA (the host picks the instantiation), fixed-base digits are extracted with static offsets
+// MINB: resident blocks per SM the register allocation is held to (3 = 40 registers with a few spills, 2 = 64 registers)
+template <int CA, int MINB>
+__global__ void __launch_bounds__(SJ_THREADS, MINB)
 msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
                     const uint32_t* __restrict__ job_start, uint32_t* __restrict__ offsets, uint32_t* __restrict__ counts,
                     uint32_t* __restrict__ sorted) {
@@ -206,33 +233,37 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
   const bool fold = (pl.order[0] | pl.order[7]) != 0;
   for (uint32_t k = tid; k < KPJ; k += SJ_THREADS) sm[k] = 0;
   __syncthreads();
-  // The shared atomics bound this kernel (~10 cycles per wavefront per SM, r01h capture), so the histogram pass keeps the
-  // rank every atomic returns — 8 bits each, four per word — and the scatter pass needs none: position = bucket start +
-  // rank. Only for unsplit jobs of at most SJ_RANK_TERMS terms per thread and SJ_RANK_WINDOWS windows; a rank above 254
-  // (a bucket that long) sends the whole job back to the two-pass form.
-  uint32_t ranks[SJ_RANK_TERMS * (SJ_RANK_WINDOWS / 4)];
-  const bool keep_ranks = levels == 1 && K <= SJ_RANK_TERMS * SJ_THREADS && pl.WA <= SJ_RANK_WINDOWS && pl.WB <= SJ_RANK_WINDOWS;
-  uint32_t rank_overflow = 0, term_i = 0;
   // pass 1: histogram
-  for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS, term_i++) {
-    uint32_t s[8], p;
-    if (!msm_job_digits(pl, scalars, pidx, t, s, p)) continue;
+  for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS) {
+    uint32_t q[8], p;  // statically indexed only: registers
+    if (!msm_job_digits(pl, scalars, pidx, t, q, p)) continue;
     const bool fixed = p < pl.n_fixed;
     const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
-    if (fixed && fold) msm_fold_half(pl, s);
+    if (fixed && fold) msm_fold_half(pl, q);
     uint32_t carry = 0;
+    if (CA > 0 && fixed && levels == 1) {
+      constexpr int CAx = CA > 0 ? CA : 12, WMAX = (256 + CAx - 1) / CAx + 1;
+#pragma unroll
+      for (int w0 = 0; w0 < WMAX; w0 += 4) {
+        if ((uint32_t)w0 >= W) break;
+        uint32_t key[4], ref[4];
+        msm_digits4_static<CAx>(pl, q, W, w0, 0u, 0u, carry, key, ref);
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (key[u] != 0xffffffffu) atomicAdd(&sm[key[u]], 1u);
+      }
+      continue;
+    }
+    uint32_t s[8];  // indexed by a runtime bit offset below: lives in local memory
+#pragma unroll
+    for (int i = 0; i < 8; i++) s[i] = q[i];
     if (levels == 1 || !fixed) {
       for (uint32_t w0 = 0; w0 < W; w0 += 4) {
         uint32_t key[4], ref[4];
         msm_digits4(pl, s, fixed, c, W, w0, 0u, 0u, carry, key, ref);
-        uint32_t r[4] = {0, 0, 0, 0};
 #pragma unroll
         for (int u = 0; u < 4; u++)
-          if (key[u] != 0xffffffffu) r[u] = atomicAdd(&sm[key[u]], 1u);
-        if (keep_ranks) {
-          rank_overflow |= (r[0] | r[1] | r[2] | r[3]) > 254u;
-          ranks[term_i * (SJ_RANK_WINDOWS / 4) + (w0 >> 2)] = (r[0] & 255u) | ((r[1] & 255u) << 8) | ((r[2] & 255u) << 16) | (r[3] << 24);
-        }
+          if (key[u] != 0xffffffffu) atomicAdd(&sm[key[u]], 1u);
       }
       continue;
     }
@@ -246,7 +277,6 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
       else atomicAdd(&sm[pl.NBA + w * pl.NBB + mag - 1], 1u);
     }
   }
-  const bool use_ranks = keep_ranks && !__syncthreads_or((int)rank_overflow);
   __syncthreads();
   // exclusive scan of cnt[0..KPJ): contiguous chunk per thread
   const uint32_t ch = (KPJ + SJ_THREADS - 1) / SJ_THREADS;
@@ -284,29 +314,40 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
   }
   __syncthreads();
   // pass 2: scatter
-  term_i = 0;
-  for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS, term_i++) {
-    uint32_t s[8], p;
-    if (!msm_job_digits(pl, scalars, pidx, t, s, p)) continue;
+  for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS) {
+    uint32_t q[8], p;
+    if (!msm_job_digits(pl, scalars, pidx, t, q, p)) continue;
     const bool fixed = p < pl.n_fixed;
     const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
     const uint32_t refbase = fixed ? p : pl.wtab_points + (p - pl.n_fixed);
-    const uint32_t flip = (fixed && fold) ? msm_fold_half(pl, s) : 0u;
+    const uint32_t flip = (fixed && fold) ? msm_fold_half(pl, q) : 0u;
     uint32_t carry = 0;
+    if (CA > 0 && fixed && levels == 1) {
+      constexpr int CAx = CA > 0 ? CA : 12, WMAX = (256 + CAx - 1) / CAx + 1;
+#pragma unroll
+      for (int w0 = 0; w0 < WMAX; w0 += 4) {
+        if ((uint32_t)w0 >= W) break;
+        uint32_t key[4], ref[4], pos[4];
+        msm_digits4_static<CAx>(pl, q, W, w0, refbase, flip, carry, key, ref);
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (key[u] != 0xffffffffu) pos[u] = atomicAdd(&sm[key[u]], 1u);
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (key[u] != 0xffffffffu) sorted[ebase + pos[u]] = ref[u];
+      }
+      continue;
+    }
+    uint32_t s[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) s[i] = q[i];
     if (levels == 1 || !fixed) {
       for (uint32_t w0 = 0; w0 < W; w0 += 4) {
         uint32_t key[4], ref[4], pos[4];
         msm_digits4(pl, s, fixed, c, W, w0, refbase, flip, carry, key, ref);
-        if (use_ranks) {  // sm[] still holds the bucket starts: nothing in this pass modifies it
-          const uint32_t rk = ranks[term_i * (SJ_RANK_WINDOWS / 4) + (w0 >> 2)];
 #pragma unroll
-          for (int u = 0; u < 4; u++)
-            if (key[u] != 0xffffffffu) pos[u] = sm[key[u]] + ((rk >> (8 * u)) & 255u);
-        } else {
-#pragma unroll
-          for (int u = 0; u < 4; u++)
-            if (key[u] != 0xffffffffu) pos[u] = atomicAdd(&sm[key[u]], 1u);
-        }
+        for (int u = 0; u < 4; u++)
+          if (key[u] != 0xffffffffu) pos[u] = atomicAdd(&sm[key[u]], 1u);
 #pragma unroll
         for (int u = 0; u < 4; u++)
           if (key[u] != 0xffffffffu) sorted[ebase + pos[u]] = ref[u];
