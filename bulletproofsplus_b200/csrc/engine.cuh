@@ -333,13 +333,7 @@ struct Msm {
     if (n_entries >= (1ull << 32)) { ctx->err = "msm: too many bucket entries for one call"; return BPP_ERR_LENGTH; }
     if (KPJ <= 12288) {
       // small key space per job: one block sorts a whole job in shared memory
-      // window width known at compile time for the usual key sizes (n*m = 256 ... 8192): static digit extraction
-      static const bool two_blocks = getenv("BPP_SORT_BLOCKS") && atoi(getenv("BPP_SORT_BLOCKS")) == 2;
-      auto k3 = pl.cA == 12 ? msm_sort_job_kernel<12, 3> : pl.cA == 11 ? msm_sort_job_kernel<11, 3> : pl.cA == 13 ? msm_sort_job_kernel<13, 3>
-              : pl.cA == 10 ? msm_sort_job_kernel<10, 3> : pl.cA == 14 ? msm_sort_job_kernel<14, 3> : msm_sort_job_kernel<0, 3>;
-      auto k2 = pl.cA == 12 ? msm_sort_job_kernel<12, 2> : pl.cA == 11 ? msm_sort_job_kernel<11, 2> : pl.cA == 13 ? msm_sort_job_kernel<13, 2>
-              : pl.cA == 10 ? msm_sort_job_kernel<10, 2> : pl.cA == 14 ? msm_sort_job_kernel<14, 2> : msm_sort_job_kernel<0, 2>;
-      auto k = two_blocks ? k2 : k3;
+      auto k = msm_sort_job_kernel<0>;
       const size_t smem = (size_t)KPJ * 4;
       if (smem > 48 * 1024) BPP_CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       BPP_LAUNCH(k, n_jobs, SJ_THREADS, smem, pl, dyn_per_job, scalars, pidx, d_job_start, offsets, counts, sorted);

@@ -187,36 +187,8 @@ __device__ __forceinline__ void msm_digits4(const MsmPlan& pl, const uint32_t* s
   }
 }
 
-// The same for a fixed-base term when the window width is a compile-time constant: every bit offset is static, so the
-// scalar stays in registers (the generic form indexes s[] dynamically = local memory) and a digit costs ~12 instructions
-// instead of ~65 (r01h/r01i captures: the kernel was bound by instruction issue and local-memory latency, not by atomics).
-template <int CA>
-__device__ __forceinline__ void msm_digits4_static(const MsmPlan& pl, const uint32_t* s, uint32_t W, int w0, uint32_t refbase, uint32_t flip,
-                                                   uint32_t& carry, uint32_t* key, uint32_t* ref) {
-  constexpr uint32_t half = 1u << (CA - 1), mask = (1u << CA) - 1u;
-#pragma unroll
-  for (int u = 0; u < 4; u++) {
-    const int w = w0 + u, off = w * CA, word = off >> 5, sh = off & 31;
-    key[u] = 0xffffffffu;
-    ref[u] = 0;
-    if ((uint32_t)w < W && word < 8) {
-      const uint32_t lo = s[word], hi = word + 1 < 8 ? s[word + 1] : 0u;
-      const uint32_t raw = (__funnelshift_r(lo, hi, sh) & mask) + carry;
-      const uint32_t neg = raw > half;
-      const uint32_t mag = neg ? (1u << CA) - raw : raw;
-      carry = neg;
-      if (mag) {
-        key[u] = mag - 1;
-        ref[u] = (refbase + (uint32_t)w * pl.n_fixed) | ((neg ^ flip) << 31);
-      }
-    }
-  }
-}
-
-// CA > 0: pl.cA == CA (the host picks the instantiation), fixed-base digits are extracted with static offsets
-// MINB: resident blocks per SM the register allocation is held to (3 = 40 registers with a few spills, 2 = 64 registers)
-template <int CA, int MINB>
-__global__ void __launch_bounds__(SJ_THREADS, MINB)
+template <int DUMMY>
+__global__ void __launch_bounds__(SJ_THREADS)
 msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
                     const uint32_t* __restrict__ job_start, uint32_t* __restrict__ offsets, uint32_t* __restrict__ counts,
                     uint32_t* __restrict__ sorted) {
@@ -235,28 +207,12 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
   __syncthreads();
   // pass 1: histogram
   for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS) {
-    uint32_t q[8], p;  // statically indexed only: registers
-    if (!msm_job_digits(pl, scalars, pidx, t, q, p)) continue;
+    uint32_t s[8], p;
+    if (!msm_job_digits(pl, scalars, pidx, t, s, p)) continue;
     const bool fixed = p < pl.n_fixed;
     const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
-    if (fixed && fold) msm_fold_half(pl, q);
+    if (fixed && fold) msm_fold_half(pl, s);
     uint32_t carry = 0;
-    if (CA > 0 && fixed && levels == 1) {
-      constexpr int CAx = CA > 0 ? CA : 12, WMAX = (256 + CAx - 1) / CAx + 1;
-#pragma unroll
-      for (int w0 = 0; w0 < WMAX; w0 += 4) {
-        if ((uint32_t)w0 >= W) break;
-        uint32_t key[4], ref[4];
-        msm_digits4_static<CAx>(pl, q, W, w0, 0u, 0u, carry, key, ref);
-#pragma unroll
-        for (int u = 0; u < 4; u++)
-          if (key[u] != 0xffffffffu) atomicAdd(&sm[key[u]], 1u);
-      }
-      continue;
-    }
-    uint32_t s[8];  // indexed by a runtime bit offset below: lives in local memory
-#pragma unroll
-    for (int i = 0; i < 8; i++) s[i] = q[i];
     if (levels == 1 || !fixed) {
       for (uint32_t w0 = 0; w0 < W; w0 += 4) {
         uint32_t key[4], ref[4];
@@ -315,32 +271,13 @@ msm_sort_job_kernel(MsmPlan pl, uint32_t dyn_per_job, const uint32_t* __restrict
   __syncthreads();
   // pass 2: scatter
   for (uint32_t t = t0 + tid; t < t1; t += SJ_THREADS) {
-    uint32_t q[8], p;
-    if (!msm_job_digits(pl, scalars, pidx, t, q, p)) continue;
+    uint32_t s[8], p;
+    if (!msm_job_digits(pl, scalars, pidx, t, s, p)) continue;
     const bool fixed = p < pl.n_fixed;
     const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB, half = 1u << (c - 1);
     const uint32_t refbase = fixed ? p : pl.wtab_points + (p - pl.n_fixed);
-    const uint32_t flip = (fixed && fold) ? msm_fold_half(pl, q) : 0u;
+    const uint32_t flip = (fixed && fold) ? msm_fold_half(pl, s) : 0u;
     uint32_t carry = 0;
-    if (CA > 0 && fixed && levels == 1) {
-      constexpr int CAx = CA > 0 ? CA : 12, WMAX = (256 + CAx - 1) / CAx + 1;
-#pragma unroll
-      for (int w0 = 0; w0 < WMAX; w0 += 4) {
-        if ((uint32_t)w0 >= W) break;
-        uint32_t key[4], ref[4], pos[4];
-        msm_digits4_static<CAx>(pl, q, W, w0, refbase, flip, carry, key, ref);
-#pragma unroll
-        for (int u = 0; u < 4; u++)
-          if (key[u] != 0xffffffffu) pos[u] = atomicAdd(&sm[key[u]], 1u);
-#pragma unroll
-        for (int u = 0; u < 4; u++)
-          if (key[u] != 0xffffffffu) sorted[ebase + pos[u]] = ref[u];
-      }
-      continue;
-    }
-    uint32_t s[8];
-#pragma unroll
-    for (int i = 0; i < 8; i++) s[i] = q[i];
     if (levels == 1 || !fixed) {
       for (uint32_t w0 = 0; w0 < W; w0 += 4) {
         uint32_t key[4], ref[4], pos[4];
