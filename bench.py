@@ -89,7 +89,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._halt.wait(0.2)
+            self._halt.wait(0.02)  # nvidia-smi itself takes ~50 ms: several samples even in a 0.2 s timed region
 
     def stop(self):
         self._halt.set()
