@@ -379,7 +379,9 @@ struct Msm {
       ctx->hot_pending.push_back({e0, e1});
       ctx->hot_launches++;
     }
-    BPP_LAUNCH(msm_reduce_chunks_kernel<C>, ceil_div(pl.n_chunks, 128), 128, 0, pl, counts, buckets, chunk_S, chunk_T);
+    static const bool chunks4 = getenv("BPP_CHUNKS_BLOCKS") && atoi(getenv("BPP_CHUNKS_BLOCKS")) == 4;  // A/B: 128 registers, 4 blocks per SM
+    if (chunks4) BPP_LAUNCH((msm_reduce_chunks_kernel<C, 4>), ceil_div(pl.n_chunks, 128), 128, 0, pl, counts, buckets, chunk_S, chunk_T);
+    else BPP_LAUNCH((msm_reduce_chunks_kernel<C, 1>), ceil_div(pl.n_chunks, 128), 128, 0, pl, counts, buckets, chunk_S, chunk_T);
     auto sets = [&](uint32_t n_sets, uint32_t first_chunk, uint32_t q, uint32_t NB, uint32_t* out) -> int {
       const uint32_t cps = NB / q;  // chunks per set
       // threads per set: the group's suffix scan costs log2(tps) additions in EVERY thread, so many sets get few threads

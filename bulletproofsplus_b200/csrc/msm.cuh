@@ -607,8 +607,9 @@ msm_giant_merge_kernel(const uint32_t* __restrict__ ctl, const uint4* __restrict
 
 // ---- bucket reduction: sum_b (b+1) * bucket[b] per bucket set ---------------------------------------------
 // level 1 — thread per chunk of q consecutive buckets: S = sum of the chunk, T = sum_k (k+1) * bucket[lo+k]
-template <class C>
-__global__ void __launch_bounds__(128)
+// MINB: resident blocks per SM the register allocation is held to (1 = unconstrained: 139 registers, 3 blocks on Ed25519)
+template <class C, int MINB>
+__global__ void __launch_bounds__(128, MINB)
 msm_reduce_chunks_kernel(MsmPlan pl, const uint32_t* __restrict__ counts, const uint32_t* __restrict__ buckets,
                          uint32_t* __restrict__ chunk_S, uint32_t* __restrict__ chunk_T) {
   uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
