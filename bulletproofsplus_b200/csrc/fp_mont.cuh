@@ -90,7 +90,11 @@ struct Fp {
     mul_wide_n<NL>(t, a.v, b.v);
     return mont_reduce(t);
   }
-  BPP_DEV static Fp sqr(const Fp& a) { return mul(a, a); }
+  BPP_DEV static Fp sqr(const Fp& a) {  // NL (NL + 1) / 2 wide products instead of NL^2
+    uint32_t t[2 * NL];
+    sqr_wide_n<NL>(t, a.v);
+    return mont_reduce(t);
+  }
   BPP_DEV bool is_zero() const { uint32_t o = 0; for (int i = 0; i < NL; i++) o |= v[i]; return o == 0; }
   BPP_DEV static bool eq(const Fp& a, const Fp& b) { uint32_t o = 0; for (int i = 0; i < NL; i++) o |= a.v[i] ^ b.v[i]; return o == 0; }
   BPP_DEV static Fp from_canonical(const uint32_t* limbs) {
