@@ -21,7 +21,7 @@ SYMBOLS = [
     "bpp_msm_prepared_dev", "bpp_raw_point_bytes", "bpp_msm_prepared_raw", "bpp_points_sum_raw", "bpp_msm_prepared_raw_dev", "bpp_points_sum_raw_dev", "bpp_range_prove_batch",
     "bpp_range_verify_batch", "bpp_range_prove_batch_dev", "bpp_range_verify_batch_dev", "bpp_range_prove", "bpp_range_verify",
     "bpp_wip_prove", "bpp_wip_verify", "bpp_range_verify_batch_fs", "bpp_range_verify_batch_rlc", "bpp_range_verify_batch_rlc_dev", "bpp_range_verify_batch_fs_dev", "bpp_range_prove_begin", "bpp_range_prove_step",
-    "bpp_range_prove_finish", "bpp_prove_session_rounds", "bpp_prove_session_free", "bpp_int_peak_probe", "bpp_fp64_peak_probe", "bpp_fe_mul_probe", "bpp_hot_kernel_stats", "bpp_debug_op",
+    "bpp_range_prove_finish", "bpp_prove_session_rounds", "bpp_prove_session_free", "bpp_int_peak_probe", "bpp_fp64_peak_probe", "bpp_fe_mul_probe", "bpp_hot_kernel_stats", "bpp_trace", "bpp_trace_dump", "bpp_debug_op",
 ]
 
 
@@ -99,6 +99,8 @@ def load() -> C.CDLL:
     L.bpp_fp64_peak_probe.argtypes = [vp, C.POINTER(C.c_double)]
     L.bpp_fe_mul_probe.argtypes = [vp, i, i, i, C.POINTER(C.c_double)]
     L.bpp_hot_kernel_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64), i]
+    L.bpp_trace.argtypes = [vp, i]
+    L.bpp_trace_dump.argtypes = [vp, C.c_char_p, sz]
     L.bpp_debug_op.argtypes = [vp, i, i, sz, u8p, u8p, u8p, u8p]
     _LIB = L
     return L

@@ -99,6 +99,19 @@ class Context:
         self.check(self.lib.bpp_fp64_peak_probe(self.h, rates), "fp64_peak_probe")
         return dict(dfma_per_s=rates[0], f5_mul_per_s=rates[1])
 
+    def trace(self, on: bool):
+        self.check(self.lib.bpp_trace(self.h, 1 if on else 0), "trace")
+
+    def trace_dump(self):
+        """[(stream, start_us, end_us, kernel)] of the launches recorded since trace(True), over both streams."""
+        buf = C.create_string_buffer(1 << 22)
+        self.lib.bpp_trace_dump(self.h, buf, len(buf))
+        out = []
+        for line in buf.value.decode().splitlines():
+            s_, a, b, name = line.split(" ", 3)
+            out.append((int(s_), float(a), float(b), name))
+        return out
+
     def hot_kernel_stats(self, reset=False):
         ms, n = C.c_double(), C.c_uint64()
         self.check(self.lib.bpp_hot_kernel_stats(self.h, C.byref(ms), C.byref(n), 1 if reset else 0), "hot_kernel_stats")

@@ -452,4 +452,34 @@ int bpp_hot_kernel_stats(bpp_ctx* ctx, double* ms, uint64_t* launches, int reset
   return BPP_OK;
 }
 
+int bpp_trace(bpp_ctx* ctx, int on) {
+  BPP_ENTER(ctx);
+  ctx->trace_on = on != 0;
+  return BPP_OK;
+}
+int bpp_trace_dump(bpp_ctx* ctx, char* buf, size_t cap) {
+  if (!ctx) return -1;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  if (ctx->aux_stream) cudaStreamSynchronize(ctx->aux_stream);
+  std::string out;
+  const int n = (int)ctx->trace.size();
+  for (auto& r : ctx->trace) {
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, ctx->trace[0].e0, r.e0);
+    cudaEventElapsedTime(&b, ctx->trace[0].e0, r.e1);
+    char line[256];
+    snprintf(line, sizeof line, "%d %.1f %.1f %s\n", r.aux, a * 1e3, b * 1e3, r.name);
+    out += line;
+  }
+  for (auto& r : ctx->trace) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+  ctx->trace.clear();
+  if (buf && cap) {
+    size_t k = out.size() < cap - 1 ? out.size() : cap - 1;
+    memcpy(buf, out.data(), k);
+    buf[k] = 0;
+  }
+  return n;
+}
+
 }  // extern "C"

@@ -37,7 +37,7 @@ struct DevBuf {
 enum BufId {
   B_SCALARS, B_PIDX, B_JOBSTART, B_COUNTS, B_OFFSETS, B_CURSOR, B_TILES, B_SORTED, B_PERM, B_BINS, B_BUCKETS, B_CHUNK_S, B_CHUNK_T,
   B_WINDOWS, B_FIXEDRES, B_RESULTS, B_DYN, B_DYN_OK, B_IN0, B_IN1, B_IN2, B_IN3, B_OUT0, B_PARAMS, B_TAB0, B_TAB1, B_TAB2, B_TAB3, B_TAB4,
-  B_TAB5, B_TAB6, B_WORK0, B_WORK1, B_WORK2, B_FLAGS, B_FLAGS2, B_EXT, B_GIANT_CTL, B_GIANT_ITEMS, B_GIANT_KEYS, B_GIANT_PART, B_DYNF, B_COUNT_
+  B_TAB5, B_TAB6, B_WORK0, B_WORK1, B_WORK2, B_FLAGS, B_FLAGS2, B_EXT, B_GIANT_CTL, B_GIANT_ITEMS, B_GIANT_KEYS, B_GIANT_PART, B_DYNF, B_CHUNK_S2, B_CHUNK_T2, B_COUNT_
 };
 
 }  // namespace bpp
@@ -51,6 +51,7 @@ struct bpp_ctx {
   // (Msm::run): its Horner pass is a chain of ~SCALAR_BITS dependent doublings per job, latency-bound on a few warps
   bpp::DevBuf buf2[bpp::B_COUNT_];
   cudaStream_t aux_stream = nullptr;
+  bool aux_swapped = false;  // ctx->stream currently names the auxiliary stream (Msm::aux_enter / swap_scratch)
   cudaEvent_t aux_fork = nullptr, aux_join = nullptr;
   std::string err;
   uint64_t launches = 0;
@@ -70,6 +71,11 @@ struct bpp_ctx {
   uint32_t tab_kind = 0;     // 1 verifier tables, 2 prover tables
   uint32_t tab_shape[5] = {0, 0, 0, 0, 0};  // N, n, m, mode, curve
   const void* tab_pk = nullptr;
+  // launch tracer (bpp_trace): one event pair per BPP_LAUNCH on whichever stream it went to; the timeline of a call over
+  // both streams is read back by bpp_trace_dump. Off by default (two event records per launch when on).
+  struct TraceRec { const char* name; cudaEvent_t e0, e1; int aux; };
+  bool trace_on = false;
+  std::vector<TraceRec> trace;
   std::vector<struct bpp_prove_session*> session_pool;  // at most two parked sessions (cudaMalloc/cudaFree cost milliseconds each)
   size_t tab_caps = 0;       // capacities of the table buffers when they were filled (a re-allocation invalidates them)
 };
@@ -125,9 +131,15 @@ namespace bpp {
   } while (0)
 #define BPP_LAUNCH(kernel, grid, block, smem, ...)                         \
   do {                                                                     \
+    cudaEvent_t _t0 = nullptr, _t1 = nullptr;                              \
+    if (ctx->trace_on) { cudaEventCreate(&_t0); cudaEventCreate(&_t1); cudaEventRecord(_t0, ctx->stream); } \
     kernel<<<(grid), (block), (smem), ctx->stream>>>(__VA_ARGS__);         \
     ctx->launches++;                                                       \
     BPP_CK(cudaGetLastError());                                            \
+    if (ctx->trace_on) {                                                   \
+      cudaEventRecord(_t1, ctx->stream);                                   \
+      ctx->trace.push_back({#kernel, _t0, _t1, ctx->aux_swapped ? 1 : 0}); \
+    }                                                                      \
   } while (0)
 
 // block roles of the hybrid accumulation kernel: bit i set = blocks with (index % 4) == i run on the FP64 pipe. 0 (the
@@ -191,9 +203,10 @@ struct Msm {
     BPP_CK(cudaEventRecord(ctx->aux_fork, ctx->stream));
     BPP_CK(cudaStreamWaitEvent(ctx->aux_stream, ctx->aux_fork, 0));
     std::swap(ctx->stream, ctx->aux_stream);
+    ctx->aux_swapped = !ctx->aux_swapped;
     return BPP_OK;
   }
-  static void aux_leave(bpp_ctx* ctx) { std::swap(ctx->stream, ctx->aux_stream); }
+  static void aux_leave(bpp_ctx* ctx) { std::swap(ctx->stream, ctx->aux_stream); ctx->aux_swapped = !ctx->aux_swapped; }
 
   // Runs the segmented MSM over terms already in ctx->buf[B_SCALARS] / [B_PIDX]. Terms with point index < n_fixed use the
   // window tables `wtab` (cA, WA from the public key); the others index `dyn` (per-call affine table) at idx - n_fixed and
@@ -212,10 +225,11 @@ struct Msm {
     BPP_CK(cudaEventRecord(ctx->aux_fork, ctx->stream));
     BPP_CK(cudaStreamWaitEvent(ctx->aux_stream, ctx->aux_fork, 0));
     static const BufId scratch[] = {B_COUNTS, B_OFFSETS, B_CURSOR, B_TILES, B_SORTED, B_PERM, B_BINS, B_BUCKETS, B_CHUNK_S, B_CHUNK_T, B_WINDOWS,
-                                    B_FIXEDRES, B_RESULTS, B_GIANT_CTL, B_GIANT_ITEMS, B_GIANT_KEYS, B_GIANT_PART, B_DYNF};
+                                    B_FIXEDRES, B_RESULTS, B_GIANT_CTL, B_GIANT_ITEMS, B_GIANT_KEYS, B_GIANT_PART, B_DYNF, B_CHUNK_S2, B_CHUNK_T2};
     auto swap_scratch = [&]() {
       for (BufId id : scratch) std::swap(ctx->buf[id], ctx->buf2[id]);
       std::swap(ctx->stream, ctx->aux_stream);
+      ctx->aux_swapped = !ctx->aux_swapped;
     };
     swap_scratch();
     const bool timing = ctx->hot_timing;
@@ -225,8 +239,11 @@ struct Msm {
     const uint32_t* part_b = ctx->buf[B_RESULTS].as<uint32_t>();
     if (rc == BPP_OK && cudaEventRecord(ctx->aux_join, ctx->stream) != cudaSuccess) { ctx->err = "cudaEventRecord(aux_join)"; rc = BPP_ERR_CUDA; }
     swap_scratch();
-    BPP_TRY(rc);
-    BPP_TRY(run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, 0, 1, wtab_f, dyn_f));
+    // whatever was queued on the auxiliary stream shares B_SCALARS / B_DYN with the next call: on any failure from here on
+    // wait for it before returning
+    if (rc != BPP_OK) { cudaStreamSynchronize(ctx->aux_stream); return rc; }
+    rc = run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, 0, 1, wtab_f, dyn_f);
+    if (rc != BPP_OK) { cudaStreamSynchronize(ctx->aux_stream); return rc; }
     BPP_CK(cudaStreamWaitEvent(ctx->stream, ctx->aux_join, 0));
     BPP_LAUNCH(msm_join_kernel<C>, ceil_div(n_jobs, 128), 128, 0, n_jobs, ctx->buf[B_RESULTS].as<uint32_t>(), part_b);
     return BPP_OK;
@@ -254,11 +271,16 @@ struct Msm {
     }
     pl.wtab_points = pl.WA * pl.n_fixed;
     const uint32_t KPJ = pl.NBA + pl.WB * pl.NBB;
+    // per-job sort in shared memory (one block per job) when the job's key space fits AND there are enough jobs to fill the
+    // chip or the jobs are small; one or a few large jobs (a raw MSM of 2^12 points took longer than one of 2^14 when a
+    // single 512-thread block sorted it) go through the grid-wide histogram / scan / scatter instead
+    const uint32_t Wmax = pl.WA > pl.WB ? pl.WA : pl.WB;
+    const bool job_sort = KPJ <= 12288 && (n_jobs >= 16 || (uint64_t)n_terms * Wmax / n_jobs <= 16384);
     pl.sort_mult = 1;
     if (pl.NBA) {
       for (int i = 0; i < 8; i++) pl.order[i] = C::order_word(i);
       // split digits (msm.cuh): only on the per-job shared-memory sort, and only where some job can be small enough
-      if (KPJ <= 12288 && pl.cA >= 8 && getenv("BPP_NO_SPLIT") == nullptr) {
+      if (job_sort && pl.cA >= 8 && getenv("BPP_NO_SPLIT") == nullptr) {
         const uint32_t k2 = pl.NBA / 9, k3 = pl.NBA / 64;
         if (!uniform || uniform <= k2) {
           pl.k2 = k2; pl.k3 = k3;
@@ -331,11 +353,12 @@ struct Msm {
     BPP_CK(cudaMemsetAsync(bins, 0, 256 * 4, ctx->stream));
     BPP_CK(cudaMemsetAsync(gctl, 0, 16, ctx->stream));
     if (n_entries >= (1ull << 32)) { ctx->err = "msm: too many bucket entries for one call"; return BPP_ERR_LENGTH; }
-    if (KPJ <= 12288) {
+    if (job_sort) {
       // small key space per job: one block sorts a whole job in shared memory
       auto k = msm_sort_job_kernel<0>;
       const size_t smem = (size_t)KPJ * 4;
-      if (smem > 48 * 1024) BPP_CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      // the kernel also has 64 B of static shared memory: opt in before dynamic + static can pass the 48 KB default
+      if (smem > 40 * 1024) BPP_CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       BPP_LAUNCH(k, n_jobs, SJ_THREADS, smem, pl, dyn_per_job, scalars, pidx, d_job_start, offsets, counts, sorted);
     } else {
       BPP_CK(cudaMemsetAsync(counts, 0, (size_t)n_keys * 4, ctx->stream));
@@ -383,19 +406,41 @@ struct Msm {
     if (chunks4) BPP_LAUNCH((msm_reduce_chunks_kernel<C, 4>), ceil_div(pl.n_chunks, 128), 128, 0, pl, counts, buckets, chunk_S, chunk_T);
     else BPP_LAUNCH((msm_reduce_chunks_kernel<C, 1>), ceil_div(pl.n_chunks, 128), 128, 0, pl, counts, buckets, chunk_S, chunk_T);
     auto sets = [&](uint32_t n_sets, uint32_t first_chunk, uint32_t q, uint32_t NB, uint32_t* out) -> int {
-      const uint32_t cps = NB / q;  // chunks per set
+      uint32_t cps = NB / q;  // chunks per set
+      const uint32_t* cS = chunk_S + (size_t)first_chunk * C::EXT_WORDS;
+      const uint32_t* cT = chunk_T + (size_t)first_chunk * C::EXT_WORDS;
+      // few sets with many chunks each (one large MSM): merge groups of chunks into heavier chunks with whole-chip kernels
+      // until a set is 128 chunks, so that the set kernel below has no serial walk left (it was 0.36 ms of a 2^22-point MSM)
+      if (n_sets < 256 && cps > 128) {
+        BPP_CK(ctx->buf[B_CHUNK_S2].ensure((size_t)n_sets * (cps / 2) * C::EXT_WORDS * 4));
+        BPP_CK(ctx->buf[B_CHUNK_T2].ensure((size_t)n_sets * (cps / 2) * C::EXT_WORDS * 4));
+        uint32_t* pingS = ctx->buf[B_CHUNK_S2].as<uint32_t>();
+        uint32_t* pingT = ctx->buf[B_CHUNK_T2].as<uint32_t>();
+        uint32_t* pongS = chunk_S + (size_t)first_chunk * C::EXT_WORDS;  // the consumed input of the previous level
+        uint32_t* pongT = chunk_T + (size_t)first_chunk * C::EXT_WORDS;
+        while (cps > 128) {
+          const uint32_t per = cps / 128 < 8 ? cps / 128 : 8, groups = n_sets * (cps / per);
+          BPP_LAUNCH(msm_reduce_level_kernel<C>, ceil_div(groups, 128), 128, 0, groups, q, per, cS, cT, pingS, pingT);
+          cS = pingS; cT = pingT;
+          std::swap(pingS, pongS); std::swap(pingT, pongT);
+          cps /= per; q *= per;
+        }
+      }
       // threads per set: the group's suffix scan costs log2(tps) additions in EVERY thread, so many sets get few threads
       // each (serial running sums over `per` chunks, work-efficient) and few sets get many (latency); ~32 K threads in all
       uint32_t tps = 1;
       while (tps < 128 && tps < cps && (uint64_t)tps * n_sets < 32768) tps <<= 1;
       const uint32_t per = cps / tps;
-      BPP_LAUNCH(msm_reduce_sets_kernel<C>, ceil_div(n_sets, 128 / tps), 128, 0, n_sets, first_chunk, q, per, tps, chunk_S, chunk_T, out);
+      BPP_LAUNCH(msm_reduce_sets_kernel<C>, ceil_div(n_sets, 128 / tps), 128, 0, n_sets, 0u, q, per, tps, cS, cT, out);
       return BPP_OK;
     };
     if (pl.NBA) BPP_TRY(sets(n_jobs, 0, pl.qA, pl.NBA, pl.WB ? fixedres : results));
     if (pl.WB) {
       BPP_TRY(sets(n_setsB, pl.chunksA, pl.qB, pl.NBB, windows));
-      BPP_LAUNCH(msm_combine_kernel<C>, ceil_div(n_jobs, 128), 128, 0, pl, windows, fixedres, results);
+      // jobs per warp: as few as keeps about two warps on every SM sub-partition (148 x 4)
+      uint32_t lanes = ceil_div(n_jobs, 148 * 4 * 2);
+      lanes = lanes > 32 ? 32 : lanes;
+      BPP_LAUNCH(msm_combine_kernel<C>, ceil_div(n_jobs, lanes), 32, 0, pl, lanes, windows, fixedres, results);
     }
     return BPP_OK;
   }

@@ -651,6 +651,34 @@ msm_reduce_chunks_kernel(MsmPlan pl, const uint32_t* __restrict__ counts, const 
   store_words<C::EXT_WORDS>(chunk_T + (size_t)id * C::EXT_WORDS, sum);
 }
 
+// level 1b — thread per group of `per` consecutive chunks of weight q: (S', T') of the group as one chunk of weight q * per,
+//   S' = sum_k S_k,  T' = sum_k T_k + q * sum_k k * S_k.
+// Run before the set reduction when there are few sets with many chunks each (one large MSM): the set kernel then has no
+// serial walk left and the work of this level spreads over the whole chip.
+template <class C>
+__global__ void __launch_bounds__(128)
+msm_reduce_level_kernel(uint32_t n_groups, uint32_t q, uint32_t per, const uint32_t* __restrict__ in_S, const uint32_t* __restrict__ in_T,
+                        uint32_t* __restrict__ out_S, uint32_t* __restrict__ out_T) {
+  const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_groups) return;
+  const size_t c0 = (size_t)g * per;
+  typename C::Ext S, T, acc, p;
+  load_words<C::EXT_WORDS>(S, in_S + (c0 + per - 1) * C::EXT_WORDS);
+  load_words<C::EXT_WORDS>(T, in_T + (c0 + per - 1) * C::EXT_WORDS);
+  acc = S;  // sum_k k * S_k as running suffix sums: after the loop acc = sum_{t >= 1} sum_{u >= t} S_u
+  for (int k = (int)per - 2; k >= 0; k--) {
+    load_words<C::EXT_WORDS>(p, in_T + (c0 + k) * C::EXT_WORDS);
+    C::add(T, p);
+    load_words<C::EXT_WORDS>(p, in_S + (c0 + k) * C::EXT_WORDS);
+    C::add(S, p);
+    if (k > 0) C::add(acc, S);
+  }
+  C::dbl_n(acc, 31u - __clz(q));
+  C::add(T, acc);
+  store_words<C::EXT_WORDS>(out_S + (size_t)g * C::EXT_WORDS, S);
+  store_words<C::EXT_WORDS>(out_T + (size_t)g * C::EXT_WORDS, T);
+}
+
 // level 2 — a group of `tps` threads per bucket set (128-thread blocks, 128 / tps sets per block); each thread owns
 // `per` consecutive chunks, then the group does a suffix scan and a tree sum in shared memory:
 //   set total = sum_t [ T'_t + (q * per) * t * S'_t ],   sum_t t * S'_t = sum_{t >= 1} (sum_{u >= t} S'_u)
@@ -677,7 +705,7 @@ msm_reduce_sets_kernel(uint32_t n_sets, uint32_t first_chunk, uint32_t q, uint32
       load_words<C::EXT_WORDS>(p, chunk_S + (c0 + k) * C::EXT_WORDS);
       if (k > 0) { C::add(S, p); C::add(acc, S); }
       else {
-        for (uint32_t s = q; s > 1 && per > 1; s >>= 1) C::dbl(acc);
+        if (per > 1) C::dbl_n(acc, 31u - __clz(q));
         if (per > 1) C::add(T, acc);
         C::add(S, p);
       }
@@ -696,7 +724,7 @@ msm_reduce_sets_kernel(uint32_t n_sets, uint32_t first_chunk, uint32_t q, uint32
   }
   // V_t = T'_t + (q * per) * R_t for t >= 1
   if (lane >= 1) {
-    for (uint32_t s = q * per; s > 1; s >>= 1) C::dbl(S);
+    C::dbl_n(S, 31u - __clz(q * per));
     C::add(T, S);
   }
   *mine = T;
@@ -712,18 +740,22 @@ msm_reduce_sets_kernel(uint32_t n_sets, uint32_t first_chunk, uint32_t q, uint32
   if (live && lane == 0) store_words<C::EXT_WORDS>(out + (size_t)set * C::EXT_WORDS, T);
 }
 
-// thread per job: Horner over the generic windows, plus the fixed-base part
+// Horner over the generic windows, plus the fixed-base part: one job per thread, but only `lanes` threads of each
+// 32-thread block are used. The chain is ~SCALAR_BITS dependent doublings; a warp instruction costs its sub-partition's
+// multiply pipe the same whether 1 or 32 lanes are active, so few jobs per warp on many warps (spread over all 592
+// sub-partitions) finish sooner than the same jobs packed 32 to a warp on a few SMs.
 template <class C>
-__global__ void __launch_bounds__(128)
-msm_combine_kernel(MsmPlan pl, const uint32_t* __restrict__ windows, const uint32_t* __restrict__ fixed_res, uint32_t* __restrict__ results) {
-  uint32_t job = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(32)
+msm_combine_kernel(MsmPlan pl, uint32_t lanes, const uint32_t* __restrict__ windows, const uint32_t* __restrict__ fixed_res, uint32_t* __restrict__ results) {
+  if (threadIdx.x >= lanes) return;
+  uint32_t job = blockIdx.x * lanes + threadIdx.x;
   if (job >= pl.n_jobs) return;
   typename C::Ext acc, p;
   if (pl.WB) {
     const uint32_t* base = windows + (size_t)job * pl.WB * C::EXT_WORDS;
     load_words<C::EXT_WORDS>(acc, base + (size_t)(pl.WB - 1) * C::EXT_WORDS);
     for (int w = (int)pl.WB - 2; w >= 0; w--) {
-      for (uint32_t k = 0; k < pl.cB; k++) C::dbl(acc);
+      C::dbl_n(acc, pl.cB);
       load_words<C::EXT_WORDS>(p, base + (size_t)w * C::EXT_WORDS);
       C::add(acc, p);
     }
@@ -760,7 +792,7 @@ __global__ void wtab_build_kernel(uint32_t n, uint32_t c, uint32_t W, const uint
   store_words<C::AFF_WORDS>(wtab + (size_t)i * C::AFF_WORDS, q);
   C::aff_to_ext(p, q);
   for (uint32_t w = 1; w < W; w++) {
-    for (uint32_t k = 0; k < c; k++) C::dbl(p);
+    C::dbl_n(p, c);
     C::to_aff(q, p);
     store_words<C::AFF_WORDS>(wtab + ((size_t)w * n + i) * C::AFF_WORDS, q);
   }

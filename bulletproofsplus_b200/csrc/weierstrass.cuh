@@ -58,6 +58,7 @@ struct Weierstrass {
   }
   BPP_DEV static bool is_identity(const Ext& p) { return p.ZZ.is_zero(); }
   BPP_DEV static void neg(Ext& p) { p.Y = F::neg(p.Y); }
+  BPP_DEV static void dbl_n(Ext& p, uint32_t k) { for (uint32_t i = 0; i < k; i++) dbl(p); }
 
   // 2 * (x, y) for an affine point
   BPP_DEV static void mdbl(Ext& p, const F& x, const F& y) {

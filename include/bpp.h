@@ -193,6 +193,13 @@ int bpp_fp64_peak_probe(bpp_ctx* ctx, double* rates2);
  * count, since the last reset */
 int bpp_hot_kernel_stats(bpp_ctx* ctx, double* ms, uint64_t* launches, int reset);
 
+/* launch tracer (development / measurement aid): bpp_trace(ctx, 1) starts recording one CUDA-event pair per kernel launch
+ * on whichever of the context's two streams it goes to, bpp_trace(ctx, 0) stops. bpp_trace_dump synchronises and writes
+ * one line per recorded launch, "<stream 0|1> <start_us> <end_us> <kernel>", times relative to the first record, into buf
+ * (NUL-terminated, truncated to cap); returns the number of records and clears them. */
+int bpp_trace(bpp_ctx* ctx, int on);
+int bpp_trace_dump(bpp_ctx* ctx, char* buf, size_t cap);
+
 /* test surface: element-wise device arithmetic (field ops 0-4, group ops 10-14, scalar-field ops 20-23) */
 int bpp_debug_op(bpp_ctx* ctx, int curve, int op, size_t n, const uint8_t* a, const uint8_t* b, uint8_t* out, uint8_t* ok);
 
