@@ -221,6 +221,24 @@ template <class G> struct Ctx {
   }
 };
 
+// B2 hook for Ristretto255: oracle points -> 128-byte extended coordinates -> baseline_msm.cpp -> oracle point
+extern "C" int b2_msm_ext(size_t k, const uint8_t* scalars, const uint8_t* points, int threads, uint8_t* out);
+int g_b2_threads = 1;
+Ristretto::Point b2_hook(const std::vector<Ristretto::Sc>& sc, const std::vector<Ristretto::Point>& pts) {
+  const size_t k = sc.size();
+  std::vector<uint8_t> sb(32 * k), pb(128 * k);
+  for (size_t i = 0; i < k; i++) {
+    sc[i].to_bytes_le(&sb[32 * i], 32);
+    pts[i].X.to_bytes_le(&pb[128 * i], 32); pts[i].Y.to_bytes_le(&pb[128 * i + 32], 32);
+    pts[i].Z.to_bytes_le(&pb[128 * i + 64], 32); pts[i].T.to_bytes_le(&pb[128 * i + 96], 32);
+  }
+  uint8_t out[128];
+  b2_msm_ext(k, sb.data(), pb.data(), g_b2_threads, out);
+  Ristretto::Point r;
+  r.X.from_bytes_le(out, 32); r.Y.from_bytes_le(out + 32, 32); r.Z.from_bytes_le(out + 64, 32); r.T.from_bytes_le(out + 96, 32);
+  return r;
+}
+
 template <class F> int guard(F f) {
   try { return f(); } catch (const std::exception&) { return 3; }
 }
@@ -237,6 +255,13 @@ template <class F> int guard(F f) {
 
 extern "C" {
 
+// CPU baselines only (bench.py): backend 0 = the reference's per-term loop (B1, default), 1 = bucket MSM of baseline_msm.cpp
+// (B2, Ristretto255 only) with `threads` host threads inside each MSM. Process-wide; not thread-safe against running calls.
+void orc_set_msm_backend(int backend, int threads) {
+  MsmHook<Ristretto>::fn() = b2_hook;
+  g_b2_threads = threads < 1 ? 1 : threads;
+  msm_backend() = backend;
+}
 int orc_point_bytes(int curve) { return curve == 0 ? 32 : curve == 1 ? 64 : curve == 2 ? 96 : -1; }
 int orc_pk_new(int curve, size_t len, uint8_t* g, uint8_t* h, uint8_t* G, uint8_t* H) { DISPATCH(curve, pk_new(len, g, h, G, H)) }
 int orc_commit(int curve, size_t count, const uint64_t* v, const uint8_t* gamma, uint8_t* out) { DISPATCH(curve, commit(count, v, gamma, out)) }

@@ -52,6 +52,8 @@ class Oracle:
         sz, u8p, u64p = C.c_size_t, C.c_char_p, C.POINTER(C.c_uint64)
         pp = C.POINTER(OrcParams)
         L.orc_pk_new.argtypes = [C.c_int, sz, u8p, u8p, u8p, u8p]
+        L.orc_set_msm_backend.argtypes = [C.c_int, C.c_int]
+        L.orc_set_msm_backend.restype = None
         L.orc_commit.argtypes = [C.c_int, sz, u64p, u8p, u8p]
         L.orc_msm_naive.argtypes = [C.c_int, sz, u8p, u8p, u8p]
         L.orc_scalar_mul.argtypes = [C.c_int, u8p, u8p, u8p]
@@ -64,6 +66,10 @@ class Oracle:
         L.orc_range_verify.argtypes = [C.c_int, sz, sz, u8p, u8p, sz, pp]
         L.orc_wip_prove.argtypes = [C.c_int, sz, u8p, u8p, u8p, u8p, pp, u8p, C.POINTER(sz)]
         L.orc_wip_verify.argtypes = [C.c_int, sz, u8p, u8p, u8p, u8p, sz, u8p, u8p, u8p, u8p, sz, pp]
+
+    def set_msm_backend(self, backend: int, threads: int = 1):
+        """CPU baselines only: 0 = the reference's per-term MulVec loop (B1), 1 = bucket MSM (B2, Ristretto255)."""
+        self.lib.orc_set_msm_backend(backend, threads)
 
     @staticmethod
     def _chk(rc, what):

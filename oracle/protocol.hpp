@@ -33,6 +33,15 @@ struct Params {
   }
 };
 
+// Baseline switch (NOT part of the restatement): when a group installs a hook and the process-wide backend is 1
+// (orc_set_msm_backend), MulVec::calculate hands MSMs of >= 16 terms to it — B2, the bucket MSM of baseline_msm.cpp — instead
+// of running the reference's per-term loop. Default 0: every parity test runs the literal loop below.
+inline int& msm_backend() { static int b = 0; return b; }
+template <class G> struct MsmHook {
+  typedef typename G::Point (*Fn)(const std::vector<typename G::Sc>&, const std::vector<typename G::Point>&);
+  static Fn& fn() { static Fn f = nullptr; return f; }
+};
+
 // ---- src/bls12_381/building_block/mulvec.rs:13-53 ------------------------------------
 template <class G>
 struct MulVec {
@@ -48,6 +57,7 @@ struct MulVec {
   Point calculate() const {
     if (scalars.size() != points.size())
       throw std::runtime_error("mulvec: lengths of scalars and points must match");
+    if (msm_backend() == 1 && MsmHook<G>::fn() && scalars.size() >= 16) return MsmHook<G>::fn()(scalars, points);
     Point sum = G::identity();
     for (size_t i = 0; i < scalars.size(); i++) {
       Point p = scalar_mul<G>(points[i], scalars[i]);

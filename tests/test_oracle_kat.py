@@ -252,3 +252,121 @@ def test_oracle_vs_checker_grid(oracle, curve, n, m):
         vs2 = [2**n] + vs[1:]
         proof2 = oracle.range_prove(curve, n, m, vs2, gam)
         assert oracle.range_verify(curve, n, m, oracle.commit(curve, vs2, gam), proof2) == 1
+
+
+# ------------------------------------------------------------------ BASELINE.json sizes: the C++ oracle is never the only witness
+def _check_range_against_checker(oracle, curve, n, m, seed):
+    q = pyref.CURVES[curve]["order"]
+    pb = pyref.CURVES[curve]["pb"]
+    rng = random.Random(seed)
+    vs = [rng.randrange(0, 2**31) for _ in range(m)]
+    gam = [rng.randrange(q) for _ in range(m)]
+    rounds = (n * m).bit_length() - 1
+    chk = ec.Checker(q)
+    exp = chk.range_prove(n, m, vs, gam)
+    proof = oracle.range_prove(curve, n, m, vs, gam)
+    got = _split_proof(proof, pb, rounds)
+    mul = lambda k: oracle.scalar_mul(curve, k % q)
+    assert got["A"] == mul(exp.A)
+    assert got["L"] == [mul(x) for x in exp.L] and got["R"] == [mul(x) for x in exp.R]
+    assert got["wipA"] == mul(exp.wipA) and got["wipB"] == mul(exp.wipB)
+    assert (got["r_prime"], got["s_prime"], got["d_prime"]) == (exp.r_prime, exp.s_prime, exp.d_prime)
+    # both restatements accept it, and both reject r' + 1
+    V_dlogs = [chk.commit(v, g) for v, g in zip(vs, gam)]
+    assert chk.range_verify(n, m, V_dlogs, exp)
+    return vs, gam, proof, exp, V_dlogs
+
+
+def test_oracle_vs_checker_n64_m16(oracle):
+    """config 1 / the headline shape (n=64, m=16): proof points as discrete logs, Ristretto255."""
+    vs, gam, proof, exp, V_dlogs = _check_range_against_checker(oracle, R, 64, 16, 6416)
+    V = oracle.commit(R, vs, gam)
+    assert oracle.range_verify(R, 64, 16, V, proof) == 0
+    bad = bytearray(proof)
+    bad[(2 * 10 + 3) * 32] ^= 1
+    assert oracle.range_verify(R, 64, 16, V, bytes(bad)) == 1
+    import copy
+    exp_bad = copy.copy(exp)
+    exp_bad.r_prime = (exp.r_prime + 1) % pyref.CURVES[R]["order"]
+    assert not ec.Checker(pyref.CURVES[R]["order"]).range_verify(64, 16, V_dlogs, exp_bad)
+
+
+def test_oracle_vs_checker_n64_m64(oracle):
+    """config 3 (n=64, m=64, N=4096, 8285-term verifier MSM). The oracle's verify runs on the B2 bucket MSM here (its naive loop
+    takes seconds at this size and is covered at (64,16)); the prover runs the literal loops."""
+    vs, gam, proof, exp, V_dlogs = _check_range_against_checker(oracle, R, 64, 64, 6464)
+    V = oracle.commit(R, vs, gam)
+    oracle.set_msm_backend(1, 1)
+    try:
+        assert oracle.range_verify(R, 64, 64, V, proof) == 0
+    finally:
+        oracle.set_msm_backend(0, 1)
+
+
+def test_oracle_vs_checker_wip_4096(oracle):
+    """config 2: standalone weighted-inner-product argument over 2^12 generators."""
+    q = pyref.CURVES[R]["order"]
+    N, rounds = 4096, 12
+    rng = random.Random(4096)
+    a = [rng.randrange(q) for _ in range(N)]
+    b = [rng.randrange(q) for _ in range(N)]
+    ypow = [pow(12, i + 1, q) for i in range(N)]
+    gamma = rng.randrange(q)
+    enc = lambda xs: b"".join(int(x).to_bytes(32, "little") for x in xs)
+    prm = ec.Params.reference(2, rounds)
+    Ls, Rs, wA, wB, rp, sp, dp = ec.Checker(q).wip_prove(N, a, b, ypow, gamma, prm)
+    proof = oracle.wip_prove(R, N, enc(a), enc(b), enc(ypow), gamma)
+    pts = [proof[i * 32:(i + 1) * 32] for i in range(2 * rounds + 2)]
+    mul = lambda k: oracle.scalar_mul(R, k % q)
+    assert pts[:rounds] == [mul(x) for x in Ls] and pts[rounds:2 * rounds] == [mul(x) for x in Rs]
+    assert pts[2 * rounds] == mul(wA) and pts[2 * rounds + 1] == mul(wB)
+    sc = proof[(2 * rounds + 2) * 32:]
+    assert [int.from_bytes(sc[i * 32:(i + 1) * 32], "little") for i in range(3)] == [rp, sp, dp]
+
+
+# ------------------------------------------------------------------ B2, the bucket-MSM CPU baseline (oracle/baseline_msm.cpp)
+def test_b2_bucket_msm_matches_exponent_value(oracle):
+    q = pyref.CURVES[R]["order"]
+    rng = random.Random(22)
+    oracle.set_msm_backend(1, 1)
+    try:
+        for k, kind in ((16, "rand"), (300, "rand"), (1500, "rand"), (257, "edge")):
+            ks = [rng.randrange(q) for _ in range(k)]
+            ss = [rng.randrange(q) for _ in range(k)]
+            if kind == "edge":
+                ss[:6] = [0, 1, q - 1, (q - 1) // 2, (q + 1) // 2, 2**252]
+                ks[10] = ks[11]            # duplicate base
+                ks[12] = (q - ks[13]) % q  # negated base
+                ss[20:40] = [ss[20]] * 20  # one bucket collects many terms
+            pts = b"".join(oracle.scalar_mul(R, x) for x in ks)
+            want = oracle.scalar_mul(R, sum(a * b for a, b in zip(ks, ss)) % q)
+            assert oracle.msm_naive(R, b"".join(s.to_bytes(32, "little") for s in ss), pts) == want, (k, kind)
+        oracle.set_msm_backend(1, 4)  # point-range split over threads
+        k = 1500
+        ks = [rng.randrange(q) for _ in range(k)]
+        ss = [rng.randrange(q) for _ in range(k)]
+        pts = b"".join(oracle.scalar_mul(R, x) for x in ks)
+        want = oracle.scalar_mul(R, sum(a * b for a, b in zip(ks, ss)) % q)
+        assert oracle.msm_naive(R, b"".join(s.to_bytes(32, "little") for s in ss), pts) == want
+    finally:
+        oracle.set_msm_backend(0, 1)
+
+
+def test_b2_protocol_equals_b1(oracle):
+    """With the B2 MSM switched in, prove is byte-identical and verify verdicts equal the literal restatement's."""
+    q = pyref.CURVES[R]["order"]
+    rng = random.Random(5)
+    n, m = 32, 4
+    vs = [rng.randrange(2**31) for _ in range(m)]
+    gam = [rng.randrange(q) for _ in range(m)]
+    proof = oracle.range_prove(R, n, m, vs, gam)
+    V = oracle.commit(R, vs, gam)
+    bad = bytearray(proof)
+    bad[-96] ^= 1
+    want = [oracle.range_verify(R, n, m, V, proof), oracle.range_verify(R, n, m, V, bytes(bad))]
+    oracle.set_msm_backend(1, 1)
+    try:
+        assert oracle.range_prove(R, n, m, vs, gam) == proof
+        assert [oracle.range_verify(R, n, m, V, proof), oracle.range_verify(R, n, m, V, bytes(bad))] == want == [0, 1]
+    finally:
+        oracle.set_msm_backend(0, 1)
