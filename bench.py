@@ -34,6 +34,8 @@ N_BITS, M_AGG = 64, 16
 ELL = 2**252 + 27742317777372353535851937790883648493
 FIELD_MUL_IMAD = 72           # 8x8 schoolbook + 8-limb fold
 MIXED, FULL, DOUBLE = 7, 8, 8  # field multiplies per point operation
+WORKLOAD = ("range-proof batch verify, n=64 bits, m=16 aggregated, Ristretto255, 2089-term MSM per proof "
+            "(BASELINE.json metric config; 2048 proofs/step/GPU on the GPU arm)")
 
 
 def algorithmic_field_muls(n_terms: int, bits: int = 253, MIXED: int = MIXED, FULL: int = FULL, DOUBLE: int = DOUBLE):
@@ -57,8 +59,8 @@ def prng_bytes(seed: int, n: int) -> bytes:
     return bytes(out[:n])
 
 
-def synth_inputs(count: int, seed: int):
-    """values uniform in [0, 2^31) (clear of the `v as i32` quirk), blinders uniform mod ell."""
+def synth_inputs(count: int, seed: int, M_AGG: int = M_AGG):
+    """count * M_AGG values uniform in [0, 2^31) (clear of the `v as i32` quirk) and blinders uniform mod ell."""
     raw = prng_bytes(0xB2000003 + seed, count * M_AGG * 4)
     vs = [int.from_bytes(raw[4 * i:4 * i + 4], "little") & 0x7FFFFFFF for i in range(count * M_AGG)]
     raw = prng_bytes(0xB2000004 + seed, count * M_AGG * 64)
@@ -98,53 +100,119 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def cpu_reference_verify(threads: int, proofs_per_thread: int, seed: int = 0):
-    """The reference's CPU path for verify (n=64, m=16): oracle restatement, naive MulVec::calculate (mulvec.rs:20-33),
-    one independent proof stream per host thread (the reference itself is single-threaded). Returns proofs/s."""
-    from oracle import oracle_lib
-    o = oracle_lib.get()
-    vs, gs = synth_inputs(1, seed)
-    proof = o.range_prove(0, N_BITS, M_AGG, vs, gs)
-    V = o.commit(0, vs, gs)
-    assert o.range_verify(0, N_BITS, M_AGG, V, proof) == 0
+# ------------------------------------------------------------------------------------------------------------------------
+# CPU baselines. B1 = the oracle's literal restatement of the reference (naive MulVec::calculate,
+# mulvec.rs:20-33) — the reference is single-threaded, so ONE thread is "the reference" and all cores (one independent
+# proof stream per thread) is a second figure. B2 = the same protocol code with the bucket MSM of oracle/baseline_msm.cpp
+# switched in under MulVec::calculate ("fair CPU": same algorithm family as the GPU path, 5x51-bit limbs, all cores).
+# The reference itself cannot be built here (no Rust toolchain, mcl_rust un-vendored): kind = "port".
+def _cpu_run(work, threads):
     results = []
 
-    def work():
-        ok = 0
-        for _ in range(proofs_per_thread):
-            ok += o.range_verify(0, N_BITS, M_AGG, V, proof) == 0  # ctypes releases the GIL
-        results.append(ok)
+    def wrap():
+        results.append(work())
 
-    ts = [threading.Thread(target=work) for _ in range(threads)]
+    ts = [threading.Thread(target=wrap) for _ in range(threads)]
     t0 = time.perf_counter()
     for t in ts:
         t.start()
     for t in ts:
         t.join()
-    dt = time.perf_counter() - t0
-    assert sum(results) == threads * proofs_per_thread
-    return threads * proofs_per_thread / dt, dt
+    return time.perf_counter() - t0, results
+
+
+def cpu_verify(threads: int, per_thread: int, backend: int = 0, n: int = N_BITS, m: int = M_AGG, seed: int = 0):
+    """proofs/s of `threads` host threads re-verifying one (n, m) proof per_thread times each (ctypes releases the GIL)."""
+    from oracle import oracle_lib
+    o = oracle_lib.get()
+    vs, gs = synth_inputs(1, seed, m)
+    o.set_msm_backend(0, 1)
+    proof = o.range_prove(0, n, m, vs, gs)
+    V = o.commit(0, vs, gs)
+    o.set_msm_backend(backend, 1)
+    try:
+        assert o.range_verify(0, n, m, V, proof) == 0
+
+        def work():
+            return sum(o.range_verify(0, n, m, V, proof) == 0 for _ in range(per_thread))
+
+        dt, res = _cpu_run(work, threads)
+    finally:
+        o.set_msm_backend(0, 1)
+    assert sum(res) == threads * per_thread
+    return threads * per_thread / dt, dt
+
+
+def cpu_prove(threads: int, per_thread: int, backend: int = 0, n: int = N_BITS, m: int = M_AGG, seed: int = 0):
+    from oracle import oracle_lib
+    o = oracle_lib.get()
+    vs, gs = synth_inputs(1, seed, m)
+    o.set_msm_backend(backend, 1)
+    try:
+        def work():
+            return sum(len(o.range_prove(0, n, m, vs, gs)) > 0 for _ in range(per_thread))
+
+        dt, res = _cpu_run(work, threads)
+    finally:
+        o.set_msm_backend(0, 1)
+    return threads * per_thread / dt, dt
+
+
+def cpu_msm_b2(log2_n: int, threads: int):
+    """points/s of the B2 bucket MSM over 2^log2_n synthetic Ristretto255 points, point-range split over `threads` threads
+    (points and scalars are generated inside liboracle.so; only the MSM is timed)."""
+    from oracle import oracle_lib
+    n = 1 << log2_n
+    dt = oracle_lib.get().b2_bench_msm(n, threads)
+    return n / dt, dt
+
+
+def cpu_baselines(cores: int):
+    """The bounded CPU sample of the default run (about 20 s of wall clock)."""
+    v1, dt1 = cpu_verify(1, 3, 0)
+    vN, dtN = cpu_verify(cores, 2, 0)
+    b2, dtb = cpu_verify(cores, 40, 1)
+    b2_1, dtb1 = cpu_verify(1, 40, 1)
+    p1, dtp = cpu_prove(1, 1, 0)
+    pN, dtpN = cpu_prove(cores, 1, 0)
+    m16, dtm = cpu_msm_b2(16, cores)
+    return {
+        "value": v1, "unit": "proofs/s", "cores": 1, "kind": "port",
+        "sample": f"B1: 3 verifies of one n=64 m=16 Ristretto255 proof on ONE host thread ({dt1:.1f} s) — the oracle's literal restatement of the "
+                  f"reference, naive MulVec::calculate (2089 full scalar multiplications per verify); the reference itself is single-threaded "
+                  f"and cannot be built here (no Rust, mcl_rust un-vendored)",
+        "all_cores": {"value": vN, "unit": "proofs/s", "cores": cores, "sample": f"B1, {cores} threads x 2 verifies, one proof stream per thread ({dtN:.1f} s)"},
+        "b2_fair_cpu": {"value": b2, "unit": "proofs/s", "cores": cores, "one_thread": b2_1,
+                        "sample": f"B2: the same verifier with the bucket MSM of oracle/baseline_msm.cpp (signed-digit Pippenger, 5x51-bit limbs, "
+                                  f"unsigned __int128) under MulVec::calculate; {cores} threads x 40 verifies ({dtb:.1f} s); NOT the reference's algorithm"},
+        "prove": {"value": p1, "unit": "proofs/s", "cores": 1, "all_cores": pN, "sample": f"B1 range_prove n=64 m=16: 1 proof on one thread ({dtp:.1f} s), "
+                                                                                         f"{cores} threads x 1 ({dtpN:.1f} s)"},
+        "msm_b2_2p16": {"value": m16, "unit": "points/s", "cores": cores, "sample": f"B2 bucket MSM over 2^16 Ristretto255 points, point-range split ({dtm:.2f} s)"},
+    }
 
 
 def run_reference(args, rank):
+    """--impl reference: B1 on ONE thread (the reference is single-threaded: that is every host thread it can use)."""
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    per_thread = max(1, args.ref_proofs)
+    per_step = max(1, args.ref_proofs)
     for _ in range(min(args.warmup, 1)):
-        cpu_reference_verify(cores, 1)
-    vals = []
-    for _ in range(args.steps):
-        v, dt = cpu_reference_verify(cores, per_thread)
-        vals.append((v, dt))
-    total = sum(cores * per_thread for _ in vals) / sum(dt for _, dt in vals)
-    ms = 1e3 * sum(dt for _, dt in vals) / len(vals)
-    sample = f"{cores} threads x {per_thread} verifies of one n=64 m=16 proof per step (literal MulVec loop, 2089 scalar muls each)"
+        cpu_verify(1, 1, 0)
+    runs = [cpu_verify(1, per_step, 0) for _ in range(args.steps)]
+    total = per_step * len(runs) / sum(dt for _, dt in runs)
+    ms = 1e3 * sum(dt for _, dt in runs) / len(runs)
+    vN, _ = cpu_verify(cores, 1, 0)
+    b2, _ = cpu_verify(cores, 20, 1)
+    sample = (f"1 thread x {per_step} verifies of one n=64 m=16 proof per step (literal MulVec loop, 2089 scalar multiplications each); "
+              f"the reference is single-threaded")
     line = {"impl": "reference", "metric": "range_proof_verifies_per_sec_n64_m16", "value": total, "unit": "proofs/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u32 limbs (integer)", "data": "synthetic",
-            "config": {"workload": "range-proof verify n=64 m=16, Ristretto255, reference CPU algorithm (oracle port)"},
-            "cpu_baseline": {"value": total, "unit": "proofs/s", "cores": cores, "kind": "port", "sample": sample},
+            "config": {"workload": WORKLOAD},
+            "cpu_baseline": {"value": total, "unit": "proofs/s", "cores": 1, "kind": "port", "sample": sample,
+                             "all_cores": {"value": vN, "cores": cores, "note": "B1, one independent proof stream per host thread"},
+                             "b2_fair_cpu": {"value": b2, "cores": cores, "note": "bucket-MSM verifier (oracle/baseline_msm.cpp), not the reference's algorithm"}},
             "e2e": {"value": total, "unit": "proofs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
 
@@ -166,6 +234,93 @@ def quiet_stdout():
     os.dup2(2, 1)
 
 
+def prove_algorithmic_field_muls(n: int, m: int):
+    """SURVEY §8(d) 'of a prove': W(N+m+3) + sum over rounds [2 W(2n'+2) + 2n' x (2-term joint scalar multiplication, 3040
+    field multiplies on Ristretto)] + 2N mixed point additions."""
+    N = n * m
+    total = algorithmic_field_muls(N + m + 3)[0] + 2 * N * MIXED
+    half = N
+    while half > 1:
+        half //= 2
+        total += 2 * algorithmic_field_muls(2 * half + 2)[0] + 2 * half * 3040
+    return total
+
+
+class Bench:
+    """Device-side state shared by the timed sections."""
+
+    def __init__(self, args, torch, dist, rank, world, local_rank):
+        from bulletproofsplus_b200 import api, _lib
+        self.args, self.torch, self.dist, self.rank, self.world = args, torch, dist, rank, world
+        self.api, self._lib = api, _lib
+        self.dev = torch.device("cuda", local_rank)
+        # a non-default torch stream, made current: the library launches on exactly this stream, so torch.cuda.Event records on
+        # it bracket the library's kernels (the legacy default stream has handle 0 = "make a private stream")
+        self.stream = torch.cuda.Stream(self.dev)
+        torch.cuda.set_stream(self.stream)
+        assert self.stream.cuda_stream != 0
+        self.ctx = api.Context(local_rank, self.stream.cuda_stream)
+        self.lib = self.ctx.lib
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)
+        self.local_rank = local_rank
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def to_dev(self, b: bytes):
+        return self.torch.frombuffer(bytearray(b), dtype=self.torch.uint8).to(self.dev)
+
+    def pinned(self, b: bytes):
+        return self.torch.frombuffer(bytearray(b), dtype=self.torch.uint8).pin_memory()
+
+    def timed(self, fn, reps=5, warm=2, flush=False):
+        """ms per call, CUDA events on the library's stream."""
+        torch = self.torch
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(self.stream)
+        for _ in range(reps):
+            if flush:
+                self.flush.zero_()
+            fn()
+        e1.record(self.stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    def timed_host(self, fn, reps=5, warm=2, flush=False):
+        """ms per call by the host clock around calls that end with a stream synchronisation (host-buffer ABI)."""
+        for _ in range(warm):
+            fn()
+        self.torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            if flush:
+                self.flush.zero_()
+            fn()
+        self.torch.cuda.synchronize()
+        return (time.perf_counter() - t0) * 1e3 / reps
+
+    def max_over_ranks(self, *vals):
+        t = self.torch.tensor(list(vals), dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return [float(x) for x in t]
+
+    def make_proofs(self, pk, n, m, count, seed):
+        """count valid proofs from the library's own prover (256 per call) + their commitments, as bytes."""
+        vs, gs = synth_inputs(count, seed, m)
+        proofs = []
+        for c0 in range(0, count, 256):
+            c1 = min(count, c0 + 256)
+            proofs += self.api.prove_batch(pk, n, m, vs[c0 * m:c1 * m], gs[c0 * m:c1 * m])
+        Vs = pk.commit_batch(vs, gs)
+        return b"".join(proofs), b"".join(Vs), vs, gs
+
+
 def main():
     quiet_stdout()
     ap = argparse.ArgumentParser()
@@ -175,9 +330,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=2048, help="proofs per step per GPU")
     ap.add_argument("--prove-batch", type=int, default=256)
-    ap.add_argument("--ref-proofs", type=int, default=2, help="reference arm: verifies per thread per step")
+    ap.add_argument("--ref-proofs", type=int, default=2, help="reference arm: verifies per step (one thread)")
     ap.add_argument("--msm-max-log", type=int, default=22)
-    ap.add_argument("--no-extras", action="store_true", help="skip proves/s, MSM sweep and CPU baseline")
+    ap.add_argument("--no-extras", action="store_true", help="skip proves/s, configs 2-4, the MSM sweep and the CPU baseline")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -193,16 +348,10 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    dev = torch.device("cuda", local_rank)
-    from bulletproofsplus_b200 import api, _lib
     import ctypes as C
-    # a non-default torch stream, made current: the library launches on exactly this stream, so torch.cuda.Event
-    # records on it bracket the library's kernels (the legacy default stream has handle 0 = "make a private stream")
-    stream = torch.cuda.Stream(dev)
-    torch.cuda.set_stream(stream)
-    assert stream.cuda_stream != 0
-    ctx = api.Context(local_rank, stream.cuda_stream)
-    lib, B, K_steps = ctx.lib, args.batch, args.steps
+    bn = Bench(args, torch, dist, rank, world, local_rank)
+    api, _lib, ctx, lib, dev, stream = bn.api, bn._lib, bn.ctx, bn.lib, bn.dev, bn.stream
+    B, K_steps = args.batch, args.steps
     NM = N_BITS * M_AGG
     pk = api.PublicKey.new(NM, _lib.RISTRETTO255, ctx)
     plen = lib.bpp_range_proof_len(0, N_BITS, M_AGG)
@@ -211,19 +360,13 @@ def main():
     ROT = 2
     host_proofs, host_V, dev_proofs, dev_V = [], [], [], []
     for r in range(ROT):
-        vs, gs = synth_inputs(B, seed=rank * 1000 + r)
-        proofs = []
-        for c0 in range(0, B, 256):  # the library's own prover, 256 proofs per call
-            c1 = min(B, c0 + 256)
-            proofs += api.prove_batch(pk, N_BITS, M_AGG, vs[c0 * M_AGG:c1 * M_AGG], gs[c0 * M_AGG:c1 * M_AGG])
-        Vs = pk.commit_batch(vs, gs)
-        hp = torch.frombuffer(bytearray(b"".join(proofs)), dtype=torch.uint8).pin_memory()
-        hv = torch.frombuffer(bytearray(b"".join(Vs)), dtype=torch.uint8).pin_memory()
+        pb, vb, _, _ = bn.make_proofs(pk, N_BITS, M_AGG, B, seed=rank * 1000 + r)
+        hp, hv = bn.pinned(pb), bn.pinned(vb)
         host_proofs.append(hp); host_V.append(hv)
         dev_proofs.append(hp.to(dev)); dev_V.append(hv.to(dev))
     d_verdicts = torch.full((B,), 255, dtype=torch.uint8, device=dev)
     h_verdicts = torch.empty((B,), dtype=torch.uint8).pin_memory()
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    flush = bn.flush
 
     def step_dev(i):
         flush.zero_()  # L2 flush: 256 MB > 126 MB L2
@@ -239,10 +382,7 @@ def main():
                                         C.cast(host_proofs[r].data_ptr(), C.c_char_p), None, C.cast(h_verdicts.data_ptr(), C.c_char_p))
         ctx.check(rc, "verify_batch")
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    barrier = bn.barrier
 
     # ---- integer-pipe peak (live) ----
     probe = ctx.int_peak_probe()
@@ -293,7 +433,6 @@ def main():
         e2e_ms = e2e_s * 1e3
     value = world * B * K_steps / (elapsed_ms * 1e-3)
     e2e_value = world * B * K_steps / (e2e_ms * 1e-3)
-
     # ---- roofline of the dominant kernel ----
     n_terms = 5 + 2 * 10 + 2 * NM + M_AGG  # 2089
     W, c_star, acc_share = algorithmic_field_muls(n_terms)
@@ -351,49 +490,268 @@ def main():
 
     extras = {}
     cpu = None
-    split = None
-    if not args.no_extras and world > 1:
-        split = run_msm_split(args, torch, dist, api, _lib, ctx, dev, stream, rank, world, int_peak)
-    if not args.no_extras and rank == 0:
-        extras = run_extras(args, torch, api, _lib, ctx, pk, dev, stream, int_peak)
-    if not args.no_extras and rank == 0 and world == 1:
-        cores = os.cpu_count() or 1
-        v, dt = cpu_reference_verify(cores, 4)
-        cpu = {"value": v, "unit": "proofs/s", "cores": cores, "kind": "port",
-               "sample": f"{cores} threads x 4 verifies of an n=64 m=16 proof ({dt:.1f} s wall, {cores * dt:.0f} CPU-s), oracle restatement "
-                         f"of the reference (naive MulVec, one proof stream per thread; the reference itself is single-threaded)"}
+    if not args.no_extras:
+        # per-GPU sections that shard trivially (every rank runs its own; max over ranks) and the multi-rank sections
+        extras.update(run_fs_verify(bn, pk, B))
+        extras.update(run_proves(bn, pk, int_peak))
+        extras.update(run_config4(bn))
+        if world > 1:
+            extras["msm_point_range_split"] = run_msm_split(bn, int_peak)
+        if world == 1:
+            extras.update(run_configs_2_3(bn))
+            extras.update(run_msm_sweep(bn, int_peak))
+            if rank == 0:
+                cpu = cpu_baselines(os.cpu_count() or 1)
+                if "proves" in extras:
+                    extras["proves"]["cpu_baseline"] = cpu.pop("prove")
 
     if rank == 0:
         line = {
             "metric": "range_proof_verifies_per_sec_n64_m16", "value": value, "unit": "proofs/s", "n_gpus": world, "steps": K_steps,
             "warmup": args.warmup, "ms_per_step": elapsed_ms / K_steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u32 limbs (integer, GF(2^255-19) / mod ell)", "data": "synthetic",
-            "config": {"workload": f"range-proof batch verify, n=64 bits, m=16 aggregated, Ristretto255, {B} proofs/step/GPU, "
-                                   f"2089-term MSM each, fixed-challenge (reference) mode", "batch_per_gpu": B, "parallelism": f"proofs sharded x{world}",
+            "config": {"workload": WORKLOAD, "batch_per_gpu": B, "parallelism": f"proofs sharded x{world}",
+                       "challenge_mode": "the reference's constants (parity mode; challenge tables reused across calls). The same batch with "
+                                         "per-proof Fiat-Shamir challenges is `verify_per_proof_challenges` in this line",
                        "l2": "256 MB memset between steps (inside the timed region); intermediates per step > L2"},
             "e2e": {"value": e2e_value, "unit": "proofs/s", "h2d_bytes_per_step": B * (plen + M_AGG * 32), "d2h_bytes_per_step": B},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         }
         line.update(extras)
-        if split:
-            line["msm_point_range_split"] = split
         emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
-def run_msm_split(args, torch, dist, api, _lib, ctx, dev, stream, rank, world, int_peak):
-    """One MSM of 2^msm_max_log points split by point range over the ranks: per-rank MSM to one raw
-    partial point, NCCL all-gather of world x 128 B, local sum + encode. Strong scaling; time = max over ranks."""
-    lib = ctx.lib
+def run_fs_verify(bn, pk, B):
+    """The headline batch with PER-PROOF challenges (bpp_range_verify_batch_fs*: what a Fiat-Shamir verifier has to call):
+    every proof builds its own challenge tables. Device-resident value + e2e with host buffers; challenges are the constants, so
+    the host's transcript hashing (merlin.py is pure Python) is not in these numbers."""
+    import ctypes as C
+    torch, lib, ctx = bn.torch, bn.lib, bn.ctx
+    pb, vb, _, _ = bn.make_proofs(pk, N_BITS, M_AGG, B, seed=bn.rank * 1000 + 7)
+    L = 10
+    block = b"".join(int(x).to_bytes(32, "little") for x in [12, 23, 99] + [7] * L)
+    h_pr, h_V, h_ch = bn.pinned(pb), bn.pinned(vb), bn.pinned(block * B)
+    d_pr, d_V, d_ch = h_pr.to(bn.dev), h_V.to(bn.dev), h_ch.to(bn.dev)
+    d_vd = torch.full((B,), 255, dtype=torch.uint8, device=bn.dev)
+    h_vd = torch.empty((B,), dtype=torch.uint8).pin_memory()
+
+    def dev_call():
+        ctx.check(lib.bpp_range_verify_batch_fs_dev(ctx.h, pk.handle, N_BITS, M_AGG, B, d_V.data_ptr(), d_pr.data_ptr(), d_ch.data_ptr(),
+                                                    d_vd.data_ptr()), "verify_fs_dev")
+
+    def host_call():
+        ctx.check(lib.bpp_range_verify_batch_fs(ctx.h, pk.handle, N_BITS, M_AGG, B, C.cast(h_V.data_ptr(), C.c_char_p),
+                                                C.cast(h_pr.data_ptr(), C.c_char_p), C.cast(h_ch.data_ptr(), C.c_char_p),
+                                                C.cast(h_vd.data_ptr(), C.c_char_p)), "verify_fs")
+
+    bn.barrier()
+    ms = bn.timed(dev_call, reps=5, warm=2, flush=True)
+    assert bool((d_vd == 0).all())
+    ms_h = bn.timed_host(host_call, reps=5, warm=1, flush=True)
+    assert bool((h_vd == 0).all())
+    ms, ms_h = bn.max_over_ranks(ms, ms_h)
+    out = {"verify_per_proof_challenges": {
+        "value": bn.world * B / (ms * 1e-3), "unit": "proofs/s", "batch_per_gpu": B, "ms_per_step": ms, "entry": "bpp_range_verify_batch_fs_dev",
+        "e2e": {"value": bn.world * B / (ms_h * 1e-3), "unit": "proofs/s", "entry": "bpp_range_verify_batch_fs (host buffers)",
+                "h2d_bytes_per_step": B * (len(pb) // B + M_AGG * 32 + len(block)), "d2h_bytes_per_step": B}}}
+    # random-linear-combination batch verification of the same proofs: one combined MSM per rank (per-proof fallback on failure)
+    import secrets
+    d_w = bn.to_dev(b"".join((secrets.randbits(128) | 1).to_bytes(32, "little") for _ in range(B)))
+    fb = C.c_int(0)
+
+    def rlc_call():
+        ctx.check(lib.bpp_range_verify_batch_rlc_dev(ctx.h, pk.handle, N_BITS, M_AGG, B, d_V.data_ptr(), d_pr.data_ptr(), None, None, d_w.data_ptr(),
+                                                     d_vd.data_ptr(), C.byref(fb)), "verify_rlc")
+
+    ms_r = bn.timed(rlc_call, reps=5, warm=2, flush=True)
+    assert bool((d_vd == 0).all()) and fb.value == 0
+    (ms_r,) = bn.max_over_ranks(ms_r)
+    out["verifies_per_sec_rlc_batch"] = {"value": bn.world * B / (ms_r * 1e-3), "unit": "proofs/s", "batch_per_gpu": B, "ms_per_step": ms_r,
+                                         "entry": "bpp_range_verify_batch_rlc_dev (all proofs valid: no fallback; one host sync per batch inside); "
+                                                  "every rank combines its own shard, verdicts need no exchange"}
+    return out
+
+
+def run_proves(bn, pk, int_peak):
+    """proves/s at n=64, m=16: device-resident, e2e through bpp_range_prove_batch with host buffers, whole-step roofline."""
+    import ctypes as C
+    torch, lib, ctx, args = bn.torch, bn.lib, bn.ctx, bn.args
+    PB = args.prove_batch
+    vs, gs = synth_inputs(PB, 99 + bn.rank, M_AGG)
+    plen = lib.bpp_range_proof_len(0, N_BITS, M_AGG)
+    h_v = torch.tensor(vs, dtype=torch.int64).pin_memory()
+    h_g = bn.pinned(b"".join(g.to_bytes(32, "little") for g in gs))
+    h_p = torch.empty(PB * plen, dtype=torch.uint8).pin_memory()
+    d_v, d_g = h_v.to(bn.dev), h_g.to(bn.dev)
+    d_p = torch.empty(PB * plen, dtype=torch.uint8, device=bn.dev)
+
+    def dev_call():
+        ctx.check(lib.bpp_range_prove_batch_dev(ctx.h, pk.handle, N_BITS, M_AGG, PB, d_v.data_ptr(), d_g.data_ptr(), None, d_p.data_ptr()), "prove")
+
+    def host_call():
+        ctx.check(lib.bpp_range_prove_batch(ctx.h, pk.handle, N_BITS, M_AGG, PB, C.cast(h_v.data_ptr(), C.POINTER(C.c_uint64)),
+                                            C.cast(h_g.data_ptr(), C.c_char_p), None, C.cast(h_p.data_ptr(), C.c_char_p)), "prove host")
+
+    bn.barrier()
+    ctx.hot_kernel_stats(reset=True)
+    reps = 5
+    ms = bn.timed(dev_call, reps=reps, warm=2, flush=True)
+    hot_ms, hot_n = ctx.hot_kernel_stats(reset=True)
+    hot_ms_per_call = hot_ms * reps / (reps + 2) / reps  # the bracket also saw the two warm-up calls
+    ms_h = bn.timed_host(host_call, reps=5, warm=1, flush=True)
+    assert bytes(h_p.numpy().tobytes()) == bytes(d_p.cpu().numpy().tobytes()), "host-ABI proofs differ from the device-ABI ones"
+    ms, ms_h = bn.max_over_ranks(ms, ms_h)
+    Wp = prove_algorithmic_field_muls(N_BITS, M_AGG)
+    alg = PB * Wp * FIELD_MUL_IMAD / (ms * 1e-3)
+    NM, L = N_BITS * M_AGG, 10
+    terms = 1 + 2 * L * (NM + 2) + (2 * NM + 2) + 2
+    return {"proves": {
+        "metric": "range_proof_proves_per_sec_n64_m16", "value": bn.world * PB / (ms * 1e-3), "unit": "proofs/s", "batch_per_gpu": PB, "ms_per_batch": ms,
+        "entry": "bpp_range_prove_batch_dev (fixed-nonce parity mode, byte-identical to the oracle)",
+        "e2e": {"value": bn.world * PB / (ms_h * 1e-3), "unit": "proofs/s", "entry": "bpp_range_prove_batch (host buffers)",
+                "h2d_bytes_per_step": PB * M_AGG * 40, "d2h_bytes_per_step": PB * plen},
+        "roofline": {"bound": "int-imad", "achieved": alg / 1e12, "peak": int_peak / 1e12, "unit": "T 32x32+64 multiply-adds/s", "frac": alg / int_peak,
+                     "algorithmic": f"PB * W_prove(64,16) * 72, W_prove = {Wp} field multiplies (SURVEY §8(d): W(N+m+3) + rounds [2 W(2n'+2) + 2n' * 3040] + 2N adds)",
+                     "kernel": "msm_accumulate_kernel<Ed25519> + long-bucket variants, all (2L+3) MSM jobs of all proofs in one launch sequence",
+                     "avg_launch_ms": hot_ms_per_call, "kernel_share_of_step": hot_ms_per_call / ms if ms else None,
+                     "executed": {"terms_per_proof": terms, "note": "generators are never folded (DESIGN §3.3): every L/R job is a fixed-base MSM over the "
+                                  "original G, H, so the 2n' joint scalar multiplications per round of the algorithmic count are not executed at all; "
+                                  "about terms x 21 table additions per proof instead"}}}}
+
+
+def run_configs_2_3(bn):
+    """BASELINE.json config 2 (standalone WIP over 2^12 generators, prove + verify) and config 3 (one aggregated n=64, m=64
+    proof: 8285-term verifier MSM) — single-call latencies through the host-buffer ABI, plus a 128-proof batch for config 3."""
+    import random
+    api, ctx, lib = bn.api, bn.ctx, bn.lib
+    out = {}
+    N = 4096
+    pk = api.PublicKey.new(N, 0, ctx)
+    rng = random.Random(0xC2)
+    a = [rng.randrange(ELL) for _ in range(N)]
+    b = [rng.randrange(ELL) for _ in range(N)]
+    ypow = [pow(12, i + 1, ELL) for i in range(N)]
+    gamma = rng.randrange(ELL)
+    proof = api.WeightedInnerProductProof.prove(pk, a, b, ypow, gamma)
+    dl = (sum(a[i] * 3 * (i + 1) + b[i] * 5 * (i + 1) + a[i] * b[i] * ypow[i] for i in range(N)) + 2 * gamma) % ELL
+    one = api.Points.from_multipliers((1).to_bytes(32, "little"), 0, ctx)
+    P = one.msm(dl.to_bytes(32, "little"))  # the commitment a b-weighted-inner-product prover would publish, as dl * g
+    zeros = [0] * N
+    proof.verify(pk, ypow, zeros, zeros, 0, [], P, [])
+    enc = lambda v: b"".join(int(x).to_bytes(32, "little") for x in v)
+    ea, eb, ey, ez = enc(a), enc(b), enc(ypow), enc(zeros)
+    import ctypes as C
+    buf = C.create_string_buffer(lib.bpp_wip_proof_len(0, N))
+    ln = C.c_size_t(len(buf))
+    pbytes = proof.to_bytes()
+
+    def wip_prove():
+        ln.value = len(buf)
+        ctx.check(lib.bpp_wip_prove(ctx.h, pk.handle, ea, eb, ey, gamma.to_bytes(32, "little"), None, buf, C.byref(ln)), "wip_prove")
+
+    def wip_verify():
+        rc = lib.bpp_wip_verify(ctx.h, pk.handle, ey, ez, ez, (0).to_bytes(32, "little"), 0, None, P, None, pbytes, len(pbytes), None)
+        assert rc == 0, rc
+
+    out["config2_wip_4096"] = {
+        "prove_ms": bn.timed_host(wip_prove, reps=5, warm=2), "verify_ms": bn.timed_host(wip_verify, reps=5, warm=2),
+        "note": "one standalone weighted-inner-product argument over 2^12 generators, Ristretto255, host-buffer ABI (H2D of 3 x 128 KB of scalars "
+                "inside): prove = 12 rounds, 26 fixed-base MSM jobs; verify = one 8221-term MSM",
+        "algorithmic_field_muls_verify": algorithmic_field_muls(8221)[0]}
+    # config 3
+    n, m = 64, 64
+    vs, gs = synth_inputs(1, 0xC3, m)
+    pr = api.prove_batch(pk, n, m, vs, gs)
+    Vs = pk.commit_batch(vs, gs)
+    assert api.verify_batch(pk, n, m, pr, [Vs]) == [0]
+    t_p = bn.timed_host(lambda: api.prove_batch(pk, n, m, vs, gs), reps=5, warm=1)
+    t_v = bn.timed_host(lambda: api.verify_batch(pk, n, m, pr, [Vs]), reps=5, warm=1)
+    CB = 128
+    pb, vb, _, _ = bn.make_proofs(pk, n, m, CB, seed=0xC33)
+    d_p, d_V = bn.to_dev(pb), bn.to_dev(vb)
+    d_vd = bn.torch.full((CB,), 255, dtype=bn.torch.uint8, device=bn.dev)
+    ms = bn.timed(lambda: ctx.check(lib.bpp_range_verify_batch_dev(ctx.h, pk.handle, n, m, CB, d_V.data_ptr(), d_p.data_ptr(), None, d_vd.data_ptr()),
+                                    "verify 64x64"), reps=5, warm=2, flush=True)
+    assert bool((d_vd == 0).all())
+    out["config3_n64_m64"] = {
+        "single_proof_prove_ms": t_p, "single_proof_verify_ms": t_v, "batch": CB, "batch_verify_ms": ms, "batch_verifies_per_sec": CB / (ms * 1e-3),
+        "note": "one aggregated proof of 64 values (N = 4096): verifier MSM of 8285 terms; single-proof numbers are host-ABI latencies "
+                "(python packing included), the batch is device-resident",
+        "algorithmic_field_muls_verify": algorithmic_field_muls(8285)[0]}
+    return out
+
+
+def run_config4(bn):
+    """BASELINE.json config 4: a FIXED batch of 8192 independent n=64, m=1 proofs (146-term MSM each, 128 of them tampered)
+    sharded over the ranks by parallel.shard_range: strong scaling. Rank 0 holds the host batch; e2e includes the scatter
+    (rank 0 -> ranks, NCCL), H2D, kernels, and the all-gather of the verdict bytes; `value` is device-resident per shard."""
+    import ctypes as C
+    from bulletproofsplus_b200 import parallel
+    torch, dist, api, ctx, lib = bn.torch, bn.dist, bn.api, bn.ctx, bn.lib
+    n, m, TOTAL = 64, 1, 8192
+    pk = api.PublicKey.new(n * m, 0, ctx)
+    plen = lib.bpp_range_proof_len(0, n, m)
+    lo, hi = parallel.shard_range(TOTAL, bn.rank, bn.world)
+    cnt = hi - lo
+    # every rank builds the same full batch deterministically (setup, untimed), then keeps its shard; tamper r' of every 64th proof
+    pb, vb, _, _ = bn.make_proofs(pk, n, m, TOTAL, seed=0xC4)
+    pb = bytearray(pb)
+    for i in range(0, TOTAL, 64):
+        pb[i * plen + plen - 96] ^= 1
+    want = torch.tensor([1 if i % 64 == 0 else 0 for i in range(TOTAL)], dtype=torch.uint8)
+    h_p, h_V = bn.pinned(bytes(pb[lo * plen:hi * plen])), bn.pinned(vb[lo * 32:hi * 32])
+    d_p, d_V = h_p.to(bn.dev), h_V.to(bn.dev)
+    d_vd = torch.full((cnt,), 255, dtype=torch.uint8, device=bn.dev)
+    d_all = torch.full((TOTAL,), 255, dtype=torch.uint8, device=bn.dev)
+    h_vd = torch.empty((cnt,), dtype=torch.uint8).pin_memory()
+    even = TOTAL % bn.world == 0
+
+    def dev_call():
+        ctx.check(lib.bpp_range_verify_batch_dev(ctx.h, pk.handle, n, m, cnt, d_V.data_ptr(), d_p.data_ptr(), None, d_vd.data_ptr()), "cfg4")
+        if bn.world > 1 and even:
+            dist.all_gather_into_tensor(d_all, d_vd)  # verdict exchange inside the timed region
+
+    def host_call():
+        ctx.check(lib.bpp_range_verify_batch(ctx.h, pk.handle, n, m, cnt, C.cast(h_V.data_ptr(), C.c_char_p), C.cast(h_p.data_ptr(), C.c_char_p), None,
+                                             C.cast(h_vd.data_ptr(), C.c_char_p)), "cfg4 host")
+        if bn.world > 1 and even:
+            d_vd.copy_(h_vd, non_blocking=True)
+            dist.all_gather_into_tensor(d_all, d_vd)
+
+    bn.barrier()
+    ms = bn.timed(dev_call, reps=5, warm=2, flush=True)
+    bn.barrier()
+    ms_h = bn.timed_host(host_call, reps=5, warm=1, flush=True)
+    got = d_all.cpu() if (bn.world > 1 and even) else d_vd.cpu()
+    ref = want if (bn.world > 1 and even) else want[lo:hi]
+    assert bool((got == ref).all()), "config 4 verdicts differ from the tamper pattern"
+    ms, ms_h = bn.max_over_ranks(ms, ms_h)
+    return {"config4_batch8192_n64_m1": {
+        "value": TOTAL / (ms * 1e-3), "unit": "proofs/s", "ms": ms, "scaling": "strong", "n_gpus": bn.world, "proofs_total": TOTAL, "proofs_per_gpu": cnt,
+        "tampered": TOTAL // 64, "verdicts_match_tamper_pattern": True,
+        "e2e": {"value": TOTAL / (ms_h * 1e-3), "unit": "proofs/s", "ms": ms_h, "h2d_bytes_per_step": cnt * (plen + 32), "d2h_bytes_per_step": cnt},
+        "exchange": "all-gather of the verdict bytes (NCCL)" if bn.world > 1 else "none",
+        "algorithmic_field_muls_per_proof": algorithmic_field_muls(146)[0]}}
+
+
+def run_msm_split(bn, int_peak):
+    """One MSM of 2^msm_max_log points split by point range over the ranks: per-rank MSM to one raw partial
+    point, NCCL all-gather of world x 128 B, local sum + encode. Strong scaling; time = max over ranks. The result is compared
+    with the exponent-domain value (sum_i s_i k_i mod ell) * g, computed in Python integers per rank and multiplied out by a
+    one-term MSM."""
+    torch, dist, api, ctx, lib, args = bn.torch, bn.dist, bn.api, bn.ctx, bn.lib, bn.args
+    world, rank, dev = bn.world, bn.rank, bn.dev
     n_total = 1 << args.msm_max_log
     n_loc = n_total // world
     g = torch.Generator().manual_seed(1234 + rank)
     mult = torch.randint(0, 256, (n_loc, 32), dtype=torch.uint8, generator=g)
     mult[:, 31] &= 0x0F
-    pts = api.Points.from_multipliers(bytes(mult.numpy().tobytes()), _lib.RISTRETTO255, ctx)
     sc = torch.randint(0, 256, (n_loc, 32), dtype=torch.uint8, generator=g)
     sc[:, 31] &= 0x0F
+    mb, sb = bytes(mult.numpy().tobytes()), bytes(sc.numpy().tobytes())
+    pts = api.Points.from_multipliers(mb, 0, ctx)
     d_sc = sc.to(dev)
     d_raw = torch.empty(128, dtype=torch.uint8, device=dev)
     d_all = torch.empty(128 * world, dtype=torch.uint8, device=dev)
@@ -404,175 +762,75 @@ def run_msm_split(args, torch, dist, api, _lib, ctx, dev, stream, rank, world, i
         dist.all_gather_into_tensor(d_all, d_raw)
         ctx.check(lib.bpp_points_sum_raw_dev(ctx.h, 0, d_all.data_ptr(), world, d_out.data_ptr()), "sum_raw_dev")
 
-    for _ in range(3):
-        step()
-    torch.cuda.synchronize()
-    outs = [torch.empty(32, dtype=torch.uint8, device=dev) for _ in range(world)]
-    dist.all_gather(outs, d_out)
-    same = all(bool((o == outs[0]).all()) for o in outs)
-    reps = 5
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    dist.barrier()
-    torch.cuda.synchronize()
-    e0.record(stream)
-    for _ in range(reps):
-        step()
-    e1.record(stream)
-    dist.barrier()
-    torch.cuda.synchronize()
-    t = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t[0])
+    ms = bn.timed(step, reps=5, warm=3)
+    bn.barrier()
+    (ms,) = bn.max_over_ranks(ms)
+    # exponent-domain check
+    dl = 0
+    for i in range(n_loc):
+        dl += int.from_bytes(mb[32 * i:32 * i + 32], "little") * int.from_bytes(sb[32 * i:32 * i + 32], "little")
+    d_dl = bn.to_dev((dl % ELL).to_bytes(32, "little"))
+    d_dls = torch.empty(32 * world, dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(d_dls, d_dl)
+    raw = bytes(d_dls.cpu().numpy().tobytes())
+    total = sum(int.from_bytes(raw[32 * r:32 * r + 32], "little") for r in range(world)) % ELL
+    one = api.Points.from_multipliers((1).to_bytes(32, "little"), 0, ctx)
+    want = one.msm(total.to_bytes(32, "little"))
+    got = bytes(d_out.cpu().numpy().tobytes())
+    ok = torch.tensor([1 if got == want else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    assert int(ok[0]) == 1, "point-range-split MSM differs from (sum s_i k_i) * g"
     W, _, _ = algorithmic_field_muls(n_total)
     return {"log2_n": args.msm_max_log, "n_gpus": world, "ms": ms, "points_per_sec": n_total / (ms * 1e-3), "scaling": "strong",
-            "all_ranks_agree": same, "exchange": f"all-gather of {world} x 128 B partial points + local sum",
+            "equals_exponent_domain_value": True, "exchange": f"all-gather of {world} x 128 B partial points + local sum",
             "int_roofline_frac_per_gpu": W * FIELD_MUL_IMAD / (ms * 1e-3) / int_peak / world}
 
 
-def run_extras(args, torch, api, _lib, ctx, pk, dev, stream, int_peak):
-    """proves/s (n=64, m=16) and the MSM points/s sweep, device-resident, CUDA-event timed."""
-    lib = ctx.lib
+def run_msm_sweep(bn, int_peak):
+    """MSM points/s vs size, every power of two 2^10 .. 2^msm_max_log, three curves, device-resident, CUDA-event timed.
+    SURVEY §8(d): field multiply = 72 IMAD for 2^255-19, 300 for BLS12-381; the secp256k1 field here is generic Montgomery
+    (8 x 8 + 8 x 8 = 128 IMAD executed), so its fraction is given for both the algorithmic 72 and the executed 128.
+    Edwards mixed/full/double = 7/8/8 field multiplies, short Weierstrass 11/16/7."""
+    torch, api, ctx, lib, _lib, args = bn.torch, bn.api, bn.ctx, bn.lib, bn._lib, bn.args
     out = {}
-    # proves/s
-    PB = args.prove_batch
-    vs, gs = synth_inputs(PB, seed=99)
-    d_v = torch.tensor(vs, dtype=torch.int64, device=dev)
-    d_g = torch.frombuffer(bytearray(b"".join(g.to_bytes(32, "little") for g in gs)), dtype=torch.uint8).to(dev)
-    plen = lib.bpp_range_proof_len(0, N_BITS, M_AGG)
-    d_p = torch.empty(PB * plen, dtype=torch.uint8, device=dev)
-
-    def prove():
-        ctx.check(lib.bpp_range_prove_batch_dev(ctx.h, pk.handle, N_BITS, M_AGG, PB, d_v.data_ptr(), d_g.data_ptr(), None, d_p.data_ptr()), "prove")
-
-    for _ in range(2):
-        prove()
-    torch.cuda.synchronize()
-    reps = 5
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(reps):
-        prove()
-    e1.record(stream)
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / reps
-    out["proves_per_sec_n64_m16"] = {"value": PB / (ms * 1e-3), "unit": "proofs/s", "batch": PB, "ms_per_batch": ms}
-    # real Fiat-Shamir, GPU side: per-proof challenges on the verifier, the interactive prover (12 host round trips per batch).
-    # The challenges are the constants, so the transcript hashing of the host (merlin.py is pure Python) is not in these numbers.
-    import ctypes as C
-    B = args.batch
-    vs2, gs2 = synth_inputs(B, seed=7)
-    proofs = []
-    for c0 in range(0, B, 256):
-        c1 = min(B, c0 + 256)
-        proofs += api.prove_batch(pk, N_BITS, M_AGG, vs2[c0 * M_AGG:c1 * M_AGG], gs2[c0 * M_AGG:c1 * M_AGG])
-    d_pr = torch.frombuffer(bytearray(b"".join(proofs)), dtype=torch.uint8).to(dev)
-    d_V = torch.frombuffer(bytearray(b"".join(pk.commit_batch(vs2, gs2))), dtype=torch.uint8).to(dev)
-    L = 10
-    block = b"".join(int(x).to_bytes(32, "little") for x in [12, 23, 99] + [7] * L)
-    d_ch = torch.frombuffer(bytearray(block * B), dtype=torch.uint8).to(dev)
-    d_vd = torch.full((B,), 255, dtype=torch.uint8, device=dev)
-
-    def verify_fs():
-        ctx.check(lib.bpp_range_verify_batch_fs_dev(ctx.h, pk.handle, N_BITS, M_AGG, B, d_V.data_ptr(), d_pr.data_ptr(), d_ch.data_ptr(), d_vd.data_ptr()),
-                  "verify_fs")
-
-    for _ in range(2):
-        verify_fs()
-    torch.cuda.synchronize()
-    assert bool((d_vd == 0).all())
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(reps):
-        verify_fs()
-    e1.record(stream)
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / reps
-    out["verifies_per_sec_per_proof_challenges"] = {"value": B / (ms * 1e-3), "unit": "proofs/s", "batch": B, "ms_per_batch": ms,
-                                                    "entry": "bpp_range_verify_batch_fs_dev"}
-
-    # random-linear-combination batch verification: same proofs, one combined MSM per batch (fallback to per-proof on failure)
-    import secrets
-    d_w = torch.frombuffer(bytearray(b"".join((secrets.randbits(128) | 1).to_bytes(32, "little") for _ in range(B))), dtype=torch.uint8).to(dev)
-    fb = C.c_int(0)
-
-    def verify_rlc():
-        ctx.check(lib.bpp_range_verify_batch_rlc_dev(ctx.h, pk.handle, N_BITS, M_AGG, B, d_V.data_ptr(), d_pr.data_ptr(), None, None, d_w.data_ptr(),
-                                                     d_vd.data_ptr(), C.byref(fb)), "verify_rlc")
-
-    for _ in range(2):
-        verify_rlc()
-    torch.cuda.synchronize()
-    assert bool((d_vd == 0).all()) and fb.value == 0
-    e0.record(stream)
-    for _ in range(reps):
-        verify_rlc()
-    e1.record(stream)
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / reps
-    out["verifies_per_sec_rlc_batch"] = {"value": B / (ms * 1e-3), "unit": "proofs/s", "batch": B, "ms_per_batch": ms,
-                                         "entry": "bpp_range_verify_batch_rlc_dev (all proofs valid: no fallback; one host sync per batch inside)"}
-
-    def prove_fs():
-        ses = api.ProveSession(pk, N_BITS, M_AGG, vs[:PB * M_AGG], gs[:PB * M_AGG])
-        ch = [(12, 23)] * PB
-        for _ in range(ses.rounds + 1):
-            ses.step(ch)
-            ch = [7] * PB
-        return ses.finish([99] * PB)
-
-    prove_fs()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(3):
-        got = prove_fs()
-    dt = (time.perf_counter() - t0) / 3
-    out["proves_per_sec_interactive"] = {"value": PB / dt, "unit": "proofs/s", "batch": PB, "ms_per_batch": dt * 1e3, "host_round_trips": 12,
-                                         "entry": "bpp_range_prove_begin/_step/_finish (host wall clock, host buffers)"}
-    # MSM sweep, all three curves (SURVEY §8(d): field multiply = 72 IMAD for 2^255-19 and the secp256k1 prime, 300 for
-    # BLS12-381; Edwards mixed/full/double = 7/8/8, short Weierstrass 11/16/7 field multiplies)
-    curves = (("", _lib.RISTRETTO255, args.msm_max_log, 253, 72, (7, 8, 8)),
-              ("_secp256k1", _lib.SECP256K1, min(args.msm_max_log, 20), 256, 72, (11, 16, 7)),
-              ("_bls12_381_g1", _lib.BLS12_381_G1, min(args.msm_max_log, 20), 255, 300, (11, 16, 7)))
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    def timed(fn):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize()
-        reps = 5
-        e0.record(stream)
-        for _ in range(reps):
-            fn()
-        e1.record(stream)
-        torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / reps
-
-    for suffix, curve, max_log, bits, imad, costs in curves:
+    curves = (("", _lib.RISTRETTO255, 253, 72, None, (7, 8, 8), 20),
+              ("_secp256k1", _lib.SECP256K1, 256, 72, 128, (11, 16, 7), 16),
+              ("_bls12_381_g1", _lib.BLS12_381_G1, 255, 300, None, (11, 16, 7), 16))
+    for suffix, curve, bits, imad, imad_exec, costs, tables_max in curves:
         sweep = []
+        max_log = args.msm_max_log
         n_max = 1 << max_log
         mult = torch.randint(0, 256, (n_max, 32), dtype=torch.uint8)
         mult[:, 31] &= 0x0F  # < 2^252 < every group order
         sc = torch.randint(0, 256, (n_max, 32), dtype=torch.uint8)
         sc[:, 31] &= 0x0F
-        d_sc = sc.to(dev)
-        d_out = torch.empty(lib.bpp_point_bytes(curve), dtype=torch.uint8, device=dev)
-        for lg in range(10, max_log + 1, 2):
+        d_sc = sc.to(bn.dev)
+        d_out = torch.empty(lib.bpp_point_bytes(curve), dtype=torch.uint8, device=bn.dev)
+        mult_b = bytes(mult.numpy().tobytes())
+        for lg in range(10, max_log + 1):
             n = 1 << lg
             # one point set per size: P_i = mult_i * g generated on the device (SURVEY §8(d) config 5)
-            pts = api.Points.from_multipliers(bytes(mult[:n].numpy().tobytes()), curve, ctx)
+            pts = api.Points.from_multipliers(mult_b[:32 * n], curve, ctx)
 
             def msm():
                 ctx.check(lib.bpp_msm_prepared_dev(ctx.h, pts.h, d_sc.data_ptr(), n, 1, d_out.data_ptr()), "msm")
 
-            generic_ms = timed(msm)          # Pippenger over the bare points (what a one-shot MulVec::calculate gets)
+            reps = 5 if lg >= 18 else 10
+            generic_ms = bn.timed(msm, reps=reps, warm=2)  # Pippenger over the bare points (what a one-shot MulVec::calculate gets)
             first = bytes(d_out.cpu().numpy().tobytes())
-            pts.precompute()                 # window tables for a reused point set: no doublings, one bucket set
-            tables_ms = timed(msm)
-            assert bytes(d_out.cpu().numpy().tobytes()) == first, "window-table MSM disagrees with the generic one"
-            # tables win while the Horner pass dominates (small N); beyond ~2^18 points the 16x larger gather footprint costs more
-            ms, path = (tables_ms, "window tables") if tables_ms < generic_ms else (generic_ms, "generic")
+            tables_ms = None
+            if lg <= tables_max:  # window tables for a reused point set: no doublings, one bucket set; lose beyond ~2^18 points
+                pts.precompute()
+                tables_ms = bn.timed(msm, reps=reps, warm=2)
+                assert bytes(d_out.cpu().numpy().tobytes()) == first, "window-table MSM disagrees with the generic one"
+            ms, path = (tables_ms, "window tables") if tables_ms is not None and tables_ms < generic_ms else (generic_ms, "generic")
             W, c_star, _ = algorithmic_field_muls(n, bits, *costs)
-            sweep.append({"log2_n": lg, "ms": ms, "points_per_sec": n / (ms * 1e-3), "int_roofline_frac": W * imad / (ms * 1e-3) / int_peak,
-                          "path": path, "generic_ms": generic_ms, "tables_ms": tables_ms})
+            row = {"log2_n": lg, "ms": ms, "points_per_sec": n / (ms * 1e-3), "int_roofline_frac": W * imad / (ms * 1e-3) / int_peak,
+                   "path": path, "generic_ms": generic_ms, "tables_ms": tables_ms,
+                   "generic_int_roofline_frac": W * imad / (generic_ms * 1e-3) / int_peak}
+            if imad_exec:
+                row["int_roofline_frac_at_executed_imad_per_mul"] = W * imad_exec / (ms * 1e-3) / int_peak
+            sweep.append(row)
             del pts
         out["msm_points_per_sec" + suffix] = sweep
     return out

@@ -251,4 +251,29 @@ int b2_msm_ext(size_t k, const uint8_t* scalars, const uint8_t* points, int thre
   return 0;
 }
 
+
+// Timing aid for bench.py's cpu_baseline leg: an MSM over n points P_i = P_0 + i * Q (built here by repeated addition from
+// the caller's two extended points, so that no decoding or conversion is inside the timed region) with xorshift scalars
+// below 2^252. Returns the seconds spent in the MSM alone (conversion to the cached form included, as a CPU library would
+// pay it per call); out = the result, so the work cannot be optimised away.
+double b2_bench_msm(size_t n, const uint8_t* p0, const uint8_t* q, int threads, uint8_t* out) {
+  using namespace b2;
+  std::vector<uint8_t> pts(128 * n), sc(32 * n);
+  ge cur = ge_from_bytes(p0);
+  const ge_cached step = ge_to_cached(ge_from_bytes(q));
+  uint64_t x = 0x9E3779B97F4A7C15ULL;
+  for (size_t i = 0; i < n; i++) {
+    ge_to_bytes(&pts[128 * i], cur);
+    cur = ge_add_cached(cur, step, false);
+    for (int w = 0; w < 4; w++) {
+      x ^= x << 13; x ^= x >> 7; x ^= x << 17;
+      memcpy(&sc[32 * i + 8 * w], &x, 8);
+    }
+    sc[32 * i + 31] &= 0x0F;
+  }
+  const auto t0 = std::chrono::steady_clock::now();
+  b2_msm_ext(n, sc.data(), pts.data(), threads, out);
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
 }  // extern "C"

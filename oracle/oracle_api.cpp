@@ -262,6 +262,17 @@ void orc_set_msm_backend(int backend, int threads) {
   g_b2_threads = threads < 1 ? 1 : threads;
   msm_backend() = backend;
 }
+// B2 MSM timing (Ristretto255): n points built from two oracle points, MSM alone timed inside baseline_msm.cpp
+extern "C" double b2_bench_msm(size_t n, const uint8_t* p0, const uint8_t* q, int threads, uint8_t* out);
+double orc_b2_bench_msm(size_t n, int threads) {
+  auto ext = [](const Ristretto::Point& p, uint8_t* b) {
+    p.X.to_bytes_le(b, 32); p.Y.to_bytes_le(b + 32, 32); p.Z.to_bytes_le(b + 64, 32); p.T.to_bytes_le(b + 96, 32);
+  };
+  uint8_t p0[128], q[128], out[128];
+  ext(scalar_mul<Ristretto>(Ristretto::base(), Ristretto::Sc::from_i32(1234567)), p0);
+  ext(scalar_mul<Ristretto>(Ristretto::base(), Ristretto::Sc::from_i32(7654321)), q);
+  return b2_bench_msm(n, p0, q, threads, out);
+}
 int orc_point_bytes(int curve) { return curve == 0 ? 32 : curve == 1 ? 64 : curve == 2 ? 96 : -1; }
 int orc_pk_new(int curve, size_t len, uint8_t* g, uint8_t* h, uint8_t* G, uint8_t* H) { DISPATCH(curve, pk_new(len, g, h, G, H)) }
 int orc_commit(int curve, size_t count, const uint64_t* v, const uint8_t* gamma, uint8_t* out) { DISPATCH(curve, commit(count, v, gamma, out)) }

@@ -54,6 +54,8 @@ class Oracle:
         L.orc_pk_new.argtypes = [C.c_int, sz, u8p, u8p, u8p, u8p]
         L.orc_set_msm_backend.argtypes = [C.c_int, C.c_int]
         L.orc_set_msm_backend.restype = None
+        L.orc_b2_bench_msm.argtypes = [sz, C.c_int]
+        L.orc_b2_bench_msm.restype = C.c_double
         L.orc_commit.argtypes = [C.c_int, sz, u64p, u8p, u8p]
         L.orc_msm_naive.argtypes = [C.c_int, sz, u8p, u8p, u8p]
         L.orc_scalar_mul.argtypes = [C.c_int, u8p, u8p, u8p]
@@ -70,6 +72,10 @@ class Oracle:
     def set_msm_backend(self, backend: int, threads: int = 1):
         """CPU baselines only: 0 = the reference's per-term MulVec loop (B1), 1 = bucket MSM (B2, Ristretto255)."""
         self.lib.orc_set_msm_backend(backend, threads)
+
+    def b2_bench_msm(self, n: int, threads: int) -> float:
+        """seconds of one B2 bucket MSM over n synthetic Ristretto255 points (CPU baseline timing only)."""
+        return float(self.lib.orc_b2_bench_msm(n, threads))
 
     @staticmethod
     def _chk(rc, what):
