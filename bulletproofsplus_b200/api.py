@@ -296,8 +296,24 @@ def verify_batch(pk: PublicKey, n: int, m: int, proofs, commitments, params: Bpp
     return list(out.raw[:count])
 
 
+REFERENCE_NONCES = "reference-nonces"
+"""Pass as `nonces` to get the reference snapshot's PUBLIC constant blinding scalars (alpha = 7 / 33, r, s, delta, eta = 33, 44, 88,
+123, d_L = 4, d_R = 5: range/mod.rs:94,256, wip.rs:94-95,175-178). Proofs made with them are byte-comparable with the oracle and
+NOT zero-knowledge: anyone can solve r', s', delta' for gamma and the bits of v. Parity tests and benchmarks only."""
+
+
+def random_nonces(q: int, count: int, rounds: int) -> list:
+    """Fresh uniform non-zero blinding scalars per proof from the operating system's CSPRNG."""
+    import secrets
+    draw = lambda: 1 + secrets.randbelow(q - 1)
+    return [dict(alpha=draw(), r=draw(), s=draw(), delta=draw(), eta=draw(), d_L=[draw() for _ in range(rounds)], d_R=[draw() for _ in range(rounds)])
+            for _ in range(count)]
+
+
 class ProveSession:
-    """Interactive batch proving for a transcript-owning host (bpp_range_prove_begin / _step / _finish). Scalars are ints."""
+    """Interactive batch proving for a transcript-owning host (bpp_range_prove_begin / _step / _finish). Scalars are ints.
+    nonces: None = fresh random blinding scalars per proof (random_nonces); a list of dicts = the caller's; REFERENCE_NONCES = the
+    reference's public constants (parity only)."""
 
     def __init__(self, pk: PublicKey, n: int, m: int, values, gammas, nonces=None):
         _shape_asserts(pk, n, m)
@@ -306,7 +322,9 @@ class ProveSession:
         self.plen = pk.ctx.lib.bpp_range_proof_len(pk.curve, n, m)
         arr = (C.c_uint64 * (self.count * m))(*[v & (2**64 - 1) for v in values])
         nb = None
-        if nonces is not None:  # per proof: dict(alpha, r, s, delta, eta, d_L[L], d_R[L])
+        if nonces is None:
+            nonces = random_nonces(self.q, self.count, (n * m).bit_length() - 1)
+        if nonces != REFERENCE_NONCES:  # per proof: dict(alpha, r, s, delta, eta, d_L[L], d_R[L])
             nb = b"".join(b"".join(_sc(x % self.q) for x in [d["alpha"], d["r"], d["s"], d["delta"], d["eta"], *d["d_L"], *d["d_R"]]) for d in nonces)
         h = C.c_void_p()
         out = C.create_string_buffer(self.count * pk.pb)

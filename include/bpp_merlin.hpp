@@ -3,6 +3,7 @@
 // sees a transcript: the host feeds the challenges to bpp_range_prove_step / bpp_range_verify_batch_fs.
 // Pinned to the merlin crate's `equivalence_simple` test value by tests/cpp/host_mirror_test.cpp.
 #pragma once
+#include <sys/random.h>
 #include <array>
 #include <cstdint>
 #include <cstring>
@@ -113,39 +114,43 @@ class Transcript {
   }
   // 64 transcript bytes reduced mod the group order; a zero result is drawn again
   PrimeFieldElem challenge_scalar(const std::string& label, Curve curve) {
-    const auto& q = detail::order_le(curve);
     for (;;) {
       uint8_t wide[64];
       challenge_bytes(label, wide, 64);
-      uint64_t r[5] = {0, 0, 0, 0, 0}, ql[4];
-      for (int i = 0; i < 4; i++) {
-        ql[i] = 0;
-        for (int k = 7; k >= 0; k--) ql[i] = (ql[i] << 8) | q[8 * i + k];
-      }
-      for (int bit = 511; bit >= 0; bit--) {  // r = 2r + bit, minus q when it does not fit
-        for (int i = 4; i > 0; i--) r[i] = (r[i] << 1) | (r[i - 1] >> 63);
-        r[0] = (r[0] << 1) | ((wide[bit >> 3] >> (bit & 7)) & 1);
-        bool ge = r[4] != 0;
-        if (!ge) {
-          ge = true;
-          for (int i = 3; i >= 0; i--)
-            if (r[i] != ql[i]) { ge = r[i] > ql[i]; break; }
-        }
-        if (ge) {
-          unsigned __int128 borrow = 0;
-          for (int i = 0; i < 4; i++) {
-            unsigned __int128 d = (unsigned __int128)r[i] - ql[i] - borrow;
-            r[i] = (uint64_t)d;
-            borrow = (d >> 64) & 1;
-          }
-          r[4] -= (uint64_t)borrow;
-        }
-      }
       PrimeFieldElem e;
-      bool nz = false;
-      for (int i = 0; i < 32; i++) { e.e[i] = (uint8_t)(r[i >> 3] >> (8 * (i & 7))); nz = nz || e.e[i]; }
-      if (nz) return e;
+      if (reduce_wide(wide, curve, e)) return e;
     }
+  }
+  // 512-bit little-endian value mod the group order; false when the result is zero
+  static bool reduce_wide(const uint8_t* wide, Curve curve, PrimeFieldElem& e) {
+    const auto& q = detail::order_le(curve);
+    uint64_t r[5] = {0, 0, 0, 0, 0}, ql[4];
+    for (int i = 0; i < 4; i++) {
+      ql[i] = 0;
+      for (int k = 7; k >= 0; k--) ql[i] = (ql[i] << 8) | q[8 * i + k];
+    }
+    for (int bit = 511; bit >= 0; bit--) {  // r = 2r + bit, minus q when it does not fit
+      for (int i = 4; i > 0; i--) r[i] = (r[i] << 1) | (r[i - 1] >> 63);
+      r[0] = (r[0] << 1) | ((wide[bit >> 3] >> (bit & 7)) & 1);
+      bool ge = r[4] != 0;
+      if (!ge) {
+        ge = true;
+        for (int i = 3; i >= 0; i--)
+          if (r[i] != ql[i]) { ge = r[i] > ql[i]; break; }
+      }
+      if (ge) {
+        unsigned __int128 borrow = 0;
+        for (int i = 0; i < 4; i++) {
+          unsigned __int128 d = (unsigned __int128)r[i] - ql[i] - borrow;
+          r[i] = (uint64_t)d;
+          borrow = (d >> 64) & 1;
+        }
+        r[4] -= (uint64_t)borrow;
+      }
+    }
+    bool nz = false;
+    for (int i = 0; i < 32; i++) { e.e[i] = (uint8_t)(r[i >> 3] >> (8 * (i & 7))); nz = nz || e.e[i]; }
+    return nz;
   }
 
  private:
@@ -187,15 +192,49 @@ class RangeProofTranscript {
 
 }  // namespace merlin
 
-// README-style calls with a transcript (README.md:39-52 of the reference): one proof, host-owned Fiat-Shamir
-inline RangeProof prove_with_transcript(const PublicKey& pk, size_t n, const RangeProver& prover, merlin::Transcript transcript) {
+// The prover's blinding scalars of one proof: alpha, r, s, delta, eta, d_L[L], d_R[L] (L = log2(n*m)). A proof is zero-knowledge
+// only if these are fresh, secret and uniform: random() draws them from the operating system's CSPRNG. reference() is the
+// reference snapshot's PUBLIC constants (range/mod.rs:94,256; wip.rs:94-95,175-178): with them anyone can solve the proof
+// scalars for gamma and the bits of v — parity tests only.
+struct ProverNonces {
+  std::vector<uint8_t> bytes;  // (5 + 2L) x 32 canonical scalars; empty = the reference's constants
+  static ProverNonces reference() { return ProverNonces{}; }
+  static ProverNonces random(Curve curve, size_t L) {
+    ProverNonces nn;
+    nn.bytes.resize((5 + 2 * L) * 32);
+    for (size_t j = 0; j < 5 + 2 * L; j++) {
+      PrimeFieldElem e;
+      for (;;) {
+        uint8_t wide[64];
+        size_t got = 0;
+        while (got < sizeof wide) {
+          ssize_t k = getrandom(wide + got, sizeof wide - got, 0);
+          if (k < 0) throw Panic("getrandom failed");
+          got += (size_t)k;
+        }
+        if (merlin::Transcript::reduce_wide(wide, curve, e)) break;
+      }
+      std::memcpy(&nn.bytes[32 * j], e.e.data(), 32);
+    }
+    return nn;
+  }
+};
+
+// README-style calls with a transcript (README.md:39-52 of the reference): one proof, host-owned Fiat-Shamir. `nonces` NULL =
+// fresh random blinding scalars (the only safe choice outside parity tests).
+inline RangeProof prove_with_transcript(const PublicKey& pk, size_t n, const RangeProver& prover, merlin::Transcript transcript,
+                                        const ProverNonces* nonces = nullptr) {
   const size_t m = prover.v_vec.size(), pb = pk.point_bytes();
   if (pk.len() != n * m) throw Panic("pk.G_vec.len() != n*m");
   bpp_prove_session* s = nullptr;
   Point A;
   A.bytes.resize(pb);
-  detail::check(pk.ctx(), bpp_range_prove_begin(pk.ctx(), pk.handle(), n, m, 1, prover.v_vec.data(), detail::pack(prover.gamma_vec).data(), nullptr, &s,
-                                                A.bytes.data()), "range_prove_begin");
+  size_t L0 = 0;
+  while (((size_t)1 << L0) < n * m) L0++;
+  const ProverNonces fresh = nonces ? ProverNonces{} : ProverNonces::random(pk.curve(), L0);
+  const ProverNonces& use = nonces ? *nonces : fresh;
+  detail::check(pk.ctx(), bpp_range_prove_begin(pk.ctx(), pk.handle(), n, m, 1, prover.v_vec.data(), detail::pack(prover.gamma_vec).data(),
+                                                use.bytes.empty() ? nullptr : use.bytes.data(), &s, A.bytes.data()), "range_prove_begin");
   std::shared_ptr<bpp_prove_session> guard(s, bpp_prove_session_free);
   merlin::RangeProofTranscript rt(std::move(transcript), pk.curve(), n, m, prover.commitment_vec);
   PrimeFieldElem y, z;

@@ -130,8 +130,15 @@ int main(int argc, char** argv) {
     PublicKey pk = PublicKey::new_(n * m, curve);
     RangeProver prover = RangeProver::new_();
     for (size_t j = 0; j < m; j++) prover.commit(pk, 31 + j, fe(11 + (int)j));
-    RangeProof proof = prove_with_transcript(pk, n, prover, merlin::Transcript("RangeProof Test"));
+    const ProverNonces parity = ProverNonces::reference();  // the public constants: byte-comparable with the Python host and the oracle
+    RangeProof proof = prove_with_transcript(pk, n, prover, merlin::Transcript("RangeProof Test"), &parity);
     hex("transcript_proof_n32_m4", proof.to_bytes());
+    // default = fresh random blinding scalars: two proofs of one witness differ, and both verify
+    RangeProof zk1 = prove_with_transcript(pk, n, prover, merlin::Transcript("RangeProof Test"));
+    RangeProof zk2 = prove_with_transcript(pk, n, prover, merlin::Transcript("RangeProof Test"));
+    report("default nonces are fresh: two proofs of one witness differ", zk1.to_bytes() != zk2.to_bytes() && zk1.to_bytes() != proof.to_bytes());
+    report("random-nonce transcript proofs verify", verify_with_transcript(zk1, pk, n, prover.commitment_vec, merlin::Transcript("RangeProof Test")) == Result::Ok() &&
+                                                    verify_with_transcript(zk2, pk, n, prover.commitment_vec, merlin::Transcript("RangeProof Test")) == Result::Ok());
     report("transcript verify == Ok(())", verify_with_transcript(proof, pk, n, prover.commitment_vec, merlin::Transcript("RangeProof Test")) == Result::Ok());
     report("other transcript label == Err(VerificationError)",
            verify_with_transcript(proof, pk, n, prover.commitment_vec, merlin::Transcript("RangeProof Test 2")) == Result::Err(ProofError::VerificationError));

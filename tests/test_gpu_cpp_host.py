@@ -81,5 +81,5 @@ def test_crate_style_checks_through_cpp_host(oracle, curve):
     n, m = 32, 4
     pk = api.PublicKey.new(n * m, curve, api.Arith.init())
     vs, gs = [31 + j for j in range(m)], [11 + j for j in range(m)]
-    py = api.prove_batch_fs(pk, n, m, vs, gs, [merlin.Transcript(b"RangeProof Test")])[0]
+    py = api.prove_batch_fs(pk, n, m, vs, gs, [merlin.Transcript(b"RangeProof Test")], api.REFERENCE_NONCES)[0]
     assert bytes.fromhex(f["transcript_proof_n32_m4"]) == py

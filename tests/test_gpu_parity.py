@@ -202,7 +202,9 @@ def _inputs(n, m, seed):
     return [rng.randrange(0, 2**min(n, 31)) for _ in range(m)], [rng.randrange(ELL) for _ in range(m)]
 
 
-@pytest.mark.parametrize("n,m", [(8, 1), (8, 4), (32, 1), (64, 1), (64, 2), (32, 16), (64, 16)])
+# the reference's intended grid (range/mod.rs:520-566): n in {32, 64} x m in {1, 2, 4, 8} — all eight cells — plus small shapes and
+# the BASELINE.json shapes (32, 16), (64, 16); (64, 64) is in test_gpu_full_size.py
+@pytest.mark.parametrize("n,m", [(8, 1), (8, 4), (32, 1), (32, 2), (32, 4), (32, 8), (64, 1), (64, 2), (64, 4), (64, 8), (32, 16), (64, 16)])
 def test_range_prove_is_byte_identical(api, ctx, oracle, n, m):
     pk = api.PublicKey.new(n * m, R, ctx)
     vs, gs = ([2, 5], [3, 7]) if (n, m) == (64, 2) else _inputs(n, m, 1000 + n * 100 + m)  # (64,2) = src/main.rs

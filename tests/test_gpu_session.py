@@ -40,7 +40,7 @@ def test_session_with_reference_constants_equals_one_shot(api, ctx, oracle, n, m
     L = (n * m).bit_length() - 1
     pk = api.PublicKey.new(n * m, 0, ctx)
     vs, gs = _inputs(n, m, count, 5 * n + m, ELL)
-    ses = api.ProveSession(pk, n, m, vs, gs)
+    ses = api.ProveSession(pk, n, m, vs, gs, api.REFERENCE_NONCES)
     y, z = (7, 7) if m == 1 else (12, 23)
     ch = [(y, z)] * count
     pts = [ses.A]
@@ -59,7 +59,7 @@ def test_session_with_reference_constants_equals_one_shot(api, ctx, oracle, n, m
     del ses
     vs2 = [v ^ 1 for v in vs]
     for values in (vs, vs2):
-        ses = api.ProveSession(pk, n, m, values, gs)
+        ses = api.ProveSession(pk, n, m, values, gs, api.REFERENCE_NONCES)
         ch = [(y, z)] * count
         for _ in range(L + 1):
             ses.step(ch)
@@ -134,3 +134,27 @@ def test_session_rejects_bad_host_input(api, ctx):
     with pytest.raises(api.BppError) as ei:
         ses.step([(0, 5)])  # y = 0
     assert ei.value.rc == 2
+
+
+def test_default_nonces_are_fresh_and_proofs_verify(api, ctx):
+    """with transcript challenges and the reference's public constant blinders a verifier could solve the proof
+    scalars for gamma and v. The Fiat-Shamir prover therefore draws alpha, r, s, delta, eta, d_L, d_R per proof from the CSPRNG
+    unless told otherwise: two proofs of one witness differ in every blinded element, and both verify."""
+    from bulletproofsplus_b200 import merlin
+    n, m, count = 32, 2, 2
+    pk = api.PublicKey.new(n * m, 0, ctx)
+    vs, gs = [5, 6] * count, [7, 8] * count  # the same witness twice
+    label = lambda: [merlin.Transcript(b"zk test") for _ in range(count)]
+    proofs = api.prove_batch_fs(pk, n, m, vs, gs, label())
+    again = api.prove_batch_fs(pk, n, m, vs, gs, label())
+    parity = api.prove_batch_fs(pk, n, m, vs, gs, label(), api.REFERENCE_NONCES)
+    assert parity[0] == parity[1]  # constants: same witness, same transcript, same bytes
+    L = 6
+    for a, b in ((proofs[0], proofs[1]), (proofs[0], again[0]), (proofs[0], parity[0])):
+        pa = [a[i * 32:(i + 1) * 32] for i in range(2 * L + 3 + 3)]
+        pb_ = [b[i * 32:(i + 1) * 32] for i in range(2 * L + 3 + 3)]
+        assert all(x != y for x, y in zip(pa, pb_)), "a proof element repeats across proofs made with fresh nonces"
+    Vs = pk.commit_batch(vs, gs)
+    Vl = [Vs[i * m:(i + 1) * m] for i in range(count)]
+    assert api.verify_batch_fs(pk, n, m, proofs, Vl, transcripts=label()) == [0] * count
+    assert api.verify_batch_fs(pk, n, m, again, Vl, transcripts=label()) == [0] * count

@@ -33,7 +33,7 @@ if case in ("verify", "prove", "verify_fs", "prove_fs", "verify_rlc"):
         timeit(lambda: api.prove_batch(pk, n, m, vs, gs), f"prove_batch host-ABI B={size}")
     elif case == "prove_fs":  # interactive prover, challenges = the constants (no transcript cost): the GPU side of real Fiat-Shamir
         def run():
-            ses = api.ProveSession(pk, n, m, vs, gs)
+            ses = api.ProveSession(pk, n, m, vs, gs, api.REFERENCE_NONCES)
             ch = [(12, 23)] * size
             for _ in range(ses.rounds + 1):
                 ses.step(ch)
