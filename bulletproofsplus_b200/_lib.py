@@ -18,7 +18,7 @@ SYMBOLS = [
     "bpp_init", "bpp_destroy", "bpp_last_error", "bpp_point_bytes", "bpp_range_proof_len", "bpp_wip_proof_len",
     "bpp_kernel_launches", "bpp_sync", "bpp_pk_new", "bpp_pk_export", "bpp_pk_len", "bpp_pk_free", "bpp_commit_batch", "bpp_msm",
     "bpp_points_upload", "bpp_points_from_multipliers", "bpp_points_len", "bpp_points_precompute", "bpp_points_free", "bpp_msm_prepared",
-    "bpp_msm_prepared_dev", "bpp_raw_point_bytes", "bpp_msm_prepared_raw", "bpp_points_sum_raw", "bpp_msm_prepared_raw_dev", "bpp_points_sum_raw_dev", "bpp_range_prove_batch",
+    "bpp_msm_prepared_dev", "bpp_raw_point_bytes", "bpp_msm_prepared_raw", "bpp_points_sum_raw", "bpp_msm_prepared_raw_dev", "bpp_points_sum_raw_dev", "bpp_points_sum_raw_noalloc_dev", "bpp_range_prove_batch",
     "bpp_range_verify_batch", "bpp_range_prove_batch_dev", "bpp_range_verify_batch_dev", "bpp_range_prove", "bpp_range_verify",
     "bpp_wip_prove", "bpp_wip_verify", "bpp_range_verify_batch_fs", "bpp_range_verify_batch_rlc", "bpp_range_verify_batch_rlc_dev", "bpp_range_verify_batch_fs_dev", "bpp_range_prove_begin", "bpp_range_prove_step",
     "bpp_range_prove_finish", "bpp_prove_session_rounds", "bpp_prove_session_free", "bpp_int_peak_probe", "bpp_fp64_peak_probe", "bpp_fe_mul_probe", "bpp_hot_kernel_stats", "bpp_trace", "bpp_trace_dump", "bpp_debug_op",
@@ -78,6 +78,7 @@ def load() -> C.CDLL:
     L.bpp_points_sum_raw.argtypes = [vp, i, u8p, sz, u8p]
     L.bpp_msm_prepared_raw_dev.argtypes = [vp, vp, vp, sz, vp]
     L.bpp_points_sum_raw_dev.argtypes = [vp, i, vp, sz, vp]
+    L.bpp_points_sum_raw_noalloc_dev.argtypes = [vp, i, vp, sz, vp]
     L.bpp_range_prove_batch.argtypes = [vp, vp, sz, sz, sz, C.POINTER(C.c_uint64), u8p, pp, u8p]
     L.bpp_range_verify_batch.argtypes = [vp, vp, sz, sz, sz, u8p, u8p, pp, u8p]
     L.bpp_range_prove_batch_dev.argtypes = [vp, vp, sz, sz, sz, vp, vp, pp, vp]

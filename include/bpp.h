@@ -104,6 +104,14 @@ int bpp_points_sum_raw(bpp_ctx* ctx, int curve, const uint8_t* raw_points, size_
  * partial sums sits between them (point addition is not an NCCL reduction operator) */
 int bpp_msm_prepared_raw_dev(bpp_ctx* ctx, const bpp_points* pts, const void* d_scalars, size_t k, void* d_out_raw);
 int bpp_points_sum_raw_dev(bpp_ctx* ctx, int curve, const void* d_raw_points, size_t count, void* d_out_point);
+/* bpp_points_sum_raw_dev for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc). No counterpart in the reference. Same inputs, same output
+ * bytes; calls no cudaMalloc / cudaFree / allocating routine. Its intermediate block sums live in a file-scope __device__
+ * array of 65 slots x 192 B (12 480 B, held by every GPU that loads the library until the process exits), so
+ * count <= BPP_NOALLOC_MAX_POINTS, beyond which it returns BPP_ERR_LENGTH with a message in bpp_last_error. All calls on
+ * a device share that array: calls that overlap on the GPU (two streams / contexts) race; calls on one stream do not. */
+#define BPP_NOALLOC_MAX_POINTS 65536
+int bpp_points_sum_raw_noalloc_dev(bpp_ctx* ctx, int curve, const void* d_raw_points, size_t count, void* d_out_point);
 
 /* ---- RangeProof::prove / verify (range/mod.rs:31-78) ---------------------------------------------- */
 /* `count` independent proofs, each aggregating m values of n bits against pk (bpp_pk_len(pk) == n*m).
