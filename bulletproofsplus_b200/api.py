@@ -153,12 +153,14 @@ class PublicKey:
     G_vec = property(lambda self: self._export()[2])
     H_vec = property(lambda self: self._export()[3])
 
-    def commit_batch(self, vs, gammas) -> list:
+    def commit_batch(self, vs, gammas, full_u64: bool = False) -> list:
+        """V_i = Fr(v_i as i32) g + gamma_i h as in the reference (prover.rs:37), or with all 64 bits of v_i (full_u64)."""
         n = len(vs)
         arr = (C.c_uint64 * n)(*[v & (2**64 - 1) for v in vs])
         out = C.create_string_buffer(max(1, n * self.pb))
         gam = b"".join(_sc(g % ORDERS[self.curve]) for g in gammas)
-        self.ctx.check(self.ctx.lib.bpp_commit_batch(self.ctx.h, self.handle, arr, gam, n, out), "commit_batch")
+        fn = self.ctx.lib.bpp_commit_batch_u64 if full_u64 else self.ctx.lib.bpp_commit_batch
+        self.ctx.check(fn(self.ctx.h, self.handle, arr, gam, n, out), "commit_batch")
         return [out.raw[i * self.pb:(i + 1) * self.pb] for i in range(n)]
 
     def __del__(self):
@@ -358,7 +360,7 @@ def prove_batch_fs(pk: PublicKey, n: int, m: int, values, gammas, transcripts, n
     """Real Fiat-Shamir: `transcripts[i]` is proof i's merlin.Transcript (consumed). Returns the proofs."""
     from . import merlin
     count = len(values) // m
-    Vs = pk.commit_batch(values, gammas)
+    Vs = pk.commit_batch(values, gammas, full_u64=True)  # the statement proved is about all 64 bits of v
     ses = ProveSession(pk, n, m, values, gammas, nonces)
     rts = [merlin.RangeProofTranscript(transcripts[i], ORDERS[pk.curve], n, m, Vs[i * m:(i + 1) * m]) for i in range(count)]
     ch = [rts[i].after_A(ses.A[i]) for i in range(count)]

@@ -135,7 +135,13 @@ struct Api {
   }
 
   // ---- RangeProver::commit ----------------------------------------------------------------------------
-  static int commit_batch(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out) {
+  static int commit_batch_u64(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out) {
+    return commit_batch(ctx, pk, v, gamma, count, out, true);
+  }
+  static int commit_batch_i32(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out) {
+    return commit_batch(ctx, pk, v, gamma, count, out, false);
+  }
+  static int commit_batch(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out, bool full_u64) {
     if (count == 0) return BPP_OK;
     if (count > (1u << 26)) return BPP_ERR_LENGTH;
     const uint32_t n = (uint32_t)count;
@@ -147,7 +153,7 @@ struct Api {
     BPP_CK(ctx->buf[B_OUT0].ensure((size_t)n * PB));
     BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN0].p, v, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
     BPP_CK(cudaMemcpyAsync(ctx->buf[B_IN1].p, gamma, (size_t)n * 32, cudaMemcpyHostToDevice, ctx->stream));
-    BPP_LAUNCH(commit_terms_kernel<M>, ceil_div(n, 128), 128, 0, n, ctx->buf[B_IN0].as<uint64_t>(), ctx->buf[B_IN1].as<uint32_t>(),
+    BPP_LAUNCH(commit_terms_kernel<M>, ceil_div(n, 128), 128, 0, n, full_u64 ? 1u : 0u, ctx->buf[B_IN0].as<uint64_t>(), ctx->buf[B_IN1].as<uint32_t>(),
                ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>(), ctx->buf[B_FLAGS].as<uint8_t>());
     BPP_CK(ctx->buf[B_RESULTS].ensure((size_t)n * C::EXT_WORDS * 4));
     BPP_LAUNCH(comb_eval_kernel<C>, ceil_div(n, 128), 128, 0, n, pk->comb_w, ctx->buf[B_SCALARS].as<uint32_t>(), pk->comb,
@@ -363,6 +369,7 @@ struct Api {
     T.Tmul = ctx->buf[B_TAB0].as<uint32_t>(); T.Tadd = ctx->buf[B_TAB1].as<uint32_t>(); T.tmp = ctx->buf[B_TAB2].as<uint32_t>();
     T.zpow = ctx->buf[B_TAB3].as<uint32_t>();
     T.stride_T = T.stride_tmp = T.stride_zpow = T.stride_params = 0;
+    T.pre = nullptr; T.stride_pre = 0;
     uint32_t* xs = ctx->buf[B_TAB4].as<uint32_t>();
     BPP_LAUNCH(verify_proof_scalars_kernel<M>, ceil_div(count, 128), 128, 0, count, d_proofs, proof_len, (size_t)ppp * PB, xs,
                ctx->buf[B_FLAGS2].as<uint8_t>());
@@ -371,6 +378,11 @@ struct Api {
       ctx->tab_gen = 0;  // the shared tables of an earlier call are overwritten
       BPP_LAUNCH(verify_expand_challenges_kernel<M>, ceil_div(count, 128), 128, 0, count, L, d_challenges, ctx->buf[B_TAB5].as<uint32_t>(),
                  ctx->buf[B_FLAGS2].as<uint8_t>());
+      // the L + 2 inversions of every proof, all proofs side by side, then one 128-thread block per proof for its tables
+      BPP_CK(ctx->buf[B_TAB6].ensure((size_t)count * (L + 2) * 32));
+      T.pre = ctx->buf[B_TAB6].as<uint32_t>(); T.stride_pre = (L + 2) * 8;
+      BPP_LAUNCH(verify_inverses_kernel<M>, ceil_div(count, 32), 32, 0, count, L, ctx->buf[B_TAB5].as<uint32_t>(), T.stride_params,
+                 ctx->buf[B_TAB6].as<uint32_t>(), T.stride_pre);
       BPP_LAUNCH(verify_tables_kernel<M>, count, 128, 0, vs, ctx->buf[B_TAB5].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
     } else {
       const size_t cap0 = ctx->buf[B_TAB0].cap + ctx->buf[B_TAB1].cap + ctx->buf[B_TAB2].cap + ctx->buf[B_TAB3].cap;

@@ -169,6 +169,12 @@ int bpp_commit_batch(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const ui
   BPP_DISPATCH(pk->curve, commit_batch(ctx, pk, v, gamma, count, out_points));
 }
 
+int bpp_commit_batch_u64(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out_points) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, commit_batch_u64(ctx, pk, v, gamma, count, out_points));
+}
+
 int bpp_msm(bpp_ctx* ctx, int curve, const uint8_t* scalars, const uint8_t* points, size_t k, uint8_t* out_point) {
   BPP_ENTER(ctx);
   BPP_DISPATCH(curve, msm(ctx, scalars, points, k, out_point));

@@ -11,6 +11,7 @@ struct CurveVtbl {
   int (*pk_new)(bpp_ctx*, size_t, bpp_pk**);
   int (*pk_export)(bpp_ctx*, const bpp_pk*, uint8_t*, uint8_t*, uint8_t*, uint8_t*);
   int (*commit_batch)(bpp_ctx*, const bpp_pk*, const uint64_t*, const uint8_t*, size_t, uint8_t*);
+  int (*commit_batch_u64)(bpp_ctx*, const bpp_pk*, const uint64_t*, const uint8_t*, size_t, uint8_t*);
   int (*msm)(bpp_ctx*, const uint8_t*, const uint8_t*, size_t, uint8_t*);
   int (*points_upload)(bpp_ctx*, const uint8_t*, size_t, bool, bpp_points**);
   int (*points_precompute)(bpp_ctx*, bpp_points*);
@@ -67,7 +68,8 @@ void fill_vtbl_core(CurveVtbl& v) {
   v.curve = C::CURVE_ID; v.point_bytes = C::POINT_BYTES; v.raw_bytes = C::EXT_WORDS * 4; v.field_bytes = C::FIELD_BYTES;
   v.pk_new = A::pk_new;
   v.pk_export = A::pk_export;
-  v.commit_batch = A::commit_batch;
+  v.commit_batch = A::commit_batch_i32;
+  v.commit_batch_u64 = A::commit_batch_u64;
   v.msm = A::msm;
   v.points_upload = A::points_upload;
   v.points_precompute = A::points_precompute;

@@ -117,6 +117,7 @@ struct Ed25519 {
   // Halving the Niels form lets D = Z1 instead of 2*Z1, which keeps every operand of the second-level multiplies within
   // the lazy bound; all four output coordinates come out divided by 4, i.e. the same projective point.
   static constexpr bool HAS_F64 = true;
+  static constexpr bool HAS_COOP4 = true;  // four-role point operations: msm_combine4_kernel
   struct AccF { F5 X, Y, Z, T; };
   BPP_DEV static void store_table_point_f(uint32_t* dst, const Aff& q) {
     const uint32_t hc[8] = {0xfffffff7u, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0x3fffffffu};  // (p+1)/2

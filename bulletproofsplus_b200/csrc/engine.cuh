@@ -362,12 +362,21 @@ struct Msm {
       BPP_LAUNCH(k, n_jobs, SJ_THREADS, smem, pl, dyn_per_job, scalars, pidx, d_job_start, offsets, counts, sorted);
     } else {
       BPP_CK(cudaMemsetAsync(counts, 0, (size_t)n_keys * 4, ctx->stream));
-      const uint32_t dg = n_terms ? (ceil_div(n_terms, 256) < 148 * 16 ? ceil_div(n_terms, 256) : 148 * 16) : 1;
-      BPP_LAUNCH(msm_digits_kernel<0>, dg, 256, 0, pl, scalars, pidx, d_job_start, counts, sorted);
+      // window groups (msm_digits_kernel): one generic job whose references do not fit in L2 is scattered a few windows at a
+      // time, each pass filling the GPU, so that the slice being written (<= 32 MB) stays in L2 until it is complete
+      uint32_t n_groups = 1, gw = Wmax;
+      if (n_jobs == 1 && !pl.NBA && pl.WB && (uint64_t)n_terms * pl.WB * 4 > (48ull << 20)) {
+        gw = (uint32_t)((32ull << 20) / ((uint64_t)n_terms * 4));
+        gw = gw < 1 ? 1 : gw;
+        n_groups = ceil_div(pl.WB, gw);
+      }
+      uint32_t dg = n_terms ? (ceil_div(n_terms, 256) < 148 * 16 ? ceil_div(n_terms, 256) : 148 * 16) : 1;
+      if (n_groups > 1) dg = 148 * 8 * n_groups;  // 8 blocks of 256 threads per SM = one full wave per group
+      BPP_LAUNCH(msm_digits_kernel<0>, dg, 256, 0, pl, n_groups, gw, scalars, pidx, d_job_start, counts, sorted);
       BPP_LAUNCH(scan_tile_sums, n_tiles, SCAN_THREADS, 0, counts, n_keys, tiles);
       BPP_LAUNCH(scan_tile_offsets, 1, SCAN_THREADS, 0, tiles, n_tiles);
       BPP_LAUNCH(scan_apply, n_tiles, SCAN_THREADS, 0, counts, n_keys, tiles, offsets, cursor);
-      BPP_LAUNCH(msm_digits_kernel<1>, dg, 256, 0, pl, scalars, pidx, d_job_start, cursor, sorted);
+      BPP_LAUNCH(msm_digits_kernel<1>, dg, 256, 0, pl, n_groups, gw, scalars, pidx, d_job_start, cursor, sorted);
     }
     const uint32_t ss_tiles = ceil_div(n_keys, SS_TILE);
     BPP_LAUNCH(sizesort_hist_kernel, ss_tiles, SS_THREADS, 0, counts, n_keys, bins);
@@ -437,10 +446,16 @@ struct Msm {
     if (pl.NBA) BPP_TRY(sets(n_jobs, 0, pl.qA, pl.NBA, pl.WB ? fixedres : results));
     if (pl.WB) {
       BPP_TRY(sets(n_setsB, pl.chunksA, pl.qB, pl.NBB, windows));
-      // jobs per warp: as few as keeps about two warps on every SM sub-partition (148 x 4)
-      uint32_t lanes = ceil_div(n_jobs, 148 * 4 * 2);
-      lanes = lanes > 32 ? 32 : lanes;
-      BPP_LAUNCH(msm_combine_kernel<C>, ceil_div(n_jobs, lanes), 32, 0, pl, lanes, windows, fixedres, results);
+      if constexpr (C::HAS_COOP4) {
+        // four warps per 32 jobs, one per SM sub-partition, each computing one of the four products of every level
+        BPP_LAUNCH(msm_combine4_kernel<C>, ceil_div(n_jobs, 32), 128, 0, pl, windows, fixedres, results);
+      } else {
+        // jobs per warp: one warp per SM at most. More single-warp blocks than that (tried: ~8 per SM) fill every register
+        // file with this kernel's 255-register threads and hold up the other stream's kernels for the whole Horner chain.
+        uint32_t lanes = ceil_div(n_jobs, 148);
+        lanes = lanes > 32 ? 32 : lanes;
+        BPP_LAUNCH(msm_combine_kernel<C>, ceil_div(n_jobs, lanes), 32, 0, pl, lanes, windows, fixedres, results);
+      }
     }
     return BPP_OK;
   }

@@ -115,25 +115,39 @@ __device__ __forceinline__ uint32_t msm_bits(const uint32_t* s, uint32_t off, ui
 }
 
 // MODE 0: histogram; MODE 1: scatter. Reference bit 31 = subtract the point.
+// The windows are cut into `n_groups` groups of `gw` consecutive windows and the grid into n_groups equal parts: part g makes
+// one pass over all terms for the windows of group g only (the signed-digit carry into the group's first window is recomputed
+// from the lower bits, a few integer instructions per skipped window). With one group this is the plain kernel. With several,
+// the blocks that run at the same time touch only that group's keys: for a single large generic MSM (one bucket set per
+// window) the counters and the slice of `sorted` they scatter into — 2^22 points: 16 MB per window against 252 MB in all —
+// stay in L2 until they are complete, instead of every 4-byte reference going to DRAM as a partial sector write
+// (msm_digits<1> was 1.3 ms of a 7.4 ms MSM of 2^22 points).
 template <int MODE>
-__global__ void msm_digits_kernel(MsmPlan pl, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
+__global__ void msm_digits_kernel(MsmPlan pl, uint32_t n_groups, uint32_t gw, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
                                   const uint32_t* __restrict__ job_start, uint32_t* __restrict__ counts_or_cursor,
                                   uint32_t* __restrict__ sorted) {
-  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < pl.n_terms; t += gridDim.x * blockDim.x) {
-    uint32_t s[8];
-    const uint4* sp = reinterpret_cast<const uint4*>(scalars + 8ull * t);
-    uint4 a = __ldg(sp), b = __ldg(sp + 1);
-    s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
-    const uint32_t job = msm_find_job(job_start, pl.n_jobs, pl.uniform, t);
+  const uint32_t bpg = gridDim.x / n_groups;  // blocks per group (the host makes gridDim.x a multiple of n_groups)
+  const uint32_t grp = blockIdx.x / bpg, blk = blockIdx.x - grp * bpg;
+  const uint32_t w_lo = grp * gw;
+  for (uint32_t t = blk * blockDim.x + threadIdx.x; t < pl.n_terms; t += bpg * blockDim.x) {
     const uint32_t p = pidx[t];
     const bool fixed = p < pl.n_fixed;
     const uint32_t c = fixed ? pl.cA : pl.cB, W = fixed ? pl.WA : pl.WB;
+    if (w_lo >= W) continue;
+    const uint32_t w_hi = w_lo + gw < W ? w_lo + gw : W;
+    uint32_t s[8];
+    const uint4* sp = reinterpret_cast<const uint4*>(scalars + 8ull * t);
+    // several passes over the scalars: streaming loads, so that they do not push the group's slice of `sorted` out of L2
+    uint4 a = n_groups > 1 ? __ldcs(sp) : __ldg(sp), b = n_groups > 1 ? __ldcs(sp + 1) : __ldg(sp + 1);
+    s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
+    const uint32_t job = msm_find_job(job_start, pl.n_jobs, pl.uniform, t);
     const uint32_t half = 1u << (c - 1);
     const uint32_t keybase = fixed ? job * pl.NBA : pl.keysA + job * pl.WB * pl.NBB;
     const uint32_t refbase = fixed ? p : pl.wtab_points + (p - pl.n_fixed);
     const uint32_t flip = (fixed && (pl.order[0] | pl.order[7])) ? msm_fold_half(pl, s) : 0u;
     uint32_t carry = 0;
-    for (uint32_t w = 0; w < W; w++) {
+    for (uint32_t w = 0; w < w_lo; w++) carry = (msm_bits(s, w * c, c) + carry) > half;
+    for (uint32_t w = w_lo; w < w_hi; w++) {
       uint32_t raw = msm_bits(s, w * c, c) + carry;
       uint32_t neg = raw > half;
       uint32_t mag = neg ? (1u << c) - raw : raw;
@@ -767,6 +781,98 @@ msm_combine_kernel(MsmPlan pl, uint32_t lanes, const uint32_t* __restrict__ wind
     load_words<C::EXT_WORDS>(acc, fixed_res + (size_t)job * C::EXT_WORDS);
   }
   store_words<C::EXT_WORDS>(results + (size_t)job * C::EXT_WORDS, acc);
+}
+
+// The same Horner pass for curves whose policy has the four-role point operations (C::HAS_COOP4: Ed25519). ONE warp already
+// saturates the multiply pipe of its SM sub-partition whatever its number of active lanes (72 IMAD.WIDE at ~4.6 issue cycles
+// each per field multiply), so the serial chain of ~SCALAR_BITS doublings cannot be shortened inside a warp — spreading the
+// four independent multiplies of a doubling over four LANES was measured slower. Here they go to four WARPS of a
+// block, i.e. to the four sub-partitions of an SM: warp r computes the r-th product of each of the two levels of a doubling /
+// addition, lane l of every warp works on job 32 * blockIdx.x + l, and the operands cross warps through shared memory (two
+// barriers per point operation). Role r keeps coordinate r of the accumulator (X, Y, Z, T) in registers; X and Y are also
+// published in shared memory because three roles read them.
+template <class C>
+__global__ void __launch_bounds__(128)
+msm_combine4_kernel(MsmPlan pl, const uint32_t* __restrict__ windows, const uint32_t* __restrict__ fixed_res, uint32_t* __restrict__ results) {
+  typedef typename C::F F;
+  __shared__ uint32_t sh_l1[4][8][32];  // level-1 products of the operation in flight
+  __shared__ uint32_t sh_xy[2][8][32];  // X, Y of the accumulator
+  const uint32_t lane = threadIdx.x & 31, role = threadIdx.x >> 5;
+  const uint32_t job = blockIdx.x * 32 + lane;
+  const bool live = job < pl.n_jobs;
+  const uint32_t jj = live ? job : 0;  // idle lanes shadow job 0 (every thread has to reach the barriers)
+  auto put = [&](uint32_t (*buf)[8][32], uint32_t slot, const F& v) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) buf[slot][i][lane] = v.v[i];
+  };
+  auto get = [&](uint32_t (*buf)[8][32], uint32_t slot, F& v) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) v.v[i] = buf[slot][i][lane];
+  };
+  // level 2 of both operations: E F G H from the four level-1 values, then this role's product
+  auto finish = [&](F& mine, const F& e, const F& f, const F& g, const F& h) {
+    if (role == 0) fe_mul(mine, e, f);
+    else if (role == 1) fe_mul(mine, g, h);
+    else if (role == 2) fe_mul(mine, f, g);
+    else fe_mul(mine, e, h);
+    if (role < 2) put(sh_xy, role, mine);
+    __syncthreads();
+  };
+  // acc += q (q: extended point in global memory); add-2008-hwcd-3 with k = 2d
+  auto add_point = [&](F& mine, const uint32_t* q) {
+    F v, x, y, qx, qy;
+    if (role < 2) {
+      get(sh_xy, 0, x); get(sh_xy, 1, y);
+      C::load_fe(qx, q); C::load_fe(qy, q + 8);
+      F t0, t1;
+      if (role == 0) { fe_sub(t0, y, x); fe_sub(t1, qy, qx); } else { fe_add(t0, y, x); fe_add(t1, qy, qx); }
+      fe_mul(v, t0, t1);                       // A = (Y1-X1)(Y2-X2)   |   B = (Y1+X1)(Y2+X2)
+    } else if (role == 2) {
+      C::load_fe(qx, q + 16);
+      fe_mul(v, mine, qx); fe_dbl(v, v);       // D = 2 Z1 Z2
+    } else {
+      C::load_fe(qx, q + 24);
+      fe_mul(v, mine, qx); fe_mul(v, v, C::k_d2());  // C = 2d T1 T2
+    }
+    put(sh_l1, role, v);
+    __syncthreads();
+    F a, b, c, d, e, f, g, h;
+    get(sh_l1, 0, a); get(sh_l1, 1, b); get(sh_l1, 3, c); get(sh_l1, 2, d);
+    fe_sub(e, b, a); fe_sub(f, d, c); fe_add(g, d, c); fe_add(h, b, a);
+    finish(mine, e, f, g, h);
+  };
+  auto dbl_point = [&](F& mine) {  // dbl-2008-hwcd, a = -1
+    F v;
+    if (role == 3) { F x, y; get(sh_xy, 0, x); get(sh_xy, 1, y); fe_add(v, x, y); fe_sqr(v, v); }  // (X+Y)^2
+    else fe_sqr(v, mine);                                                                          // X^2 | Y^2 | Z^2
+    put(sh_l1, role, v);
+    __syncthreads();
+    F a, b, c, e, f, g, h;
+    get(sh_l1, 0, a); get(sh_l1, 1, b); get(sh_l1, 2, c); get(sh_l1, 3, e);
+    fe_dbl(c, c);
+    fe_sub(e, e, a); fe_sub(e, e, b);
+    fe_sub(g, b, a);
+    fe_sub(f, g, c);
+    fe_add(h, a, b); fe_neg(h, h);
+    finish(mine, e, f, g, h);
+  };
+  F mine;
+  const uint32_t* base = pl.WB ? windows + (size_t)jj * pl.WB * C::EXT_WORDS : fixed_res + (size_t)jj * C::EXT_WORDS;
+  C::load_fe(mine, base + (pl.WB ? (size_t)(pl.WB - 1) * C::EXT_WORDS : 0) + 8 * role);
+  if (role < 2) put(sh_xy, role, mine);
+  __syncthreads();
+  if (pl.WB) {
+    for (int w = (int)pl.WB - 2; w >= 0; w--) {
+      for (uint32_t k = 0; k < pl.cB; k++) dbl_point(mine);
+      add_point(mine, base + (size_t)w * C::EXT_WORDS);
+    }
+    if (pl.NBA) add_point(mine, fixed_res + (size_t)jj * C::EXT_WORDS);
+  }
+  if (live) {
+    uint4* o = reinterpret_cast<uint4*>(results + (size_t)job * C::EXT_WORDS + 8 * role);
+    o[0] = make_uint4(mine.v[0], mine.v[1], mine.v[2], mine.v[3]);
+    o[1] = make_uint4(mine.v[4], mine.v[5], mine.v[6], mine.v[7]);
+  }
 }
 
 // thread per job: results[job] += part[job] (joins the two segments of Msm::run)

@@ -64,12 +64,14 @@ __global__ void base_mul_kernel(uint32_t n, const uint32_t* __restrict__ mult, u
 }
 
 // K5 terms — V = Fr(v as i32) * g + gamma * h  (range/prover.rs:36-39, publickey.rs:50-52)
+// full_u64: V = Fr(v) * g + gamma * h with all 64 bits of v (bpp_commit_batch_u64) — what an n = 64 prover needs, since the
+// prover itself uses every bit of v (range/mod.rs:260-277) and the reference's cast makes v >= 2^31 unprovable.
 template <class M>
-__global__ void commit_terms_kernel(uint32_t count, const uint64_t* __restrict__ v, const uint32_t* __restrict__ gamma,
+__global__ void commit_terms_kernel(uint32_t count, uint32_t full_u64, const uint64_t* __restrict__ v, const uint32_t* __restrict__ gamma,
                                     uint32_t* __restrict__ scalars, uint32_t* __restrict__ pidx, uint8_t* __restrict__ bad) {
   uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= count) return;
-  sc_store<M>(scalars + 16 * (size_t)t, Sc<M>::from_i32((int32_t)(uint32_t)v[t]));
+  sc_store<M>(scalars + 16 * (size_t)t, full_u64 ? Sc<M>::from_u64(v[t]) : Sc<M>::from_i32((int32_t)(uint32_t)v[t]));
   bool ok = Sc<M>::canonical_ok(gamma + 8 * (size_t)t);
   for (int i = 0; i < 8; i++) scalars[16 * (size_t)t + 8 + i] = ok ? gamma[8 * (size_t)t + i] : 0;
   if (!ok) bad[0] = 1;

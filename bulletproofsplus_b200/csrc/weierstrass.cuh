@@ -28,6 +28,7 @@ struct Weierstrass {
   // no FP64 accumulator path for the Montgomery-form base fields (Ed25519 has one; the names exist so that the hybrid
   // kernel template compiles, it is never launched with HYB = true for these curves)
   static constexpr bool HAS_F64 = false;
+  static constexpr bool HAS_COOP4 = false;
   typedef Ext AccF;
   BPP_DEV static void store_table_point_f(uint32_t* dst, const Aff& q) { store_words<AFF_WORDS>(dst, q); }
   BPP_DEV static void accf_init(AccF& p, const uint32_t* q, uint32_t neg) { init_from_ptr(p, q, neg); }

@@ -76,6 +76,10 @@ void bpp_pk_free(bpp_pk* pk);
 /* ---- RangeProver::commit / PublicKey::commitment (range/prover.rs:28-42, publickey.rs:50-52) ----- */
 /* V_i = Fr(v_i as i32)*g + gamma_i*h  (the i32 cast of prover.rs:37 is mirrored) */
 int bpp_commit_batch(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out_points);
+/* V_i = Fr(v_i)*g + gamma_i*h with all 64 bits of v_i: the commitment an n = 64 range proof is about. The reference's cast
+ * (prover.rs:37) wraps v >= 2^31, for which its own prover — which uses every bit of v, range/mod.rs:260-277 — can then never
+ * produce a verifying proof; the Fiat-Shamir helpers of the host mirrors use this entry. */
+int bpp_commit_batch_u64(bpp_ctx* ctx, const bpp_pk* pk, const uint64_t* v, const uint8_t* gamma, size_t count, uint8_t* out_points);
 
 /* ---- MulVec::calculate (bls12_381/building_block/mulvec.rs:20-33) -------------------------------- */
 int bpp_msm(bpp_ctx* ctx, int curve, const uint8_t* scalars, const uint8_t* points, size_t k, uint8_t* out_point);

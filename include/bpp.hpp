@@ -148,6 +148,13 @@ class PublicKey {
     detail::check(ctx_, bpp_commit_batch(ctx_, pk_.get(), &v, gamma.e.data(), 1, p.bytes.data()), "commitment");
     return p;
   }
+  // all 64 bits of v (bpp_commit_batch_u64): the commitment an n = 64 proof with real Fiat-Shamir is about
+  Point commitment_u64(uint64_t v, const PrimeFieldElem& gamma) const {
+    Point p;
+    p.bytes.resize(pb_);
+    detail::check(ctx_, bpp_commit_batch_u64(ctx_, pk_.get(), &v, gamma.e.data(), 1, p.bytes.data()), "commitment_u64");
+    return p;
+  }
   size_t len() const { return len_; }
   Curve curve() const { return curve_; }
   size_t point_bytes() const { return pb_; }
@@ -190,6 +197,12 @@ class RangeProver {
     v_vec.push_back(v);
     gamma_vec.push_back(gamma);
     commitment_vec.push_back(pk.commitment(v, gamma));
+  }
+  // without the reference's `v as i32` (prover.rs:37): use with prove_with_transcript when values may reach 2^31
+  void commit_u64(const PublicKey& pk, uint64_t v, const PrimeFieldElem& gamma) {
+    v_vec.push_back(v);
+    gamma_vec.push_back(gamma);
+    commitment_vec.push_back(pk.commitment_u64(v, gamma));
   }
 };
 

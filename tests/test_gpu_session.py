@@ -158,3 +158,20 @@ def test_default_nonces_are_fresh_and_proofs_verify(api, ctx):
     Vl = [Vs[i * m:(i + 1) * m] for i in range(count)]
     assert api.verify_batch_fs(pk, n, m, proofs, Vl, transcripts=label()) == [0] * count
     assert api.verify_batch_fs(pk, n, m, again, Vl, transcripts=label()) == [0] * count
+
+
+def test_fs_flow_proves_values_above_2_pow_31(api, ctx, oracle):
+    """bpp_commit_batch mirrors the reference's `v as i32` (prover.rs:37), so with it no n = 64 proof of
+    v >= 2^31 can verify. bpp_commit_batch_u64 commits to all 64 bits; the Fiat-Shamir helpers use it."""
+    from bulletproofsplus_b200 import merlin
+    n, m = 64, 2
+    pk = api.PublicKey.new(n * m, 0, ctx)
+    vs, gs = [2**63 + 12345, 2**31], [17, 19]
+    V64 = pk.commit_batch(vs, gs, full_u64=True)
+    q = api.ORDERS[0]
+    assert V64 == [oracle.scalar_mul(0, (v + 2 * g) % q) for v, g in zip(vs, gs)]          # g, h = 1g, 2g
+    assert pk.commit_batch(vs, gs) == [oracle.commit(0, [v], [g]) for v, g in zip(vs, gs)]  # the quirk stays where parity needs it
+    assert pk.commit_batch(vs, gs) != V64
+    proofs = api.prove_batch_fs(pk, n, m, vs, gs, [merlin.Transcript(b"u64")])
+    assert api.verify_batch_fs(pk, n, m, proofs, [V64], transcripts=[merlin.Transcript(b"u64")]) == [0]
+    assert api.verify_batch_fs(pk, n, m, proofs, [pk.commit_batch(vs, gs)], transcripts=[merlin.Transcript(b"u64")]) == [1]
