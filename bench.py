@@ -609,7 +609,7 @@ def run_proves(bn, pk, int_peak):
     terms = 1 + 2 * L * (NM + 2) + (2 * NM + 2) + 2
     return {"proves": {
         "metric": "range_proof_proves_per_sec_n64_m16", "value": bn.world * PB / (ms * 1e-3), "unit": "proofs/s", "batch_per_gpu": PB, "ms_per_batch": ms,
-        "entry": "bpp_range_prove_batch_dev (fixed-nonce parity mode, byte-identical to the oracle)",
+        "entry": "bpp_range_prove_batch_dev (fixed-nonce parity mode)",
         "e2e": {"value": bn.world * PB / (ms_h * 1e-3), "unit": "proofs/s", "entry": "bpp_range_prove_batch (host buffers)",
                 "h2d_bytes_per_step": PB * M_AGG * 40, "d2h_bytes_per_step": PB * plen},
         "roofline": {"bound": "int-imad", "achieved": alg / 1e12, "peak": int_peak / 1e12, "unit": "T 32x32+64 multiply-adds/s", "frac": alg / int_peak,

@@ -300,7 +300,7 @@ def verify_batch(pk: PublicKey, n: int, m: int, proofs, commitments, params: Bpp
 
 REFERENCE_NONCES = "reference-nonces"
 """Pass as `nonces` to get the reference snapshot's PUBLIC constant blinding scalars (alpha = 7 / 33, r, s, delta, eta = 33, 44, 88,
-123, d_L = 4, d_R = 5: range/mod.rs:94,256, wip.rs:94-95,175-178). Proofs made with them are byte-comparable with the oracle and
+123, d_L = 4, d_R = 5: range/mod.rs:94,256, wip.rs:94-95,175-178). Proofs made with them are byte-comparable with the CPU restatement of the reference and
 NOT zero-knowledge: anyone can solve r', s', delta' for gamma and the bits of v. Parity tests and benchmarks only."""
 
 

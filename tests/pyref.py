@@ -114,6 +114,53 @@ def ristretto_decode(b):
     return x, y
 
 
+
+# ---- RFC 9496 §4.3.4: element derivation (hash-to-ristretto255), for the hash-derived generators of bpp_pk_new_hashed
+ONE_MINUS_D_SQ = (1 - ED_D * ED_D) % P25519
+D_MINUS_ONE_SQ = (ED_D - 1) * (ED_D - 1) % P25519
+SQRT_AD_MINUS_ONE = 25063068953384623474111414158702152701244531502492656460079210482610430750235
+assert SQRT_AD_MINUS_ONE * SQRT_AD_MINUS_ONE % P25519 == (-ED_D - 1) % P25519
+
+
+def ristretto_map(t):
+    """MAP of RFC 9496 §4.3.4 -> affine (x, y) on edwards25519."""
+    p = P25519
+    r = SQRT_M1 * t % p * t % p
+    u = (r + 1) * ONE_MINUS_D_SQ % p
+    v = (-1 - r * ED_D) * (r + ED_D) % p
+    was_square, s = sqrt_ratio_m1(u, v)
+    s_prime = s * t % p
+    if not _is_neg(s_prime):
+        s_prime = (-s_prime) % p
+    if not was_square:
+        s = s_prime
+    c = (p - 1) if was_square else r
+    N = (c * (r - 1) % p * D_MINUS_ONE_SQ - v) % p
+    w0 = 2 * s * v % p
+    w1 = N * SQRT_AD_MINUS_ONE % p
+    w2 = (1 - s * s) % p
+    w3 = (1 + s * s) % p
+    X, Y, Z = w0 * w3 % p, w2 * w1 % p, w1 * w3 % p
+    zi = pow(Z, -1, p)
+    return X * zi % p, Y * zi % p
+
+
+def ristretto_from_uniform_bytes(b: bytes):
+    """64 uniform bytes -> group element (affine edwards25519 representative)."""
+    assert len(b) == 64
+    t1 = (int.from_bytes(b[:32], "little") & ((1 << 255) - 1)) % P25519
+    t2 = (int.from_bytes(b[32:], "little") & ((1 << 255) - 1)) % P25519
+    return ed_add(ristretto_map(t1), ristretto_map(t2))
+
+
+def hashed_generator_seed(domain_sep: bytes, label: bytes, index: int) -> bytes:
+    """The 64 uniform bytes bpp_pk_new_hashed feeds to the element derivation for one generator (include/bpp.h)."""
+    return hashlib.sha512(b"bpp-b200 generators v1" + len(domain_sep).to_bytes(4, "little") + domain_sep + label + index.to_bytes(8, "little")).digest()
+
+
+def hashed_generator(domain_sep: bytes, label: bytes, index: int) -> bytes:
+    return ristretto_encode(ristretto_from_uniform_bytes(hashed_generator_seed(domain_sep, label, index)))
+
 # ---------------------------------------------------------------- short Weierstrass a = 0
 SECP_P = 2**256 - 2**32 - 977
 SECP_N = 0xFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFEBAAEDCE6AF48A03BBFD25E8CD0364141

@@ -370,3 +370,12 @@ def test_b2_protocol_equals_b1(oracle):
         assert [oracle.range_verify(R, n, m, V, proof), oracle.range_verify(R, n, m, V, bytes(bad))] == want == [0, 1]
     finally:
         oracle.set_msm_backend(0, 1)
+
+
+def test_pyref_hash_to_ristretto_rfc9496_vector():
+    """RFC 9496 appendix A.3: SHA-512 of the label, then the element derivation of §4.3.4 (pins tests/pyref.py, the parity
+    reference of the hash-derived generators)."""
+    import hashlib
+    lab = b"Ristretto is traditionally a short shot of espresso coffee"
+    got = pyref.ristretto_encode(pyref.ristretto_from_uniform_bytes(hashlib.sha512(lab).digest()))
+    assert got.hex() == "3066f82a1a747d45120d1740f14358531a8f04bbffe6a819f86dfe50f44a0a46"
