@@ -491,19 +491,37 @@ def main():
     extras = {}
     cpu = None
     if not args.no_extras:
+        # A failing extra section must not lose the headline line: its error is recorded under `extras_errors` instead. At N > 1
+        # a section that raises on one rank only would leave the others waiting in a collective, so there the error is fatal.
+        errors = {}
+
+        def section(name, fn):
+            try:
+                extras.update(fn())
+            except Exception as e:  # noqa: BLE001
+                if world > 1:
+                    raise
+                import traceback
+                errors[name] = f"{type(e).__name__}: {e} | {traceback.format_exc().splitlines()[-3].strip()}"
+
         # per-GPU sections that shard trivially (every rank runs its own; max over ranks) and the multi-rank sections
-        extras.update(run_fs_verify(bn, pk, B))
-        extras.update(run_proves(bn, pk, int_peak))
-        extras.update(run_config4(bn))
+        section("verify_per_proof_challenges", lambda: run_fs_verify(bn, pk, B))
+        section("proves", lambda: run_proves(bn, pk, int_peak))
+        section("config4", lambda: run_config4(bn))
         if world > 1:
-            extras["msm_point_range_split"] = run_msm_split(bn, int_peak)
+            section("msm_point_range_split", lambda: {"msm_point_range_split": run_msm_split(bn, int_peak)})
         if world == 1:
-            extras.update(run_configs_2_3(bn))
-            extras.update(run_msm_sweep(bn, int_peak))
+            section("configs_2_3", lambda: run_configs_2_3(bn))
+            section("msm_sweep", lambda: run_msm_sweep(bn, int_peak))
             if rank == 0:
-                cpu = cpu_baselines(os.cpu_count() or 1)
-                if "proves" in extras:
-                    extras["proves"]["cpu_baseline"] = cpu.pop("prove")
+                try:
+                    cpu = cpu_baselines(os.cpu_count() or 1)
+                    if "proves" in extras:
+                        extras["proves"]["cpu_baseline"] = cpu.pop("prove")
+                except Exception as e:  # noqa: BLE001
+                    errors["cpu_baseline"] = f"{type(e).__name__}: {e}"
+        if errors:
+            extras["extras_errors"] = errors
 
     if rank == 0:
         line = {
@@ -637,7 +655,7 @@ def run_configs_2_3(bn):
     proof = api.WeightedInnerProductProof.prove(pk, a, b, ypow, gamma)
     dl = (sum(a[i] * 3 * (i + 1) + b[i] * 5 * (i + 1) + a[i] * b[i] * ypow[i] for i in range(N)) + 2 * gamma) % ELL
     one = api.Points.from_multipliers((1).to_bytes(32, "little"), 0, ctx)
-    P = one.msm(dl.to_bytes(32, "little"))  # the commitment a b-weighted-inner-product prover would publish, as dl * g
+    P = one.msm(dl.to_bytes(32, "little"))[0]  # the commitment a b-weighted-inner-product prover would publish, as dl * g
     zeros = [0] * N
     proof.verify(pk, ypow, zeros, zeros, 0, [], P, [])
     enc = lambda v: b"".join(int(x).to_bytes(32, "little") for x in v)
@@ -775,7 +793,7 @@ def run_msm_split(bn, int_peak):
     raw = bytes(d_dls.cpu().numpy().tobytes())
     total = sum(int.from_bytes(raw[32 * r:32 * r + 32], "little") for r in range(world)) % ELL
     one = api.Points.from_multipliers((1).to_bytes(32, "little"), 0, ctx)
-    want = one.msm(total.to_bytes(32, "little"))
+    want = one.msm(total.to_bytes(32, "little"))[0]
     got = bytes(d_out.cpu().numpy().tobytes())
     ok = torch.tensor([1 if got == want else 0], dtype=torch.int32, device=dev)
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)

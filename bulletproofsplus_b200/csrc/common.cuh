@@ -98,6 +98,66 @@ BPP_DEV void sqr_wide_n(uint32_t* r, const uint32_t* a) {
   asm volatile("madc.lo.cc.u32 %0, %2, %2, %0; madc.hi.u32 %1, %2, %2, %1;" : "+r"(r[2 * NL - 2]), "+r"(r[2 * NL - 1]) : "r"(a[NL - 1]));
 }
 
+// r[0..16) = a * b for 8-limb operands with one level of Karatsuba: three 4 x 4 products (48 wide multiplies) instead of 64.
+// The 16 multiplies saved cost ~60 extra integer additions — on sm_100a a gain, because IMAD.WIDE holds the FMA-heavy pipe
+// ~4.2-4.6 cycles per warp instruction (the pipe the MSM kernels saturate: 88 % busy) while IADD3 / LOP3 issue to the ALU
+// pipe, which those kernels leave mostly idle (ncu: issue slots 44 %).
+//   a = a0 + 2^128 a1, b = b0 + 2^128 b1:  a b = z0 + 2^128 ((a0 + a1)(b0 + b1) - z0 - z2) + 2^256 z2
+BPP_DEV void mul_wide_8_karatsuba(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+  uint32_t z0[8], z2[8], zm[8], sa[4], sb[4], m[9], ca, cb;
+  mul_wide_n<4>(z0, a, b);
+  mul_wide_n<4>(z2, a + 4, b + 4);
+  asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(sa[0]) : "r"(a[0]), "r"(a[4]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(sa[1]) : "r"(a[1]), "r"(a[5]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(sa[2]) : "r"(a[2]), "r"(a[6]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(sa[3]) : "r"(a[3]), "r"(a[7]));
+  asm volatile("addc.u32 %0, 0, 0;" : "=r"(ca));
+  asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(sb[0]) : "r"(b[0]), "r"(b[4]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(sb[1]) : "r"(b[1]), "r"(b[5]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(sb[2]) : "r"(b[2]), "r"(b[6]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(sb[3]) : "r"(b[3]), "r"(b[7]));
+  asm volatile("addc.u32 %0, 0, 0;" : "=r"(cb));
+  mul_wide_n<4>(zm, sa, sb);
+  // m = (sa + 2^128 ca)(sb + 2^128 cb) = zm + 2^128 (ca ? sb : 0) + 2^128 (cb ? sa : 0) + 2^256 (ca & cb)   (< 2^258: 9 limbs)
+  const uint32_t ma = 0u - ca, mb = 0u - cb;
+#pragma unroll
+  for (int i = 0; i < 4; i++) m[i] = zm[i];
+  asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(m[4]) : "r"(zm[4]), "r"(sb[0] & ma));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(m[5]) : "r"(zm[5]), "r"(sb[1] & ma));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(m[6]) : "r"(zm[6]), "r"(sb[2] & ma));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(m[7]) : "r"(zm[7]), "r"(sb[3] & ma));
+  asm volatile("addc.u32 %0, %1, 0;" : "=r"(m[8]) : "r"(ca & cb));
+  asm volatile("add.cc.u32 %0, %0, %1;" : "+r"(m[4]) : "r"(sa[0] & mb));
+  asm volatile("addc.cc.u32 %0, %0, %1;" : "+r"(m[5]) : "r"(sa[1] & mb));
+  asm volatile("addc.cc.u32 %0, %0, %1;" : "+r"(m[6]) : "r"(sa[2] & mb));
+  asm volatile("addc.cc.u32 %0, %0, %1;" : "+r"(m[7]) : "r"(sa[3] & mb));
+  asm volatile("addc.u32 %0, %0, 0;" : "+r"(m[8]));
+  // m -= z0; m -= z2   (the middle term a0 b1 + a1 b0 is non-negative: no borrow out)
+  asm volatile("sub.cc.u32 %0, %0, %1;" : "+r"(m[0]) : "r"(z0[0]));
+#pragma unroll
+  for (int i = 1; i < 8; i++) asm volatile("subc.cc.u32 %0, %0, %1;" : "+r"(m[i]) : "r"(z0[i]));
+  asm volatile("subc.u32 %0, %0, 0;" : "+r"(m[8]));
+  asm volatile("sub.cc.u32 %0, %0, %1;" : "+r"(m[0]) : "r"(z2[0]));
+#pragma unroll
+  for (int i = 1; i < 8; i++) asm volatile("subc.cc.u32 %0, %0, %1;" : "+r"(m[i]) : "r"(z2[i]));
+  asm volatile("subc.u32 %0, %0, 0;" : "+r"(m[8]));
+  // r = z0 + 2^256 z2 + 2^128 m
+#pragma unroll
+  for (int i = 0; i < 4; i++) r[i] = z0[i];
+  asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(r[4]) : "r"(z0[4]), "r"(m[0]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[5]) : "r"(z0[5]), "r"(m[1]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[6]) : "r"(z0[6]), "r"(m[2]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[7]) : "r"(z0[7]), "r"(m[3]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[8]) : "r"(z2[0]), "r"(m[4]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[9]) : "r"(z2[1]), "r"(m[5]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[10]) : "r"(z2[2]), "r"(m[6]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[11]) : "r"(z2[3]), "r"(m[7]));
+  asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r[12]) : "r"(z2[4]), "r"(m[8]));
+  asm volatile("addc.cc.u32 %0, %1, 0;" : "=r"(r[13]) : "r"(z2[5]));
+  asm volatile("addc.cc.u32 %0, %1, 0;" : "=r"(r[14]) : "r"(z2[6]));
+  asm volatile("addc.u32 %0, %1, 0;" : "=r"(r[15]) : "r"(z2[7]));
+}
+
 // 128-bit vectorised global loads/stores of whole points (AoS, 32-byte aligned)
 template <int WORDS, class T>
 BPP_DEV void load_words(T& dst, const void* src) {

@@ -49,7 +49,11 @@ BPP_DEV void fe25519_reduce_wide(Fe25519& out, const uint32_t* t) {
 
 BPP_DEV void fe_mul(Fe25519& r, const Fe25519& a, const Fe25519& b) {
   uint32_t t[16];
+#ifdef BPP_FE_KARATSUBA
+  mul_wide_8_karatsuba(t, a.v, b.v);
+#else
   mul_wide_n<8>(t, a.v, b.v);
+#endif
   fe25519_reduce_wide(r, t);
 }
 // 36 wide products (28 off-diagonal, doubled by a shift, + 8 squares) instead of 64, then the same fold
