@@ -217,6 +217,13 @@ def run_reference(args, rank):
     emit(line)
 
 
+# ncu --set full captures of the dominant kernel at B = 2048 (profiles/): numbers copied from the committed reports, not live
+NCU_BUCKET = {"capture": "profiles/r02d_verify_fs_kernels_ncu_full_details.txt (msm_accumulate_kernel<Ed25519, 0>, fixed-base segment of the bucket path)",
+              "gpu_time_ms": 5.61, "sm_busy_pct": 88.4, "smsp__issue_active_pct": 43.6, "registers_per_thread": 106, "dram_pct_of_peak": 3.8,
+              "note": "the pipe that executes IMAD.WIDE is busy 88 % of the kernel's cycles: the kernel sits at the integer-multiply roofline of "
+                      "sm_100a although only 0.4 of the 32-bit IMAD issue rate is reached (every wide multiply-add holds the pipe ~3.5-4.6 clk)"}
+NCU_DIRECT = {"capture": None, "note": "no capture of direct_accumulate_kernel yet"}
+
 _REAL_STDOUT = None
 
 
@@ -332,6 +339,8 @@ def main():
     ap.add_argument("--prove-batch", type=int, default=256)
     ap.add_argument("--ref-proofs", type=int, default=2, help="reference arm: verifies per step (one thread)")
     ap.add_argument("--msm-max-log", type=int, default=22)
+    ap.add_argument("--table-gb", type=float, default=48.0, help="HBM budget of the key's direct fixed-base tables (bpp_pk_precompute); "
+                                                                   "0 = none: the bucket path")
     ap.add_argument("--no-extras", action="store_true", help="skip proves/s, configs 2-4, the MSM sweep and the CPU baseline")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -354,6 +363,12 @@ def main():
     B, K_steps = args.batch, args.steps
     NM = N_BITS * M_AGG
     pk = api.PublicKey.new(NM, _lib.RISTRETTO255, ctx)
+    # one-time key set-up, not in any timed region: every signed-digit multiple of every window point of every generator in HBM
+    t_tab = time.perf_counter()
+    table_c = pk.precompute(int(args.table_gb * 2**30)) if args.table_gb > 0 else 0
+    t_tab = time.perf_counter() - t_tab
+    table_W = -(-252 // table_c) if table_c else 0
+    table_bytes = (table_W + 1) * (1 << (table_c - 1)) * (2 + 2 * NM) * 128 if table_c else 0
     plen = lib.bpp_range_proof_len(0, N_BITS, M_AGG)
 
     # ---- synthetic workload: ROT distinct batches of B valid proofs, produced by the library's own prover ----
@@ -441,10 +456,11 @@ def main():
     # the auxiliary stream, so only the fixed-base share of the algorithmic count is credited to the timed launches
     n_fixed_terms = 2 + 2 * NM
     ach_kernel = B * acc_share * (n_fixed_terms / n_terms) * FIELD_MUL_IMAD / (hot_avg_ms * 1e-3) if hot_n else None
-    # what the kernel actually executes: fixed-base window tables (c = 12; 21 windows since the scalars are folded below ell/2, no
-    # doublings) for the 2050 generator terms: fewer additions than the algorithmic count above (the 39 per-proof points take
-    # 64 generic 4-bit windows each, outside the timed bracket)
-    exec_madds = B * (2 + 2 * NM) * 21
+    # what the kernel actually executes for the 2050 generator terms — fewer additions than the algorithmic count above (the 39
+    # per-proof points take 64 generic 4-bit windows each, outside the timed bracket):
+    #   direct tables (bpp_pk_precompute, window c): ceil(252 / c) table additions per term, nothing else
+    #   bucket path: window tables with c = 12: 21 windows (scalars folded below ell/2), one bucket set per proof, no doublings
+    exec_madds = B * (2 + 2 * NM) * (table_W if table_c else 21)
     exec_kernel = exec_madds * MIXED * FIELD_MUL_IMAD / (hot_avg_ms * 1e-3) if hot_n else None
     ach_whole = B * W * FIELD_MUL_IMAD / (elapsed_ms / K_steps * 1e-3)
     alg_bytes = B * (n_terms * (32 + 96) + 128)  # scalars + affine points read once, one point written
@@ -457,17 +473,17 @@ def main():
     roofline = {
         "bound": "int-imad", "bound_note": "integer multiply pipe: ~20k multiply-adds per 128 B term, so neither the HBM nor the tensor roofline "
                                                "applies (north_star asks for the integer-multiply roofline); HBM figures are in `hbm` below",
-        "kernel": "msm_accumulate_kernel<Ed25519> (+ its two long-bucket variants msm_accumulate_group_kernel<.,32|4>, timed together)",
+        "kernel": (f"direct_accumulate_kernel<Ed25519>: one table addition per {table_c}-bit window and generator term, straight from the key's "
+                   f"{table_bytes / 2**30:.1f} GB of direct tables (no buckets)") if table_c else
+                  "msm_accumulate_kernel<Ed25519> (+ its two long-bucket variants msm_accumulate_group_kernel<.,32|4>, timed together)",
         "achieved": ach_kernel / 1e12 if ach_kernel else None, "peak": int_peak / 1e12, "unit": "T 32x32+64 multiply-adds/s",
         "frac": (ach_kernel / int_peak) if ach_kernel else None,
-        # dram__bytes_read.sum + dram__bytes_write.sum of ONE msm_accumulate_kernel launch at this batch size (B = 2048), from the ncu
-        # --set full capture profiles/r01g_verify_kernels_ncu_full_details.txt: 1.220 GB + 0.511 GB. Not measured live.
-        "traffic": 1.732e9 if B == 2048 else None, "traffic_unit": "bytes per launch",
-        "ncu": {"capture": "profiles/r01g_verify_kernels_ncu_full_details.txt (msm_accumulate_kernel<Ed25519, 0>, fixed-base segment)",
-                "gpu_time_ms": 5.63, "sm__pipe_fmaheavy_cycles_active_pct": 87.9, "smsp__issue_active_pct": 43.7,
-                "active_lanes_per_warp_inst": 32.0, "registers_per_thread": 106, "dram_pct_of_peak": 3.8,
-                "note": "the pipe that executes IMAD.WIDE is busy 87.9 % of the kernel's cycles: the kernel sits at the integer-multiply roofline "
-                        "of sm_100a although only 0.4 of the 32-bit IMAD issue rate is reached (every wide multiply-add holds the pipe ~4.6 clk)"},
+        # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel at this batch size (B = 2048), from the ncu
+        # --set full captures named in `ncu` (not measured live); `traffic_algorithmic` = one 128-byte table line per addition + the
+        # 32-byte scalar and 4-byte index of every term, per launch
+        "traffic": NCU_DIRECT.get("dram_bytes") if table_c else (1.732e9 if B == 2048 else None), "traffic_unit": "bytes per launch",
+        "traffic_algorithmic": exec_madds * 128 + B * n_terms * 36,
+        "ncu": NCU_DIRECT if table_c else NCU_BUCKET,
         "peak_source": "bpp_int_peak_probe: 32-bit IMAD chains with loop-produced operands on all SMs, measured in this run — the "
                        "issue peak of the integer multiply pipe, which every form of 32x32 multiply shares",
         "pipe_ceiling": {"wide_chain_T_per_s": probe["wide_chain_per_s"] / 1e12, "wide_fused_T_per_s": probe["wide_fused_per_s"] / 1e12,
@@ -508,6 +524,8 @@ def main():
         section("verify_per_proof_challenges", lambda: run_fs_verify(bn, pk, B))
         section("proves", lambda: run_proves(bn, pk, int_peak))
         section("config4", lambda: run_config4(bn))
+        if table_c:
+            section("verify_bucket_path", lambda: run_bucket_path(bn, B))
         if world > 1:
             section("msm_point_range_split", lambda: {"msm_point_range_split": run_msm_split(bn, int_peak)})
         if world == 1:
@@ -529,6 +547,8 @@ def main():
             "warmup": args.warmup, "ms_per_step": elapsed_ms / K_steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u32 limbs (integer, GF(2^255-19) / mod ell)", "data": "synthetic",
             "config": {"workload": WORKLOAD, "batch_per_gpu": B, "parallelism": f"proofs sharded x{world}",
+                       "fixed_base_tables": ({"window_bits": table_c, "windows": table_W, "bytes": table_bytes, "build_s": t_tab,
+                                              "note": "bpp_pk_precompute: one-time key set-up, outside every timed region"} if table_c else None),
                        "challenge_mode": "the reference's constants (parity mode; challenge tables reused across calls). The same batch with "
                                          "per-proof Fiat-Shamir challenges is `verify_per_proof_challenges` in this line",
                        "l2": "256 MB memset between steps (inside the timed region); intermediates per step > L2"},
@@ -590,6 +610,27 @@ def run_fs_verify(bn, pk, B):
                                          "entry": "bpp_range_verify_batch_rlc_dev (all proofs valid: no fallback; one host sync per batch inside); "
                                                   "every rank combines its own shard, verdicts need no exchange"}
     return out
+
+
+def run_bucket_path(bn, B):
+    """The headline step on a key WITHOUT direct tables: the two-segment bucket MSM (per-job sort, size sort, bucket accumulation,
+    chunk / set reduction) that the direct tables replace — kept as the fallback for keys too large for tables and as the path of
+    the other curves; reported so that the two can be compared in one run."""
+    torch, lib, ctx, api = bn.torch, bn.lib, bn.ctx, bn.api
+    pk2 = api.PublicKey.new(N_BITS * M_AGG, 0, ctx)
+    pb, vb, _, _ = bn.make_proofs(pk2, N_BITS, M_AGG, B, seed=bn.rank * 1000 + 3)
+    d_pr, d_V = bn.to_dev(pb), bn.to_dev(vb)
+    d_vd = torch.full((B,), 255, dtype=torch.uint8, device=bn.dev)
+
+    def call():
+        ctx.check(lib.bpp_range_verify_batch_dev(ctx.h, pk2.handle, N_BITS, M_AGG, B, d_V.data_ptr(), d_pr.data_ptr(), None, d_vd.data_ptr()), "verify (buckets)")
+
+    bn.barrier()
+    ms = bn.timed(call, reps=5, warm=2, flush=True)
+    assert bool((d_vd == 0).all())
+    (ms,) = bn.max_over_ranks(ms)
+    return {"verify_bucket_path": {"value": bn.world * B / (ms * 1e-3), "unit": "proofs/s", "ms_per_step": ms, "batch_per_gpu": B,
+                                   "note": "same entry point, key without bpp_pk_precompute: window tables (c = 12) + buckets"}}
 
 
 def run_proves(bn, pk, int_peak):

@@ -44,6 +44,9 @@ extern "C" {
     pub fn bpp_kernel_launches(ctx: *const bpp_ctx) -> u64;
     pub fn bpp_sync(ctx: *mut bpp_ctx) -> c_int;
     pub fn bpp_pk_new(ctx: *mut bpp_ctx, curve: c_int, len: usize, out: *mut *mut bpp_pk) -> c_int;
+    pub fn bpp_pk_new_hashed(ctx: *mut bpp_ctx, curve: c_int, len: usize, domain_sep: *const u8, domain_sep_len: usize, out: *mut *mut bpp_pk) -> c_int;
+    pub fn bpp_pk_precompute(ctx: *mut bpp_ctx, pk: *mut bpp_pk, max_bytes: usize, window_bits: *mut c_int) -> c_int;
+    pub fn bpp_pk_msm(ctx: *mut bpp_ctx, pk: *const bpp_pk, scalars: *const u8, n_jobs: usize, out_points: *mut u8) -> c_int;
     pub fn bpp_pk_export(ctx: *mut bpp_ctx, pk: *const bpp_pk, g: *mut u8, h: *mut u8, G: *mut u8, H: *mut u8) -> c_int;
     pub fn bpp_pk_len(pk: *const bpp_pk) -> usize;
     pub fn bpp_pk_free(pk: *mut bpp_pk);

@@ -113,6 +113,12 @@ impl PublicKey {
         check(unsafe { bpp_pk_new(ctx(), BPP_RISTRETTO255, len, &mut h) }, "PublicKey::new");
         PublicKey { h, len }
     }
+    /// Hash-derived generators (`bpp_pk_new_hashed`): no known discrete-log relations — use this outside parity tests.
+    pub fn new_hashed(len: usize, domain_sep: &[u8]) -> Self {
+        let mut h = ptr::null_mut();
+        check(unsafe { bpp_pk_new_hashed(ctx(), BPP_RISTRETTO255, len, domain_sep.as_ptr(), domain_sep.len(), &mut h) }, "PublicKey::new_hashed");
+        PublicKey { h, len }
+    }
     pub fn len(&self) -> usize { self.len }
     /// (g, h, G_vec, H_vec) — the pub fields of the reference struct
     pub fn generators(&self) -> (Point, Point, Vec<Point>, Vec<Point>) {

@@ -16,7 +16,7 @@ ERROR_NAMES = ["OK", "VERIFICATION", "FORMAT", "LENGTH", "NOT_POW2", "GENERATORS
 # every symbol include/bpp.h declares (checked by tests/test_abi.py against the header and the .so)
 SYMBOLS = [
     "bpp_init", "bpp_destroy", "bpp_last_error", "bpp_point_bytes", "bpp_range_proof_len", "bpp_wip_proof_len",
-    "bpp_kernel_launches", "bpp_sync", "bpp_pk_new", "bpp_pk_export", "bpp_pk_len", "bpp_pk_free", "bpp_commit_batch", "bpp_commit_batch_u64", "bpp_msm",
+    "bpp_kernel_launches", "bpp_sync", "bpp_pk_new", "bpp_pk_new_hashed", "bpp_pk_precompute", "bpp_pk_msm", "bpp_pk_export", "bpp_pk_len", "bpp_pk_free", "bpp_commit_batch", "bpp_commit_batch_u64", "bpp_msm",
     "bpp_points_upload", "bpp_points_from_multipliers", "bpp_points_len", "bpp_points_precompute", "bpp_points_free", "bpp_msm_prepared",
     "bpp_msm_prepared_dev", "bpp_raw_point_bytes", "bpp_msm_prepared_raw", "bpp_points_sum_raw", "bpp_msm_prepared_raw_dev", "bpp_points_sum_raw_dev", "bpp_points_sum_raw_noalloc_dev", "bpp_range_prove_batch",
     "bpp_range_verify_batch", "bpp_range_prove_batch_dev", "bpp_range_verify_batch_dev", "bpp_range_prove", "bpp_range_verify",
@@ -62,6 +62,9 @@ def load() -> C.CDLL:
     L.bpp_kernel_launches.argtypes = [vp]; L.bpp_kernel_launches.restype = C.c_uint64
     L.bpp_sync.argtypes = [vp]
     L.bpp_pk_new.argtypes = [vp, i, sz, C.POINTER(vp)]
+    L.bpp_pk_new_hashed.argtypes = [vp, i, sz, u8p, sz, C.POINTER(vp)]
+    L.bpp_pk_precompute.argtypes = [vp, vp, sz, C.POINTER(C.c_int)]
+    L.bpp_pk_msm.argtypes = [vp, vp, u8p, sz, u8p]
     L.bpp_pk_export.argtypes = [vp, vp, u8p, u8p, u8p, u8p]
     L.bpp_pk_len.argtypes = [vp]; L.bpp_pk_len.restype = sz
     L.bpp_pk_free.argtypes = [vp]; L.bpp_pk_free.restype = None

@@ -127,17 +127,38 @@ class Context:
 class PublicKey:
     """publickey.rs:13-18 — g, h, G_vec, H_vec live on the device; `.g .h .G_vec .H_vec` export them."""
 
-    def __init__(self, ctx: Context, curve: int, length: int):
+    def __init__(self, ctx: Context, curve: int, length: int, domain_sep: bytes | None = None):
         self.ctx, self.curve, self.length = ctx, curve, length
         self.pb = ctx.lib.bpp_point_bytes(curve)
         h = C.c_void_p()
-        ctx.check(ctx.lib.bpp_pk_new(ctx.h, curve, length, C.byref(h)), "pk_new")
+        if domain_sep is None:
+            ctx.check(ctx.lib.bpp_pk_new(ctx.h, curve, length, C.byref(h)), "pk_new")
+        else:
+            ctx.check(ctx.lib.bpp_pk_new_hashed(ctx.h, curve, length, domain_sep, len(domain_sep), C.byref(h)), "pk_new_hashed")
         self.handle = h
         self._exported = None
 
     @staticmethod
     def new(length: int, curve: int = _lib.RISTRETTO255, ctx: Context | None = None) -> "PublicKey":
         return PublicKey(ctx or Arith.init(), curve, length)
+
+    @staticmethod
+    def new_hashed(length: int, domain_sep: bytes, curve: int = _lib.RISTRETTO255, ctx: Context | None = None) -> "PublicKey":
+        """Hash-derived generators (no known discrete-log relations): the constructor to use outside parity tests."""
+        return PublicKey(ctx or Arith.init(), curve, length, domain_sep)
+
+    def precompute(self, max_bytes: int = 48 << 30) -> int:
+        """Build the direct fixed-base tables (bpp_pk_precompute) within max_bytes of HBM; returns the window width used."""
+        c = C.c_int(0)
+        self.ctx.check(self.ctx.lib.bpp_pk_precompute(self.ctx.h, self.handle, max_bytes, C.byref(c)), "pk_precompute")
+        return c.value
+
+    def msm(self, scalars, n_jobs: int = 1) -> list:
+        """n_jobs MSMs against [g, h, G.., H..] (bpp_pk_msm); scalars: flat list of n_jobs * (2 + 2 len) ints."""
+        q = ORDERS[self.curve]
+        out = C.create_string_buffer(n_jobs * self.pb)
+        self.ctx.check(self.ctx.lib.bpp_pk_msm(self.ctx.h, self.handle, b"".join(_sc(x % q) for x in scalars), n_jobs, out), "pk_msm")
+        return [out.raw[i * self.pb:(i + 1) * self.pb] for i in range(n_jobs)]
 
     def _export(self):
         if self._exported is None:

@@ -2,6 +2,8 @@
 #pragma once
 #include "engine.cuh"
 #include "proto_misc.cuh"
+#include "pk_hashed.cuh"
+#include "sha512.hpp"
 
 namespace bpp {
 
@@ -88,9 +90,53 @@ struct Api {
     if (pk->wtab) cudaFree(pk->wtab);
     if (pk->wtab_f) cudaFree(pk->wtab_f);
     if (pk->comb) cudaFree(pk->comb);
+    if (pk->dtab) cudaFree(pk->dtab);
     delete pk;
   }
-  static int pk_new(bpp_ctx* ctx, size_t len, bpp_pk** out) {
+  // Direct fixed-base tables (pk_direct.cuh): the widest window c in [8, 16] whose table fits in max_bytes. One-time cost: a
+  // few tens of milliseconds and (W + 1) * 2^(c-1) * 128 B per generator (40 GB for a 1024-generator key at c = 14).
+  static int pk_precompute(bpp_ctx* ctx, bpp_pk* pk, size_t max_bytes, int* c_out) {
+    if constexpr (!C::HAS_COOP4) {
+      ctx->err = "pk_precompute: direct tables are implemented for Ristretto255 only";
+      return BPP_ERR_UNSUPPORTED;
+    } else {
+      if (pk->dtab) { if (c_out) *c_out = (int)pk->cD; return BPP_OK; }
+      const uint32_t np = pk->n_points();
+      uint32_t c = 0, W = 0;
+      for (uint32_t cc = 16; cc >= 8; cc--) {
+        const uint32_t WW = dtab_windows(C::SCALAR_BITS, cc);
+        if (dtab_entries(np, cc, WW) * C::AFF_WORDS * 4 <= max_bytes) { c = cc; W = WW; break; }
+      }
+      if (!c) { ctx->err = "pk_precompute: max_bytes is too small for any window width >= 8"; return BPP_ERR_LENGTH; }
+      const size_t entries = dtab_entries(np, c, W);
+      uint32_t *dtab = nullptr, *base = nullptr;
+      cudaError_t e = cudaMalloc(&dtab, entries * C::AFF_WORDS * 4);
+      if (e == cudaSuccess) e = cudaMalloc(&base, (size_t)np * W * C::AFF_WORDS * 4);
+      if (e == cudaSuccess) e = ctx->buf[B_EXT].ensure((size_t)np * W * C::EXT_WORDS * 4);
+      if (e == cudaSuccess) {
+        wtab_build_kernel<C><<<ceil_div(np, 32), 32, 0, ctx->stream>>>(np, 0u, np, c, W, pk->table, base, ctx->buf[B_EXT].as<uint32_t>());
+        dtab_fill_kernel<C><<<ceil_div(np * W, 64), 64, 0, ctx->stream>>>(np, c, W, base, dtab);
+        dtab_normalise_kernel<C><<<(unsigned)((entries / DTAB_NORM + 128) / 128), 128, 0, ctx->stream>>>(entries, dtab);
+        ctx->launches += 3;
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+      }
+      if (base) cudaFree(base);
+      if (e != cudaSuccess) { if (dtab) cudaFree(dtab); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
+      pk->dtab = dtab; pk->cD = c; pk->WD = W;
+      if (c_out) *c_out = (int)c;
+      return BPP_OK;
+    }
+  }
+  static int pk_new(bpp_ctx* ctx, size_t len, bpp_pk** out) { return pk_new_impl(ctx, len, nullptr, 0, false, out); }
+  // Generators with no known relation between them: each is the RFC 9496 element derivation of SHA-512 output under the
+  // caller's domain separator (pk_hashed.cuh). Ristretto255 only. publickey.rs:21-48 stays the parity constructor (pk_new).
+  static int pk_new_hashed(bpp_ctx* ctx, size_t len, const uint8_t* domain_sep, size_t domain_len, bpp_pk** out) {
+    if (C::CURVE_ID != 0) { ctx->err = "pk_new_hashed: hash-to-group is implemented for Ristretto255 only"; return BPP_ERR_UNSUPPORTED; }
+    if (domain_len && !domain_sep) return BPP_ERR_LENGTH;
+    return pk_new_impl(ctx, len, domain_sep, domain_len, true, out);
+  }
+  static int pk_new_impl(bpp_ctx* ctx, size_t len, const uint8_t* domain_sep, size_t domain_len, bool hashed, bpp_pk** out) {
     if (len > (1u << 22)) return BPP_ERR_LENGTH;
     bpp_pk* pk = new bpp_pk();
     pk->curve = C::CURVE_ID; pk->len = len; pk->device = ctx->device;
@@ -103,8 +149,31 @@ struct Api {
     if (e == cudaSuccess) e = cudaMalloc(&pk->wtab, (size_t)np * pk->WA * C::AFF_WORDS * 4);
     if (e == cudaSuccess) e = cudaMalloc(&pk->comb, (size_t)2 * pk->comb_w * COMB_D * C::AFF_WORDS * 4);
     if (e != cudaSuccess) { pk_release(pk); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
-    pk_gen_kernel<C><<<ceil_div(np, 64), 64, 0, ctx->stream>>>((uint32_t)len, pk->table);
-    wtab_build_kernel<C><<<ceil_div(np, 32), 32, 0, ctx->stream>>>(np, pk->cA, pk->WA, pk->table, pk->wtab);
+    if constexpr (C::CURVE_ID == 0) {
+      if (hashed) {  // table order g, h, G[len], H[len]: labels 'g', 'h', 'G' + i, 'H' + i
+        std::vector<uint8_t> seeds((size_t)np * 64);
+        hashed_generator_seed(domain_sep, domain_len, 'g', 0, &seeds[0]);
+        hashed_generator_seed(domain_sep, domain_len, 'h', 0, &seeds[64]);
+        for (size_t i = 0; i < len; i++) {
+          hashed_generator_seed(domain_sep, domain_len, 'G', i, &seeds[(2 + i) * 64]);
+          hashed_generator_seed(domain_sep, domain_len, 'H', i, &seeds[(2 + len + i) * 64]);
+        }
+        cudaError_t e2 = ctx->buf[B_IN0].ensure(seeds.size());
+        if (e2 == cudaSuccess) e2 = cudaMemcpyAsync(ctx->buf[B_IN0].p, seeds.data(), seeds.size(), cudaMemcpyHostToDevice, ctx->stream);
+        if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(ctx->stream);  // `seeds` is pageable host memory going out of scope
+        if (e2 != cudaSuccess) { pk_release(pk); ctx->err = cudaGetErrorString(e2); return BPP_ERR_CUDA; }
+        pk_gen_hashed_kernel<<<ceil_div(np, 64), 64, 0, ctx->stream>>>(np, ctx->buf[B_IN0].as<uint8_t>(), pk->table);
+      } else {
+        pk_gen_kernel<C><<<ceil_div(np, 64), 64, 0, ctx->stream>>>((uint32_t)len, pk->table);
+      }
+    } else {
+      pk_gen_kernel<C><<<ceil_div(np, 64), 64, 0, ctx->stream>>>((uint32_t)len, pk->table);
+    }
+    {
+      cudaError_t e3 = ctx->buf[B_EXT].ensure((size_t)np * pk->WA * C::EXT_WORDS * 4);
+      if (e3 != cudaSuccess || pk->WA > WTAB_MAX_W) { pk_release(pk); ctx->err = e3 != cudaSuccess ? cudaGetErrorString(e3) : "window count"; return BPP_ERR_CUDA; }
+    }
+    wtab_build_kernel<C><<<ceil_div(np, 32), 32, 0, ctx->stream>>>(np, 0u, np, pk->cA, pk->WA, pk->table, pk->wtab, ctx->buf[B_EXT].as<uint32_t>());
     comb_build_kernel<C><<<ceil_div(2 * pk->comb_w * COMB_D, 64), 64, 0, ctx->stream>>>(pk->comb_w, pk->table, pk->comb);
     ctx->launches += 3;
     if (C::HAS_F64 && hybrid_pattern()) {  // the window tables once more, in the slot format of the FP64 accumulators (hybrid accumulation kernel)
@@ -117,6 +186,26 @@ struct Api {
     if (e != cudaSuccess) { pk_release(pk); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
     *out = pk;
     return BPP_OK;
+  }
+  // n_jobs MSMs against the key's own generators: out[j] = sum_i scalars[j][i] * table[i], table = g, h, G[len], H[len]
+  // (vector Pedersen commitments; also the test surface of the fixed-base paths). Fixed-base segment only.
+  static int pk_msm(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* scalars, size_t n_jobs, uint8_t* out) {
+    const size_t np = pk->n_points();
+    if (n_jobs == 0 || n_jobs * np > (1ull << 27)) return BPP_ERR_LENGTH;
+    const uint32_t T = (uint32_t)(n_jobs * np), J = (uint32_t)n_jobs;
+    BPP_TRY(clear_flags(ctx));
+    BPP_CK(ctx->buf[B_SCALARS].ensure((size_t)T * 32));
+    BPP_CK(ctx->buf[B_PIDX].ensure((size_t)T * 4));
+    BPP_CK(ctx->buf[B_OUT0].ensure((size_t)J * PB));
+    BPP_CK(cudaMemcpyAsync(ctx->buf[B_SCALARS].p, scalars, (size_t)T * 32, cudaMemcpyHostToDevice, ctx->stream));
+    BPP_LAUNCH(scalars_check_kernel<M>, ceil_div(T, 256), 256, 0, T, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_FLAGS].as<uint8_t>());
+    BPP_LAUNCH(iota_kernel, ceil_div(T, 256), 256, 0, T, (uint32_t)np, ctx->buf[B_PIDX].as<uint32_t>());
+    BPP_TRY(Msm<C>::run(ctx, T, J, (uint32_t)np, nullptr, pk->wtab, (uint32_t)np, pk->cA, pk->WA, nullptr, 0, pk->wtab_f, nullptr, pk->dtab, pk->cD, pk->WD));
+    BPP_LAUNCH(points_encode_kernel<C>, ceil_div(J, 64), 64, 0, J, ctx->buf[B_RESULTS].as<uint32_t>(), ctx->buf[B_OUT0].as<uint8_t>());
+    BPP_CK(cudaMemcpyAsync(out, ctx->buf[B_OUT0].p, (size_t)J * PB, cudaMemcpyDeviceToHost, ctx->stream));
+    uint8_t bad = 0;
+    BPP_TRY(read_flag(ctx, ctx->buf[B_FLAGS].as<uint8_t>(), &bad));
+    return bad ? BPP_ERR_FORMAT : BPP_OK;
   }
   // re-encode an affine table
   static int export_table(bpp_ctx* ctx, const uint32_t* table, uint32_t n, uint8_t* host_out) {
@@ -208,9 +297,15 @@ struct Api {
     uint32_t* wtab = nullptr;
     cudaError_t e = cudaMalloc(&wtab, bytes);
     if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
-    wtab_build_kernel<C><<<ceil_div(n, 64), 64, 0, ctx->stream>>>(n, c, W, pts->table, wtab);
-    ctx->launches++;
-    e = cudaGetLastError();
+    // in slices of 2^16 points: the scratch for the extended points of a slice stays at W * 8 MB (Ristretto255)
+    const uint32_t SL = 1u << 16;
+    e = W > WTAB_MAX_W ? cudaErrorInvalidValue : ctx->buf[B_EXT].ensure((size_t)(n < SL ? n : SL) * W * C::EXT_WORDS * 4);
+    for (uint32_t i0 = 0; e == cudaSuccess && i0 < n; i0 += SL) {
+      const uint32_t cnt = n - i0 < SL ? n - i0 : SL;
+      wtab_build_kernel<C><<<ceil_div(cnt, 64), 64, 0, ctx->stream>>>(n, i0, cnt, c, W, pts->table, wtab, ctx->buf[B_EXT].as<uint32_t>());
+      ctx->launches++;
+      e = cudaGetLastError();
+    }
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { cudaFree(wtab); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
     pts->wtab = wtab; pts->cA = c; pts->WA = W;
@@ -415,7 +510,7 @@ struct Api {
                  ctx->buf[B_PIDX].as<uint32_t>(), ctx->buf[B_WORK0].as<uint32_t>(), ctx->buf[B_WORK1].as<uint32_t>());
       BPP_CK(cudaMemcpyAsync(ctx->buf[B_SCALARS].p, ctx->buf[B_WORK0].p, (size_t)T2 * 32, cudaMemcpyDeviceToDevice, ctx->stream));
       BPP_CK(cudaMemcpyAsync(ctx->buf[B_PIDX].p, ctx->buf[B_WORK1].p, (size_t)T2 * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-      BPP_TRY(Msm<C>::run(ctx, T2, 1, T2, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), count * per, pk->wtab_f));
+      BPP_TRY(Msm<C>::run(ctx, T2, 1, T2, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), count * per, pk->wtab_f, nullptr, pk->dtab, pk->cD, pk->WD));
       BPP_LAUNCH(rlc_verdict_kernel<C>, ceil_div(count, 256) < 64 ? ceil_div(count, 256) : 64, 256, 0, count, ctx->buf[B_RESULTS].as<uint32_t>(), fmt,
                  d_verdicts, flags);
       uint8_t res[2] = {0, 0};
@@ -425,7 +520,7 @@ struct Api {
       *rlc_pass = res[0];
       return BPP_OK;
     }
-    BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), ppp + vs.nV, pk->wtab_f));
+    BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), ppp + vs.nV, pk->wtab_f, nullptr, pk->dtab, pk->cD, pk->WD));
     BPP_LAUNCH(verdict_kernel<C>, ceil_div(count, 128), 128, 0, count, ppp, vs.nV, ctx->buf[B_RESULTS].as<uint32_t>(),
                ctx->buf[B_DYN_OK].as<uint8_t>(), ctx->buf[B_FLAGS2].as<uint8_t>(), d_verdicts);
     return BPP_OK;
@@ -588,7 +683,7 @@ struct Api {
                ctx->buf[B_PIDX].as<uint32_t>(), d_proofs, proof_len, scalar_off);
     BPP_LAUNCH(prove_jobstart_kernel, ceil_div(count * J + 1, 256), 256, 0, count, L, N, ps.has_A, ps.terms_per_proof,
                ctx->buf[B_JOBSTART].as<uint32_t>());
-    BPP_TRY(Msm<C>::run(ctx, T_all, count * J, 0, ctx->buf[B_JOBSTART].as<uint32_t>(), pk->wtab, pk->n_points(), pk->cA, pk->WA, nullptr, 0, pk->wtab_f));
+    BPP_TRY(Msm<C>::run(ctx, T_all, count * J, 0, ctx->buf[B_JOBSTART].as<uint32_t>(), pk->wtab, pk->n_points(), pk->cA, pk->WA, nullptr, 0, pk->wtab_f, nullptr, pk->dtab, pk->cD, pk->WD));
     // job 0 of a range proof is alpha * h; RangeProof.A = that + sum(bit ? G_i : -H_i) (range/mod.rs:98-106 / :260-277)
     BPP_LAUNCH(encode_into_proofs_kernel<C>, ceil_div(count * J, 64), 64, 0, count, J, ctx->buf[B_RESULTS].as<uint32_t>(),
                ps.has_A ? ctx->buf[B_EXT].as<uint32_t>() : nullptr, d_proofs, proof_len);
@@ -642,7 +737,7 @@ struct Api {
   static int session_emit(bpp_ctx* ctx, bpp_prove_session* s, uint32_t n_terms, uint32_t jobs, uint32_t uniform, const uint32_t* d_job_start,
                           const uint32_t* add_to_job0, uint32_t slot0, uint32_t slot1, uint8_t* host_out) {
     const size_t plen = (2 * (size_t)s->L + 3) * PB + 96;
-    BPP_TRY(Msm<C>::run(ctx, n_terms, s->count * jobs, uniform, d_job_start, s->pk->wtab, s->pk->n_points(), s->pk->cA, s->pk->WA, nullptr, 0, s->pk->wtab_f));
+    BPP_TRY(Msm<C>::run(ctx, n_terms, s->count * jobs, uniform, d_job_start, s->pk->wtab, s->pk->n_points(), s->pk->cA, s->pk->WA, nullptr, 0, s->pk->wtab_f, nullptr, s->pk->dtab, s->pk->cD, s->pk->WD));
     BPP_CK(s->out.ensure((size_t)s->count * jobs * PB));
     BPP_LAUNCH(fs_encode_kernel<C>, ceil_div(s->count * jobs, 64), 64, 0, s->count, jobs, ctx->buf[B_RESULTS].as<uint32_t>(), add_to_job0, slot0, slot1,
                s->proofs.as<uint8_t>(), plen, s->out.as<uint8_t>());

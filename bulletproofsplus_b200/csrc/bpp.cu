@@ -147,6 +147,21 @@ int bpp_pk_new(bpp_ctx* ctx, int curve, size_t len, bpp_pk** out) {
   if (!out) return BPP_ERR_LENGTH;
   BPP_DISPATCH(curve, pk_new(ctx, len, out));
 }
+int bpp_pk_new_hashed(bpp_ctx* ctx, int curve, size_t len, const uint8_t* domain_sep, size_t domain_sep_len, bpp_pk** out) {
+  BPP_ENTER(ctx);
+  if (!out) return BPP_ERR_LENGTH;
+  BPP_DISPATCH(curve, pk_new_hashed(ctx, len, domain_sep, domain_sep_len, out));
+}
+int bpp_pk_precompute(bpp_ctx* ctx, bpp_pk* pk, size_t max_bytes, int* window_bits) {
+  BPP_ENTER(ctx);
+  if (!pk) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, pk_precompute(ctx, pk, max_bytes, window_bits));
+}
+int bpp_pk_msm(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* scalars, size_t n_jobs, uint8_t* out_points) {
+  BPP_ENTER(ctx);
+  if (!pk || !scalars || !out_points) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pk->curve, pk_msm(ctx, pk, scalars, n_jobs, out_points));
+}
 int bpp_pk_export(bpp_ctx* ctx, const bpp_pk* pk, uint8_t* g, uint8_t* h, uint8_t* G, uint8_t* H) {
   BPP_ENTER(ctx);
   if (!pk) return BPP_ERR_NOT_INIT;

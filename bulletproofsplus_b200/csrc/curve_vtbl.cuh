@@ -9,6 +9,9 @@ namespace bpp {
 struct CurveVtbl {
   int curve, point_bytes, raw_bytes, field_bytes;
   int (*pk_new)(bpp_ctx*, size_t, bpp_pk**);
+  int (*pk_new_hashed)(bpp_ctx*, size_t, const uint8_t*, size_t, bpp_pk**);
+  int (*pk_precompute)(bpp_ctx*, bpp_pk*, size_t, int*);
+  int (*pk_msm)(bpp_ctx*, const bpp_pk*, const uint8_t*, size_t, uint8_t*);
   int (*pk_export)(bpp_ctx*, const bpp_pk*, uint8_t*, uint8_t*, uint8_t*, uint8_t*);
   int (*commit_batch)(bpp_ctx*, const bpp_pk*, const uint64_t*, const uint8_t*, size_t, uint8_t*);
   int (*commit_batch_u64)(bpp_ctx*, const bpp_pk*, const uint64_t*, const uint8_t*, size_t, uint8_t*);
@@ -67,6 +70,9 @@ void fill_vtbl_core(CurveVtbl& v) {
   typedef Api<C, M> A;
   v.curve = C::CURVE_ID; v.point_bytes = C::POINT_BYTES; v.raw_bytes = C::EXT_WORDS * 4; v.field_bytes = C::FIELD_BYTES;
   v.pk_new = A::pk_new;
+  v.pk_new_hashed = A::pk_new_hashed;
+  v.pk_precompute = A::pk_precompute;
+  v.pk_msm = A::pk_msm;
   v.pk_export = A::pk_export;
   v.commit_batch = A::commit_batch_i32;
   v.commit_batch_u64 = A::commit_batch_u64;

@@ -231,6 +231,18 @@ struct Ed25519 {
     fe_add(o.ypx, y, x); fe_sub(o.ymx, y, x);
     fe_mul(t, x, y); fe_mul(o.t2d, t, k_d2()); fe_neg(o.nt2d, o.t2d);
   }
+  // batched normalisation (wtab_build_kernel): the element whose inverse to_aff needs (Z is never zero on this curve), the
+  // conversion given that inverse, and the field product
+  BPP_DEV static F aff_den(const Ext& p) { return p.Z; }
+  BPP_DEV static F fmul(const F& a, const F& b) { F r; fe_mul(r, a, b); return r; }
+  BPP_DEV static F fone() { F r; fe_one(r); return r; }
+  BPP_DEV static F finv(const F& a) { F r; fe_invert(r, a); return r; }
+  BPP_DEV static void to_aff_inv(Aff& o, const Ext& p, const F& zi) {
+    F x, y, t;
+    fe_mul(x, p.X, zi); fe_mul(y, p.Y, zi);
+    fe_add(o.ypx, y, x); fe_sub(o.ymx, y, x);
+    fe_mul(t, x, y); fe_mul(o.t2d, t, k_d2()); fe_neg(o.nt2d, o.t2d);
+  }
   BPP_DEV static void aff_to_ext(Ext& p, const Aff& q) {  // via identity + q (7M; only used off the hot path)
     set_identity(p);
     madd(p, q, false);

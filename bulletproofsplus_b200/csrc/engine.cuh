@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include "../../include/bpp.h"
 #include "msm.cuh"
+#include "pk_direct.cuh"
 #include "proto_prove.cuh"
 #include "proto_session.cuh"
 
@@ -89,6 +90,10 @@ struct bpp_pk {
   uint32_t* wtab_f = nullptr; // the same in the FP64 accumulators' slot format (curves with HAS_F64; hybrid accumulation)
   uint32_t* comb = nullptr;   // comb tables of g and h (K5): [(p * comb_w + w) * 128 + d - 1] = d * 2^(8w) * {g, h}
   uint32_t cA = 0, WA = 0, comb_w = 0;
+  // direct fixed-base tables (bpp_pk_precompute, pk_direct.cuh): every signed-digit multiple of every window point; nullptr
+  // until built. With them the fixed-base segment of an MSM needs no buckets (Msm::run_direct).
+  uint32_t* dtab = nullptr;
+  uint32_t cD = 0, WD = 0;
   uint32_t n_points() const { return (uint32_t)(2 + 2 * len); }
 };
 
@@ -214,10 +219,24 @@ struct Msm {
   // Leaves n_jobs extended points in ctx->buf[B_RESULTS].
   static int run(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start,
                  const uint32_t* wtab, uint32_t n_fixed, uint32_t cA, uint32_t WA, const uint32_t* dyn, uint32_t dyn_per_job,
-                 const uint32_t* wtab_f = nullptr, const uint32_t* dyn_f = nullptr) {
+                 const uint32_t* wtab_f = nullptr, const uint32_t* dyn_f = nullptr, const uint32_t* dtab = nullptr, uint32_t cD = 0,
+                 uint32_t WD = 0) {
     if (n_jobs == 0) return BPP_OK;
+    // direct tables exist for the Ed25519 policy only; a job is one block's work there, so a handful of jobs (one proof, one RLC
+    // combination) is better served by the bucket path, which spreads a job over the whole chip
+    const bool direct = dtab && n_fixed && wtab && C::HAS_COOP4 && n_jobs >= 32;
     const bool two = n_fixed && wtab && dyn_per_job && overlaps(n_jobs);
-    if (!two) return run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 3, wtab_f, dyn_f);
+    if (!two) {
+      if (!direct) return run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 3, wtab_f, dyn_f);
+      BPP_CK(ctx->buf[B_RESULTS].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
+      if (!dyn_per_job) return run_direct(ctx, n_terms, n_jobs, uniform, d_job_start, n_fixed, dtab, cD, WD, ctx->buf[B_RESULTS].as<uint32_t>());
+      // few jobs with both kinds of terms: generic segment, then the fixed-base terms from the direct tables, one stream
+      BPP_TRY(run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 2, wtab_f, dyn_f));
+      BPP_CK(ctx->buf[B_FIXEDRES].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
+      BPP_TRY(run_direct(ctx, n_terms, n_jobs, uniform, d_job_start, n_fixed, dtab, cD, WD, ctx->buf[B_FIXEDRES].as<uint32_t>()));
+      BPP_LAUNCH(msm_join_kernel<C>, ceil_div(n_jobs, 128), 128, 0, n_jobs, ctx->buf[B_RESULTS].as<uint32_t>(), ctx->buf[B_FIXEDRES].as<uint32_t>());
+      return BPP_OK;
+    }
     // Two segments, many jobs: the generic segment (sort, buckets, reduction, Horner) goes to the auxiliary stream with its
     // own scratch and overlaps the fixed-base segment on the main stream; one addition per job joins them.
     BPP_TRY(aux_ensure(ctx));
@@ -242,10 +261,43 @@ struct Msm {
     // whatever was queued on the auxiliary stream shares B_SCALARS / B_DYN with the next call: on any failure from here on
     // wait for it before returning
     if (rc != BPP_OK) { cudaStreamSynchronize(ctx->aux_stream); return rc; }
-    rc = run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, 0, 1, wtab_f, dyn_f);
+    rc = direct ? run_direct(ctx, n_terms, n_jobs, uniform, d_job_start, n_fixed, dtab, cD, WD, ctx->buf[B_RESULTS].as<uint32_t>())
+                : run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, 0, 1, wtab_f, dyn_f);
     if (rc != BPP_OK) { cudaStreamSynchronize(ctx->aux_stream); return rc; }
     BPP_CK(cudaStreamWaitEvent(ctx->stream, ctx->aux_join, 0));
     BPP_LAUNCH(msm_join_kernel<C>, ceil_div(n_jobs, 128), 128, 0, n_jobs, ctx->buf[B_RESULTS].as<uint32_t>(), part_b);
+    return BPP_OK;
+  }
+
+  // The fixed-base terms (point index < n_fixed) of every job straight from the key's direct tables: ONE kernel, no sort, no
+  // buckets, no reduction (pk_direct.cuh). Terms with other indices are skipped (the generic segment takes them).
+  static int run_direct(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start, uint32_t n_fixed,
+                        const uint32_t* dtab, uint32_t cD, uint32_t WD, uint32_t* out) {
+    MsmPlan pl;
+    memset(&pl, 0, sizeof(pl));
+    pl.n_terms = n_terms; pl.n_jobs = n_jobs; pl.uniform = uniform; pl.n_fixed = n_fixed; pl.cA = cD; pl.WA = WD;
+    for (int i = 0; i < 8; i++) pl.order[i] = C::order_word(i);
+    // threads per job: about 16 terms per thread for big jobs, never fewer than 4 threads (the tree is cheap)
+    const uint32_t avg = n_terms / n_jobs;
+    uint32_t tpj = 128;
+    while (tpj > 4 && tpj * 8 > avg) tpj >>= 1;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ctx->hot_timing) {
+      BPP_CK(cudaEventCreate(&e0));
+      BPP_CK(cudaEventCreate(&e1));
+      BPP_CK(cudaEventRecord(e0, ctx->stream));
+    }
+    if constexpr (C::HAS_COOP4) {
+      BPP_LAUNCH(direct_accumulate_kernel<C>, ceil_div(n_jobs, 128 / tpj), 128, 0, pl, tpj, ctx->buf[B_SCALARS].as<uint32_t>(),
+                 ctx->buf[B_PIDX].as<uint32_t>(), d_job_start, dtab, out);
+    } else {
+      ctx->err = "direct tables: unsupported curve"; return BPP_ERR_UNSUPPORTED;
+    }
+    if (ctx->hot_timing) {
+      BPP_CK(cudaEventRecord(e1, ctx->stream));
+      ctx->hot_pending.push_back({e0, e1});
+      ctx->hot_launches++;
+    }
     return BPP_OK;
   }
 

@@ -888,19 +888,40 @@ __global__ void __launch_bounds__(128) msm_join_kernel(uint32_t n_jobs, uint32_t
 }
 
 // ---- window tables of a public key: wtab[w * n + i] = 2^(c*w) * P_i, ------------------------------------------
+// One thread per point: W - 1 runs of c doublings, then ALL W - 1 normalisations with ONE field inversion (Montgomery's trick
+// over the windows of the point: prefix products of the denominators forward, one Fermat chain, inverses peeled off backward).
+// The version before did a full inversion per window per point: 22 x 2050 chains of ~265 multiplications for a 1024-generator
+// key and 16 per point for bpp_points_precompute. `ext` is scratch for the W - 1 extended points of each thread
+// (cnt * (W - 1) * C::EXT_WORDS words; large point sets are built slice by slice).
+constexpr uint32_t WTAB_MAX_W = 72;  // cA >= 4 -> W <= 65 for a 256-bit order
 template <class C>
-__global__ void wtab_build_kernel(uint32_t n, uint32_t c, uint32_t W, const uint32_t* __restrict__ aff, uint32_t* __restrict__ wtab) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+__global__ void __launch_bounds__(64) wtab_build_kernel(uint32_t n, uint32_t i0, uint32_t cnt, uint32_t c, uint32_t W, const uint32_t* __restrict__ aff,
+                                                        uint32_t* __restrict__ wtab, uint32_t* __restrict__ ext) {
+  typedef typename C::F F;
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;  // index inside the slice [i0, i0 + cnt) of the n points
+  if (j >= cnt) return;
+  const uint32_t i = i0 + j;
   typename C::Aff q;
   typename C::Ext p;
   load_words<C::AFF_WORDS>(q, aff + (size_t)i * C::AFF_WORDS);
   store_words<C::AFF_WORDS>(wtab + (size_t)i * C::AFF_WORDS, q);
   C::aff_to_ext(p, q);
+  F prefix[WTAB_MAX_W];  // prefix[w] = product of the denominators of windows 1 .. w
+  F run = C::fone();
   for (uint32_t w = 1; w < W; w++) {
     C::dbl_n(p, c);
-    C::to_aff(q, p);
+    store_words<C::EXT_WORDS>(ext + ((size_t)(w - 1) * cnt + j) * C::EXT_WORDS, p);
+    run = C::fmul(run, C::aff_den(p));
+    prefix[w] = run;
+  }
+  if (W < 2) return;
+  F inv = C::finv(run);  // 1 / (den_1 ... den_{W-1})
+  for (uint32_t w = W - 1; w >= 1; w--) {
+    load_words<C::EXT_WORDS>(p, ext + ((size_t)(w - 1) * cnt + j) * C::EXT_WORDS);
+    const F den_inv = w > 1 ? C::fmul(inv, prefix[w - 1]) : inv;
+    C::to_aff_inv(q, p, den_inv);
     store_words<C::AFF_WORDS>(wtab + ((size_t)w * n + i) * C::AFF_WORDS, q);
+    inv = C::fmul(inv, C::aff_den(p));
   }
 }
 

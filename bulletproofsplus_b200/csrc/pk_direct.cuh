@@ -1,0 +1,145 @@
+// Direct fixed-base tables for the public key's generators (bpp_pk_precompute) — the B200-first form of the fixed-base
+// segment of the MSM that replaces MulVec::calculate (reference src/bls12_381/building_block/mulvec.rs:20-33) for every
+// caller on the path: with 180 GB of HBM per GPU the key can hold EVERY signed-digit multiple of every window point,
+//     dtab[dtab_offset(w, i) + j - 1] = j * 2^(c w) * P_i     (affine Niels, 128 B; j = 1 .. 2^(c-1); last window: 1 .. 2^c),
+// so a term costs one table addition per window with no buckets at all: no per-job sort, no size sort, no bucket
+// reduction (together 2.4 ms of the 8.4 ms verify step with the bucket path) and wider windows than buckets allow
+// (c = 14: 19 additions per term instead of 21, 40 GB for a 1024-generator key; the bucket path stops at c = 12 because
+// every job pays 2^(c-1) bucket reductions). The price is memory traffic: every addition reads its own 128-byte line at a
+// random place of the table (10 GB per 2048 proofs, ~2 TB/s), which HBM3e delivers beside the integer pipe's work.
+// Ristretto255 only (the tuned primary curve); the other curves and keys without these tables keep the bucket path.
+#pragma once
+#include "msm.cuh"
+
+namespace bpp {
+
+// Scalars are folded below order/2 < 2^(B), B = SCALAR_BITS - 1, before they are recoded, so W = ceil(B / c) windows hold every
+// bit. Windows 0 .. W-2 take signed digits (|d| <= 2^(c-1), carry into the next window); the LAST window takes its digit
+// unsigned (raw bits + carry <= 2^c), so nothing carries out of it and no (W+1)-th window exists: its regions hold 2^c
+// entries instead of 2^(c-1). Entries per point: (W + 1) * 2^(c-1).
+__host__ __device__ inline uint32_t dtab_windows(uint32_t scalar_bits, uint32_t c) { return (scalar_bits - 1 + c - 1) / c; }
+__host__ __device__ inline size_t dtab_entries(uint32_t n, uint32_t c, uint32_t W) { return ((size_t)(W + 1) * n) << (c - 1); }
+__host__ __device__ inline size_t dtab_offset(uint32_t w, uint32_t i, uint32_t n, uint32_t c, uint32_t W) {
+  return w + 1 < W ? ((size_t)w * n + i) << (c - 1) : (((size_t)(W - 1) * n) << (c - 1)) + ((size_t)i << c);
+}
+
+// ---- table build -------------------------------------------------------------------------------------------------------
+// step 1 (wtab_build_kernel, msm.cuh): window bases 2^(c w) P_i -> base[w * n + i]
+// step 2: thread per (w, i): running sums j * base as EXTENDED points written into the table slots (an extended point and an
+//         affine table point are both 128 B on this curve)
+template <class C>
+__global__ void __launch_bounds__(64) dtab_fill_kernel(uint32_t n, uint32_t c, uint32_t W, const uint32_t* __restrict__ base, uint32_t* __restrict__ dtab) {
+  static_assert(C::EXT_WORDS == C::AFF_WORDS, "the fill pass stores extended points in the table slots");
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;  // region = w * n + i
+  if (r >= n * W) return;
+  const uint32_t w = r / n, i = r - w * n;
+  const uint32_t half = w + 1 < W ? 1u << (c - 1) : 1u << c;
+  const uint32_t* b = base + (size_t)r * C::AFF_WORDS;
+  uint32_t* out = dtab + dtab_offset(w, i, n, c, W) * C::AFF_WORDS;
+  typename C::Ext acc;
+  C::init_from_ptr(acc, b, 0);
+  for (uint32_t j = 0; j < half; j++) {
+    store_words<C::EXT_WORDS>(out + (size_t)j * C::EXT_WORDS, acc);
+    C::madd_ptr(acc, b, 0);
+  }
+}
+// step 3: thread per run of DTAB_NORM entries: extended -> affine in place with one inversion per run (Montgomery's trick)
+constexpr uint32_t DTAB_NORM = 32;
+template <class C>
+__global__ void __launch_bounds__(128) dtab_normalise_kernel(uint64_t n_entries, uint32_t* __restrict__ dtab) {
+  typedef typename C::F F;
+  const uint64_t run = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t e0 = run * DTAB_NORM;
+  if (e0 >= n_entries) return;
+  const uint32_t cnt = n_entries - e0 < DTAB_NORM ? (uint32_t)(n_entries - e0) : DTAB_NORM;
+  uint32_t* p0 = dtab + e0 * C::EXT_WORDS;
+  F prefix[DTAB_NORM];
+  F acc = C::fone();
+  typename C::Ext p;
+  for (uint32_t k = 0; k < cnt; k++) {
+    load_words<C::EXT_WORDS>(p, p0 + (size_t)k * C::EXT_WORDS);
+    acc = C::fmul(acc, C::aff_den(p));
+    prefix[k] = acc;
+  }
+  F inv = C::finv(acc);
+  typename C::Aff q;
+  for (int k = (int)cnt - 1; k >= 0; k--) {
+    load_words<C::EXT_WORDS>(p, p0 + (size_t)k * C::EXT_WORDS);
+    const F den_inv = k > 0 ? C::fmul(inv, prefix[k - 1]) : inv;
+    C::to_aff_inv(q, p, den_inv);
+    inv = C::fmul(inv, C::aff_den(p));
+    store_words<C::AFF_WORDS>(p0 + (size_t)k * C::AFF_WORDS, q);
+  }
+}
+
+// ---- HOT: accumulation straight from the tables ------------------------------------------------------------------------
+// TPJ threads per job (a power of two <= 128; 128 / TPJ jobs per block). Thread l of a job takes terms l, l + TPJ, ... of the
+// job, recodes each scalar (half-order folding + signed c-bit digits, as in msm_digits_kernel) and adds one table point per
+// non-zero digit to its own accumulator; the next digit's line is prefetched into L2 while the current addition runs. The
+// TPJ partial sums are added in a shared-memory tree. Terms whose point is not in the key (index >= n_fixed: per-call
+// points) are left to the generic segment. results[job] = extended point.
+template <class C>
+__global__ void __launch_bounds__(128)
+direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
+                         const uint32_t* __restrict__ job_start, const uint32_t* __restrict__ dtab, uint32_t* __restrict__ results) {
+  __shared__ uint32_t sh[128 * C::EXT_WORDS];
+  const uint32_t tid = threadIdx.x, lane = tid & (tpj - 1);
+  const uint32_t job = blockIdx.x * (128 / tpj) + tid / tpj;
+  const bool live = job < pl.n_jobs;
+  const uint32_t c = pl.cA, W = pl.WA, half = 1u << (c - 1), n = pl.n_fixed;
+  typename C::Ext acc;
+  bool have = false;
+  if (live) {
+    const uint32_t t0 = pl.uniform ? job * pl.uniform : job_start[job];
+    const uint32_t t1 = pl.uniform ? t0 + pl.uniform : job_start[job + 1];
+    for (uint32_t t = t0 + lane; t < t1; t += tpj) {
+      const uint32_t p = pidx[t];
+      if (p >= n) continue;
+      uint32_t s[8];
+      const uint4* sp = reinterpret_cast<const uint4*>(scalars + 8ull * t);
+      const uint4 a = __ldg(sp), b = __ldg(sp + 1);
+      s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
+      const uint32_t flip = msm_fold_half(pl, s);
+      // software pipeline over the windows: (cur) is added while (nxt) is recoded and its line prefetched
+      uint32_t carry = 0;
+      const uint32_t* cur = nullptr;
+      uint32_t cur_neg = 0;
+      for (uint32_t w = 0; w <= W; w++) {
+        const uint32_t* nxt = nullptr;
+        uint32_t nxt_neg = 0;
+        if (w < W) {
+          const uint32_t raw = msm_bits(s, w * c, c) + carry;
+          const uint32_t neg = (w + 1 < W) && raw > half;  // the last window is taken unsigned: no carry out of it
+          const uint32_t mag = neg ? (1u << c) - raw : raw;
+          carry = neg;
+          if (mag) {
+            nxt = dtab + (dtab_offset(w, p, n, c, W) + (mag - 1)) * C::AFF_WORDS;
+            nxt_neg = neg ^ flip;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
+          }
+        }
+        if (cur) {
+          if (have) C::madd_ptr(acc, cur, cur_neg);
+          else { C::init_from_ptr(acc, cur, cur_neg); have = true; }
+        }
+        cur = nxt;
+        cur_neg = nxt_neg;
+      }
+    }
+  }
+  if (!have) C::set_identity(acc);
+  typename C::Ext* mine = reinterpret_cast<typename C::Ext*>(sh + tid * C::EXT_WORDS);
+  *mine = acc;
+  __syncthreads();
+  for (uint32_t sft = tpj >> 1; sft > 0; sft >>= 1) {
+    if (lane < sft) {
+      typename C::Ext o = *reinterpret_cast<typename C::Ext*>(sh + (tid + sft) * C::EXT_WORDS);
+      C::add(acc, o);
+      *mine = acc;
+    }
+    __syncthreads();
+  }
+  if (live && lane == 0) store_words<C::EXT_WORDS>(results + (size_t)job * C::EXT_WORDS, acc);
+}
+
+}  // namespace bpp

@@ -132,6 +132,20 @@ struct Weierstrass {
     p.ZZ = F::mul(F::mul(p.ZZ, q.ZZ), PP);
     p.ZZZ = F::mul(F::mul(p.ZZZ, q.ZZZ), PPP);
   }
+  // batched normalisation (wtab_build_kernel): the element whose inverse to_aff needs (1 for the point at infinity), the
+  // conversion given that inverse, and the field product
+  BPP_DEV static F aff_den(const Ext& p) { return p.ZZ.is_zero() ? F::one() : p.ZZZ; }
+  BPP_DEV static F fmul(const F& a, const F& b) { return F::mul(a, b); }
+  BPP_DEV static F fone() { return F::one(); }
+  BPP_DEV static F finv(const F& a) { return F::inv(a); }
+  BPP_DEV static void to_aff_inv(Aff& o, const Ext& p, const F& zzz_inv) {
+    set_identity(o);
+    if (p.ZZ.is_zero()) return;
+    o.y = F::mul(p.Y, zzz_inv);
+    F z_inv = F::mul(p.ZZ, zzz_inv);
+    o.x = F::mul(p.X, F::sqr(z_inv));
+    o.ny = F::neg(o.y);
+  }
   // Ext -> Aff (one inversion)
   __device__ static void to_aff(Aff& o, const Ext& p) {
     set_identity(o);

@@ -137,6 +137,10 @@ inline std::vector<uint8_t> pack(const std::vector<Point>& v, size_t pb) {
 class PublicKey {
  public:
   static PublicKey new_(size_t len, Curve curve = Curve::Ristretto255, bpp_ctx* ctx = nullptr) { return PublicKey(len, curve, ctx ? ctx : Arith::init()); }
+  // hash-derived generators (bpp_pk_new_hashed): no known discrete-log relations — the constructor to use outside parity tests
+  static PublicKey new_hashed(size_t len, const std::string& domain_sep, bpp_ctx* ctx = nullptr) {
+    return PublicKey(len, Curve::Ristretto255, ctx ? ctx : Arith::init(), &domain_sep);
+  }
   const Point& g() const { export_(); return g_; }
   const Point& h() const { export_(); return h_; }
   const std::vector<Point>& G_vec() const { export_(); return G_; }
@@ -162,9 +166,14 @@ class PublicKey {
   const bpp_pk* handle() const { return pk_.get(); }
 
  private:
-  PublicKey(size_t len, Curve curve, bpp_ctx* ctx) : ctx_(ctx), curve_(curve), len_(len), pb_((size_t)bpp_point_bytes((int)curve)) {
+  PublicKey(size_t len, Curve curve, bpp_ctx* ctx, const std::string* domain_sep = nullptr)
+      : ctx_(ctx), curve_(curve), len_(len), pb_((size_t)bpp_point_bytes((int)curve)) {
     bpp_pk* pk = nullptr;
-    detail::check(ctx, bpp_pk_new(ctx, (int)curve, len, &pk), "PublicKey::new");
+    if (domain_sep)
+      detail::check(ctx, bpp_pk_new_hashed(ctx, (int)curve, len, reinterpret_cast<const uint8_t*>(domain_sep->data()), domain_sep->size(), &pk),
+                    "PublicKey::new_hashed");
+    else
+      detail::check(ctx, bpp_pk_new(ctx, (int)curve, len, &pk), "PublicKey::new");
     pk_ = std::shared_ptr<bpp_pk>(pk, bpp_pk_free);
   }
   void export_() const {

@@ -148,6 +148,24 @@ int main(int argc, char** argv) {
     report("tampered transcript proof == Err(VerificationError)",
            verify_with_transcript(t2, pk, n, prover.commitment_vec, merlin::Transcript("RangeProof Test")) == Result::Err(ProofError::VerificationError));
   }
+  // hash-derived generators (bpp_pk_new_hashed; Ristretto255): the README flow over a key nobody knows a relation in
+  if (curve == Curve::Ristretto255) {
+    const size_t n = 32, m = 2;
+    PublicKey hk = PublicKey::new_hashed(n * m, "host_mirror_test");
+    report("hashed key: G_4 != H_2, g + g != h", !(hk.G_vec()[4] == hk.H_vec()[2]) && !(hk.g() == hk.h()));
+    RangeProver prover = RangeProver::new_();
+    prover.commit_u64(hk, (1ull << 31) + 5, fe(3));
+    prover.commit_u64(hk, 7, fe(9));
+    RangeProof proof = prove_with_transcript(hk, n, prover, merlin::Transcript("hashed"));
+    report("hashed key: transcript proof of v >= 2^31 out of range for n = 32 == Err", !(verify_with_transcript(proof, hk, n, prover.commitment_vec, merlin::Transcript("hashed")) == Result::Ok()));
+    PublicKey hk64 = PublicKey::new_hashed(64 * m, "host_mirror_test");
+    RangeProver p64 = RangeProver::new_();
+    p64.commit_u64(hk64, (1ull << 31) + 5, fe(3));
+    p64.commit_u64(hk64, 7, fe(9));
+    RangeProof proof64 = prove_with_transcript(hk64, 64, p64, merlin::Transcript("hashed"));
+    report("hashed key: n = 64 transcript proof of v >= 2^31 == Ok(())", verify_with_transcript(proof64, hk64, 64, p64.commitment_vec, merlin::Transcript("hashed")) == Result::Ok());
+    report("hashed key: fixed-constant prove/verify == Ok(())", RangeProof::prove(hk64, 64, p64).verify(hk64, 64, p64.commitment_vec) == Result::Ok());
+  }
   printf("%s\n", failures ? "SOME FAILED" : "ALL PASSED");
   return failures ? 1 : 0;
 }

@@ -27,6 +27,8 @@ def timeit(f, label):
 
 if case in ("verify", "prove", "verify_fs", "prove_fs", "verify_rlc"):
     pk = api.PublicKey.new(n * m, 0, ctx)
+    if float(os.environ.get('BPP_TABLE_GB', '0')) > 0:  # direct fixed-base tables (bpp_pk_precompute)
+        print('direct tables: c =', pk.precompute(int(float(os.environ['BPP_TABLE_GB']) * 2**30)), flush=True)
     vs = [rng.randrange(2**31) for _ in range(size * m)]
     gs = [rng.randrange(ELL) for _ in range(size * m)]
     if case == "prove":
