@@ -339,7 +339,7 @@ def main():
     ap.add_argument("--prove-batch", type=int, default=256)
     ap.add_argument("--ref-proofs", type=int, default=2, help="reference arm: verifies per step (one thread)")
     ap.add_argument("--msm-max-log", type=int, default=22)
-    ap.add_argument("--table-gb", type=float, default=48.0, help="HBM budget of the key's direct fixed-base tables (bpp_pk_precompute); "
+    ap.add_argument("--table-gb", type=float, default=80.0, help="HBM budget of the key's direct fixed-base tables (bpp_pk_precompute); "
                                                                    "0 = none: the bucket path")
     ap.add_argument("--no-extras", action="store_true", help="skip proves/s, configs 2-4, the MSM sweep and the CPU baseline")
     args = ap.parse_args()

@@ -277,10 +277,18 @@ struct Msm {
     memset(&pl, 0, sizeof(pl));
     pl.n_terms = n_terms; pl.n_jobs = n_jobs; pl.uniform = uniform; pl.n_fixed = n_fixed; pl.cA = cD; pl.WA = WD;
     for (int i = 0; i < 8; i++) pl.order[i] = C::order_word(i);
-    // threads per job: about 16 terms per thread for big jobs, never fewer than 4 threads (the tree is cheap)
+    // threads per slice: at least ~8 terms per thread for small jobs, never fewer than 4 threads (the tree is cheap); slices per
+    // job: enough blocks for ~8 waves of the 592 resident ones, while every thread keeps at least two whole terms
     const uint32_t avg = n_terms / n_jobs;
     uint32_t tpj = 128;
     while (tpj > 4 && tpj * 8 > avg) tpj >>= 1;
+    uint32_t S = 1;
+    while (S < 8 && (uint64_t)ceil_div(n_jobs, 128 / tpj) * S < 8 * 592 && (uint64_t)tpj * S * 2 * 2 <= avg) S <<= 1;
+    uint32_t* partial = out;
+    if (S > 1) {
+      BPP_CK(ctx->buf[B_CHUNK_S2].ensure((size_t)n_jobs * S * C::EXT_WORDS * 4));
+      partial = ctx->buf[B_CHUNK_S2].as<uint32_t>();
+    }
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->hot_timing) {
       BPP_CK(cudaEventCreate(&e0));
@@ -288,8 +296,9 @@ struct Msm {
       BPP_CK(cudaEventRecord(e0, ctx->stream));
     }
     if constexpr (C::HAS_COOP4) {
-      BPP_LAUNCH(direct_accumulate_kernel<C>, ceil_div(n_jobs, 128 / tpj), 128, 0, pl, tpj, ctx->buf[B_SCALARS].as<uint32_t>(),
-                 ctx->buf[B_PIDX].as<uint32_t>(), d_job_start, dtab, out);
+      BPP_LAUNCH(direct_accumulate_kernel<C>, ceil_div((uint64_t)n_jobs * S, 128 / tpj), 128, 0, pl, tpj, S, ctx->buf[B_SCALARS].as<uint32_t>(),
+                 ctx->buf[B_PIDX].as<uint32_t>(), d_job_start, dtab, partial);
+      if (S > 1) BPP_LAUNCH(direct_join_kernel<C>, ceil_div(n_jobs, 128), 128, 0, n_jobs, S, partial, out);
     } else {
       ctx->err = "direct tables: unsupported curve"; return BPP_ERR_UNSUPPORTED;
     }

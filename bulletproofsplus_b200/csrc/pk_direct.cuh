@@ -73,18 +73,34 @@ __global__ void __launch_bounds__(128) dtab_normalise_kernel(uint64_t n_entries,
 }
 
 // ---- HOT: accumulation straight from the tables ------------------------------------------------------------------------
-// TPJ threads per job (a power of two <= 128; 128 / TPJ jobs per block). Thread l of a job takes terms l, l + TPJ, ... of the
-// job, recodes each scalar (half-order folding + signed c-bit digits, as in msm_digits_kernel) and adds one table point per
-// non-zero digit to its own accumulator; the next digit's line is prefetched into L2 while the current addition runs. The
-// TPJ partial sums are added in a shared-memory tree. Terms whose point is not in the key (index >= n_fixed: per-call
-// points) are left to the generic segment. results[job] = extended point.
+// A job is cut into S slices of TPJ threads (TPJ a power of two <= 128, 128 / TPJ slices per block): S * TPJ "lanes" per job.
+//   phase 1  whole rounds: lane l takes terms l, l + S*TPJ, ... and adds one table point per non-zero digit of each (half-order
+//            folding + signed c-bit digits as in msm_digits_kernel; the next digit's line is prefetched into L2 meanwhile)
+//   phase 2  the K mod (S*TPJ) leftover terms are dealt out as (term, window) PAIRS, so that no lane gets a whole extra term
+//            (1026 = 8 * 128 + 2 terms per prover job would otherwise make two lanes work 9/8 as long as the others)
+// then the TPJ partial sums of a slice are added in a shared-memory tree -> partial[job * S + slice] (extended points; S == 1:
+// the job's result). Slices exist for wave quantisation: 2048 one-block jobs are 3.46 waves of the 592 resident blocks of a
+// B200 (86 % of four), 8192 quarter-job blocks are 13.8. Terms whose point is not in the key (index >= n_fixed: per-call
+// points) are left to the generic segment.
+template <class C>
+__device__ __forceinline__ void direct_add(typename C::Ext& acc, bool& have, const uint32_t* ptr, uint32_t neg) {
+  if (have) C::madd_ptr(acc, ptr, neg);
+  else { C::init_from_ptr(acc, ptr, neg); have = true; }
+}
+__device__ __forceinline__ void direct_load_scalar(const uint32_t* __restrict__ scalars, uint32_t t, uint32_t* s) {
+  const uint4* sp = reinterpret_cast<const uint4*>(scalars + 8ull * t);
+  const uint4 a = __ldg(sp), b = __ldg(sp + 1);
+  s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
+}
+
 template <class C>
 __global__ void __launch_bounds__(128)
-direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
-                         const uint32_t* __restrict__ job_start, const uint32_t* __restrict__ dtab, uint32_t* __restrict__ results) {
+direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, uint32_t S, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
+                         const uint32_t* __restrict__ job_start, const uint32_t* __restrict__ dtab, uint32_t* __restrict__ partial) {
   __shared__ uint32_t sh[128 * C::EXT_WORDS];
   const uint32_t tid = threadIdx.x, lane = tid & (tpj - 1);
-  const uint32_t job = blockIdx.x * (128 / tpj) + tid / tpj;
+  const uint32_t unit = blockIdx.x * (128 / tpj) + tid / tpj;  // (job, slice)
+  const uint32_t job = unit / S, slice = unit - job * S;
   const bool live = job < pl.n_jobs;
   const uint32_t c = pl.cA, W = pl.WA, half = 1u << (c - 1), n = pl.n_fixed;
   typename C::Ext acc;
@@ -92,13 +108,13 @@ direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, const uint32_t* __restrict__ 
   if (live) {
     const uint32_t t0 = pl.uniform ? job * pl.uniform : job_start[job];
     const uint32_t t1 = pl.uniform ? t0 + pl.uniform : job_start[job + 1];
-    for (uint32_t t = t0 + lane; t < t1; t += tpj) {
+    const uint32_t GL = tpj * S, gl = slice * tpj + lane, K = t1 - t0, full = K / GL;
+    for (uint32_t r = 0; r < full; r++) {  // phase 1
+      const uint32_t t = t0 + r * GL + gl;
       const uint32_t p = pidx[t];
       if (p >= n) continue;
       uint32_t s[8];
-      const uint4* sp = reinterpret_cast<const uint4*>(scalars + 8ull * t);
-      const uint4 a = __ldg(sp), b = __ldg(sp + 1);
-      s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
+      direct_load_scalar(scalars, t, s);
       const uint32_t flip = msm_fold_half(pl, s);
       // software pipeline over the windows: (cur) is added while (nxt) is recoded and its line prefetched
       uint32_t carry = 0;
@@ -118,13 +134,25 @@ direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, const uint32_t* __restrict__ 
             asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
           }
         }
-        if (cur) {
-          if (have) C::madd_ptr(acc, cur, cur_neg);
-          else { C::init_from_ptr(acc, cur, cur_neg); have = true; }
-        }
+        if (cur) direct_add<C>(acc, have, cur, cur_neg);
         cur = nxt;
         cur_neg = nxt_neg;
       }
+    }
+    const uint32_t tb = t0 + full * GL, R = K - full * GL;  // phase 2
+    for (uint32_t idx = gl; idx < R * W; idx += GL) {
+      const uint32_t t = tb + idx / W, w = idx % W;
+      const uint32_t p = pidx[t];
+      if (p >= n) continue;
+      uint32_t s[8];
+      direct_load_scalar(scalars, t, s);
+      const uint32_t flip = msm_fold_half(pl, s);
+      uint32_t carry = 0;
+      for (uint32_t v = 0; v < w; v++) carry = (msm_bits(s, v * c, c) + carry) > half;  // windows below w are all signed
+      const uint32_t raw = msm_bits(s, w * c, c) + carry;
+      const uint32_t neg = (w + 1 < W) && raw > half;
+      const uint32_t mag = neg ? (1u << c) - raw : raw;
+      if (mag) direct_add<C>(acc, have, dtab + (dtab_offset(w, p, n, c, W) + (mag - 1)) * C::AFF_WORDS, neg ^ flip);
     }
   }
   if (!have) C::set_identity(acc);
@@ -139,7 +167,21 @@ direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, const uint32_t* __restrict__ 
     }
     __syncthreads();
   }
-  if (live && lane == 0) store_words<C::EXT_WORDS>(results + (size_t)job * C::EXT_WORDS, acc);
+  if (live && lane == 0) store_words<C::EXT_WORDS>(partial + (size_t)unit * C::EXT_WORDS, acc);
+}
+
+// thread per job: results[job] = sum of its S slice sums
+template <class C>
+__global__ void __launch_bounds__(128) direct_join_kernel(uint32_t n_jobs, uint32_t S, const uint32_t* __restrict__ partial, uint32_t* __restrict__ results) {
+  const uint32_t job = blockIdx.x * blockDim.x + threadIdx.x;
+  if (job >= n_jobs) return;
+  typename C::Ext a, b;
+  load_words<C::EXT_WORDS>(a, partial + (size_t)job * S * C::EXT_WORDS);
+  for (uint32_t k = 1; k < S; k++) {
+    load_words<C::EXT_WORDS>(b, partial + ((size_t)job * S + k) * C::EXT_WORDS);
+    C::add(a, b);
+  }
+  store_words<C::EXT_WORDS>(results + (size_t)job * C::EXT_WORDS, a);
 }
 
 }  // namespace bpp

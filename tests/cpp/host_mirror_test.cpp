@@ -154,10 +154,10 @@ int main(int argc, char** argv) {
     PublicKey hk = PublicKey::new_hashed(n * m, "host_mirror_test");
     report("hashed key: G_4 != H_2, g + g != h", !(hk.G_vec()[4] == hk.H_vec()[2]) && !(hk.g() == hk.h()));
     RangeProver prover = RangeProver::new_();
-    prover.commit_u64(hk, (1ull << 31) + 5, fe(3));
+    prover.commit_u64(hk, (1ull << 33) + 5, fe(3));
     prover.commit_u64(hk, 7, fe(9));
     RangeProof proof = prove_with_transcript(hk, n, prover, merlin::Transcript("hashed"));
-    report("hashed key: transcript proof of v >= 2^31 out of range for n = 32 == Err", !(verify_with_transcript(proof, hk, n, prover.commitment_vec, merlin::Transcript("hashed")) == Result::Ok()));
+    report("hashed key: transcript proof of v = 2^33 + 5, out of range for n = 32 == Err", !(verify_with_transcript(proof, hk, n, prover.commitment_vec, merlin::Transcript("hashed")) == Result::Ok()));
     PublicKey hk64 = PublicKey::new_hashed(64 * m, "host_mirror_test");
     RangeProver p64 = RangeProver::new_();
     p64.commit_u64(hk64, (1ull << 31) + 5, fe(3));
