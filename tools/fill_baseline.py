@@ -1,0 +1,87 @@
+"""Fills BASELINE.md §4 from bench lines: python tools/fill_baseline.py profiles/r02X_bench_n1.json [n2.json n4.json n8.json].
+The table between the markers <!-- results:begin --> / <!-- results:end --> is regenerated; everything else is left alone."""
+import json
+import re
+import sys
+
+lines = {}
+for p in sys.argv[1:]:
+    d = json.loads(open(p).read())
+    lines[d["n_gpus"]] = (d, p)
+d1, p1 = lines[1]
+
+
+def k(x, nd=0):
+    return "—" if x is None else (f"{x:,.{nd}f}".replace(",", " "))
+
+
+def at(n, f):
+    return k(f(lines[n][0])) if n in lines else "—"
+
+
+def sweep(key):
+    s = d1.get(key)
+    if not s:
+        return "—", "—"
+    pick = {r["log2_n"]: r for r in s}
+    txt = " / ".join(f"2^{lg}: {pick[lg]['points_per_sec'] / 1e6:.1f} M" for lg in (10, 14, 18, 20, 22) if lg in pick)
+    fr = " / ".join(f"{pick[lg]['int_roofline_frac']:.3f}" for lg in (10, 14, 18, 20, 22) if lg in pick)
+    return txt, fr
+
+
+cpu = d1.get("cpu_baseline") or {}
+b1 = cpu.get("value")
+b2 = (cpu.get("b2_fair_cpu") or {}).get("value")
+b2c = (cpu.get("b2_fair_cpu") or {}).get("cores")
+pr = d1.get("proves") or {}
+prc = pr.get("cpu_baseline") or {}
+fs = d1.get("verify_per_proof_challenges") or {}
+c4 = lambda d: (d.get("config4_batch8192_n64_m1") or {}).get("value")
+c2 = d1.get("config2_wip_4096") or {}
+c3 = d1.get("config3_n64_m64") or {}
+rows = []
+rows.append(("verify n=64 m=16, reference's constant challenges (proofs/s; headline `value`, device-resident)", at(1, lambda d: d["value"]), at(2, lambda d: d["value"]),
+             at(4, lambda d: d["value"]), at(8, lambda d: d["value"]),
+             f"{d1['roofline']['frac']:.2f} kernel (algorithmic) / {d1['roofline']['executed']['frac']:.2f} executed / {d1['roofline']['whole_step']['frac']:.2f} whole step",
+             k(b1, 2), f"{k(b2)} ({b2c})"))
+rows.append(("same, end to end with host buffers (`e2e`)", at(1, lambda d: d["e2e"]["value"]), at(2, lambda d: d["e2e"]["value"]), at(4, lambda d: d["e2e"]["value"]),
+             at(8, lambda d: d["e2e"]["value"]), "", "", ""))
+rows.append(("verify n=64 m=16, per-proof Fiat-Shamir challenges (device / e2e)", f"{k(fs.get('value'))} / {k((fs.get('e2e') or {}).get('value'))}",
+             at(2, lambda d: d["verify_per_proof_challenges"]["value"]), at(4, lambda d: d["verify_per_proof_challenges"]["value"]),
+             at(8, lambda d: d["verify_per_proof_challenges"]["value"]), "", "", ""))
+rows.append(("prove n=64 m=16 (proofs/s, device / e2e)", f"{k(pr.get('value'))} / {k((pr.get('e2e') or {}).get('value'))}", at(2, lambda d: d["proves"]["value"]),
+             at(4, lambda d: d["proves"]["value"]), at(8, lambda d: d["proves"]["value"]), f"{(pr.get('roofline') or {}).get('frac', 0):.2f} whole batch (algorithmic)",
+             k(prc.get("value"), 2), f"B1 all cores: {k(prc.get('all_cores'), 1)}"))
+rows.append(("WIP 2^12 prove / verify (ms, one argument, host ABI)", f"{c2.get('prove_ms', 0):.2f} / {c2.get('verify_ms', 0):.2f}", "—", "—", "—", "", "", ""))
+rows.append(("n=64 m=64 (8 285-term MSM): single prove / verify ms; 128-proof batch verifies/s",
+             f"{c3.get('single_proof_prove_ms', 0):.2f} / {c3.get('single_proof_verify_ms', 0):.2f}; {k(c3.get('batch_verifies_per_sec'))}", "—", "—", "—", "", "", ""))
+rows.append(("batch verify 8 192 × (n=64, m=1), fixed batch sharded (proofs/s, strong scaling)", at(1, c4), at(2, c4), at(4, c4), at(8, c4), "", "", ""))
+rows.append(("RLC batch verify n=64 m=16 (proofs/s)", at(1, lambda d: d["verifies_per_sec_rlc_batch"]["value"]), at(2, lambda d: d["verifies_per_sec_rlc_batch"]["value"]),
+             at(4, lambda d: d["verifies_per_sec_rlc_batch"]["value"]), at(8, lambda d: d["verifies_per_sec_rlc_batch"]["value"]), "", "", ""))
+sp = lambda d: (d.get("msm_point_range_split") or {}).get("points_per_sec")
+for key, name in (("msm_points_per_sec", "Ristretto255"), ("msm_points_per_sec_secp256k1", "secp256k1"), ("msm_points_per_sec_bls12_381_g1", "BLS12-381 G1")):
+    txt, fr = sweep(key)
+    extra = [("2^22 split: " + k(sp(lines[n][0]) / 1e6 if sp(lines[n][0]) else None, 0) + " M") if (n in lines and key == "msm_points_per_sec") else "—" for n in (2, 4, 8)]
+    b2m = (cpu.get("msm_b2_2p16") or {}).get("value")
+    rows.append((f"MSM {name} (points/s at 2^10 / 2^14 / 2^18 / 2^20 / 2^22)", txt, *extra, fr, "", f"2^16: {k(b2m / 1e6 if b2m else None, 2)} M ({b2c})" if key == "msm_points_per_sec" else ""))
+
+hdr = "| config | 1 GPU | 2 GPU | 4 GPU | 8 GPU | roofline fraction of the integer-multiply peak (1 GPU) | B1 CPU (1 thread) | B2 CPU (all cores, count) |\n|---|---|---|---|---|---|---|---|\n"
+body = "".join("| " + " | ".join(r) + " |\n" for r in rows)
+src = ", ".join(f"N={n}: `{p}`" for n, (_, p) in sorted(lines.items()))
+tab = d1["config"].get("fixed_base_tables")
+note = (f"\nSources: {src}. B200, SM clock {d1['clocks']['sm_mhz']:.0f} MHz, no throttle reasons. Integer peak (32-bit IMAD issue rate, measured live by "
+        f"`bpp_int_peak_probe`): {d1['roofline']['peak']:.2f} T/s; ~0.43 of it is the measured ceiling of a multi-limb multiply (DESIGN §3.2). "
+        + (f"The key carries {tab['bytes'] / 2**30:.1f} GB of direct fixed-base tables (c = {tab['window_bits']}, built once in {tab['build_s']:.2f} s, outside every timed region). " if tab else "")
+        + "B1 = the literal restatement of the reference's algorithm on ONE host thread (the reference is single-threaded and cannot be built here: no Rust "
+          "toolchain, `mcl_rust` un-vendored); B2 = the same verifier with a bucket MSM (5×51-bit limbs, all host threads) — not the reference's algorithm, shown so that "
+          "the GPU/CPU ratio is not read against a naive loop only. Multi-GPU columns: proofs are sharded per rank with no data-path collective (weak scaling, "
+          "value = total proofs ÷ max-over-ranks time) except the fixed 8 192-proof batch (strong) and the 2^22-point MSM split by point range (strong, NCCL all-gather of N×128 B).\n")
+md = open("BASELINE.md").read()
+block = "<!-- results:begin -->\n" + hdr + body + note + "<!-- results:end -->"
+if "<!-- results:begin -->" in md:
+    md = re.sub(r"<!-- results:begin -->.*?<!-- results:end -->", lambda m: block, md, flags=re.S)
+else:
+    i = md.index("## 4. Results")
+    md = md[:i] + "## 4. Results\n\n" + block + "\n"
+open("BASELINE.md", "w").write(md)
+print(block)
