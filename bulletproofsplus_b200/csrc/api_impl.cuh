@@ -478,15 +478,20 @@ struct Api {
       T.pre = ctx->buf[B_TAB6].as<uint32_t>(); T.stride_pre = (L + 2) * 8;
       BPP_LAUNCH(verify_inverses_kernel<M>, ceil_div(count, 32), 32, 0, count, L, ctx->buf[B_TAB5].as<uint32_t>(), T.stride_params,
                  ctx->buf[B_TAB6].as<uint32_t>(), T.stride_pre);
-      BPP_LAUNCH(verify_tables_kernel<M>, count, 128, 0, vs, ctx->buf[B_TAB5].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
+      BPP_LAUNCH((verify_tables_kernel<M, 128>), count, 128, 0, vs, ctx->buf[B_TAB5].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
     } else {
       const size_t cap0 = ctx->buf[B_TAB0].cap + ctx->buf[B_TAB1].cap + ctx->buf[B_TAB2].cap + ctx->buf[B_TAB3].cap;
       if (!tables_cached(ctx, 1, pk, N, n, m, mode) || cap0 != ctx->tab_caps)
-        BPP_LAUNCH(verify_tables_kernel<M>, 1, VT_THREADS, 0, vs, ctx->buf[B_PARAMS].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
+        BPP_LAUNCH((verify_tables_kernel<M, VT_THREADS>), 1, VT_THREADS, 0, vs, ctx->buf[B_PARAMS].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
       ctx->tab_caps = cap0;
     }
     dim3 grid(ceil_div(K, 256), count);
-    BPP_LAUNCH(verify_scalars_kernel<M>, grid, 256, 0, vs, T, xs, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>());
+    // with the key's direct tables the generator terms' exponents are computed inside the accumulation kernel (DirectVerifySrc)
+    static const bool no_fuse = getenv("BPP_NO_FUSE") != nullptr;  // A/B switch
+    const bool fuse = !no_fuse && !d_weights && C::CURVE_ID == 0 && Msm<C>::uses_direct(pk->dtab, count);
+    BPP_LAUNCH(verify_scalars_kernel<M>, grid, 256, 0, vs, T, xs, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>(), fuse ? 1u : 0u);
+    DirectVerifySrc vsrc;
+    vsrc.enabled = 1; vsrc.K0 = 5 + 2 * L; vsrc.N = N; vsrc.stride_T = T.stride_T; vsrc.Tmul = T.Tmul; vsrc.Tadd = T.Tadd; vsrc.xs = xs;
     if (d_weights) {
       // random linear combination: one MSM of 2 + 2N + count * (ppp + nV) terms for the whole batch
       const uint32_t per = ppp + vs.nV, T2 = 2 + 2 * N + count * per;
@@ -520,7 +525,7 @@ struct Api {
       *rlc_pass = res[0];
       return BPP_OK;
     }
-    BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), ppp + vs.nV, pk->wtab_f, nullptr, pk->dtab, pk->cD, pk->WD));
+    BPP_TRY(Msm<C>::run(ctx, count * K, count, K, nullptr, pk->wtab, pk->n_points(), pk->cA, pk->WA, ctx->buf[B_DYN].as<uint32_t>(), ppp + vs.nV, pk->wtab_f, nullptr, pk->dtab, pk->cD, pk->WD, fuse ? &vsrc : nullptr));
     BPP_LAUNCH(verdict_kernel<C>, ceil_div(count, 128), 128, 0, count, ppp, vs.nV, ctx->buf[B_RESULTS].as<uint32_t>(),
                ctx->buf[B_DYN_OK].as<uint8_t>(), ctx->buf[B_FLAGS2].as<uint8_t>(), d_verdicts);
     return BPP_OK;

@@ -220,20 +220,21 @@ struct Msm {
   static int run(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start,
                  const uint32_t* wtab, uint32_t n_fixed, uint32_t cA, uint32_t WA, const uint32_t* dyn, uint32_t dyn_per_job,
                  const uint32_t* wtab_f = nullptr, const uint32_t* dyn_f = nullptr, const uint32_t* dtab = nullptr, uint32_t cD = 0,
-                 uint32_t WD = 0) {
+                 uint32_t WD = 0, const DirectVerifySrc* vsrc = nullptr) {
     if (n_jobs == 0) return BPP_OK;
     // direct tables exist for the Ed25519 policy only; a job is one block's work there, so a handful of jobs (one proof, one RLC
     // combination) is better served by the bucket path, which spreads a job over the whole chip
-    const bool direct = dtab && n_fixed && wtab && C::HAS_COOP4 && n_jobs >= 32;
+    const bool direct = uses_direct(dtab, n_jobs) && n_fixed && wtab;
+    if (vsrc && !direct) { ctx->err = "msm: fused exponents need the direct tables"; return BPP_ERR_UNSUPPORTED; }
     const bool two = n_fixed && wtab && dyn_per_job && overlaps(n_jobs);
     if (!two) {
       if (!direct) return run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 3, wtab_f, dyn_f);
       BPP_CK(ctx->buf[B_RESULTS].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
-      if (!dyn_per_job) return run_direct(ctx, n_terms, n_jobs, uniform, d_job_start, n_fixed, dtab, cD, WD, ctx->buf[B_RESULTS].as<uint32_t>());
+      if (!dyn_per_job) return run_direct(ctx, n_terms, n_jobs, uniform, d_job_start, n_fixed, dtab, cD, WD, ctx->buf[B_RESULTS].as<uint32_t>(), vsrc);
       // few jobs with both kinds of terms: generic segment, then the fixed-base terms from the direct tables, one stream
       BPP_TRY(run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 2, wtab_f, dyn_f));
       BPP_CK(ctx->buf[B_FIXEDRES].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
-      BPP_TRY(run_direct(ctx, n_terms, n_jobs, uniform, d_job_start, n_fixed, dtab, cD, WD, ctx->buf[B_FIXEDRES].as<uint32_t>()));
+      BPP_TRY(run_direct(ctx, n_terms, n_jobs, uniform, d_job_start, n_fixed, dtab, cD, WD, ctx->buf[B_FIXEDRES].as<uint32_t>(), vsrc));
       BPP_LAUNCH(msm_join_kernel<C>, ceil_div(n_jobs, 128), 128, 0, n_jobs, ctx->buf[B_RESULTS].as<uint32_t>(), ctx->buf[B_FIXEDRES].as<uint32_t>());
       return BPP_OK;
     }
@@ -261,7 +262,7 @@ struct Msm {
     // whatever was queued on the auxiliary stream shares B_SCALARS / B_DYN with the next call: on any failure from here on
     // wait for it before returning
     if (rc != BPP_OK) { cudaStreamSynchronize(ctx->aux_stream); return rc; }
-    rc = direct ? run_direct(ctx, n_terms, n_jobs, uniform, d_job_start, n_fixed, dtab, cD, WD, ctx->buf[B_RESULTS].as<uint32_t>())
+    rc = direct ? run_direct(ctx, n_terms, n_jobs, uniform, d_job_start, n_fixed, dtab, cD, WD, ctx->buf[B_RESULTS].as<uint32_t>(), vsrc)
                 : run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, 0, 1, wtab_f, dyn_f);
     if (rc != BPP_OK) { cudaStreamSynchronize(ctx->aux_stream); return rc; }
     BPP_CK(cudaStreamWaitEvent(ctx->stream, ctx->aux_join, 0));
@@ -271,8 +272,13 @@ struct Msm {
 
   // The fixed-base terms (point index < n_fixed) of every job straight from the key's direct tables: ONE kernel, no sort, no
   // buckets, no reduction (pk_direct.cuh). Terms with other indices are skipped (the generic segment takes them).
+  // whether a launch sequence over n_jobs jobs takes the direct tables (callers that fuse work into that kernel ask beforehand)
+  static bool uses_direct(const uint32_t* dtab, uint32_t n_jobs) { return dtab && C::HAS_COOP4 && n_jobs >= 32; }
   static int run_direct(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start, uint32_t n_fixed,
-                        const uint32_t* dtab, uint32_t cD, uint32_t WD, uint32_t* out) {
+                        const uint32_t* dtab, uint32_t cD, uint32_t WD, uint32_t* out, const DirectVerifySrc* vsrc = nullptr) {
+    DirectVerifySrc src;
+    memset(&src, 0, sizeof(src));
+    if (vsrc) src = *vsrc;
     MsmPlan pl;
     memset(&pl, 0, sizeof(pl));
     pl.n_terms = n_terms; pl.n_jobs = n_jobs; pl.uniform = uniform; pl.n_fixed = n_fixed; pl.cA = cD; pl.WA = WD;
@@ -296,8 +302,12 @@ struct Msm {
       BPP_CK(cudaEventRecord(e0, ctx->stream));
     }
     if constexpr (C::HAS_COOP4) {
-      BPP_LAUNCH(direct_accumulate_kernel<C>, ceil_div((uint64_t)n_jobs * S, 128 / tpj), 128, 0, pl, tpj, S, ctx->buf[B_SCALARS].as<uint32_t>(),
-                 ctx->buf[B_PIDX].as<uint32_t>(), d_job_start, dtab, partial);
+      if (src.enabled)
+        BPP_LAUNCH((direct_accumulate_kernel<C, true>), ceil_div((uint64_t)n_jobs * S, 128 / tpj), 128, 0, pl, tpj, S, ctx->buf[B_SCALARS].as<uint32_t>(),
+                   ctx->buf[B_PIDX].as<uint32_t>(), d_job_start, dtab, partial, src);
+      else
+        BPP_LAUNCH((direct_accumulate_kernel<C, false>), ceil_div((uint64_t)n_jobs * S, 128 / tpj), 128, 0, pl, tpj, S, ctx->buf[B_SCALARS].as<uint32_t>(),
+                   ctx->buf[B_PIDX].as<uint32_t>(), d_job_start, dtab, partial, src);
       if (S > 1) BPP_LAUNCH(direct_join_kernel<C>, ceil_div(n_jobs, 128), 128, 0, n_jobs, S, partial, out);
     } else {
       ctx->err = "direct tables: unsupported curve"; return BPP_ERR_UNSUPPORTED;

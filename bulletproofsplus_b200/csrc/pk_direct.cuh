@@ -10,6 +10,7 @@
 // Ristretto255 only (the tuned primary curve); the other curves and keys without these tables keep the bucket path.
 #pragma once
 #include "msm.cuh"
+#include "scalar.cuh"
 
 namespace bpp {
 
@@ -82,6 +83,34 @@ __global__ void __launch_bounds__(128) dtab_normalise_kernel(uint64_t n_entries,
 // the job's result). Slices exist for wave quantisation: 2048 one-block jobs are 3.46 waves of the 592 resident blocks of a
 // B200 (86 % of four), 8192 quarter-job blocks are 13.8. Terms whose point is not in the key (index >= n_fixed: per-call
 // points) are left to the generic segment.
+// Exponents of the generator terms of a verification MSM computed where they are used (proto_verify.cuh: exponent_k =
+// Tmul_k * x + Tadd_k, x one of the proof's r', s', delta', r's'): term k of job p is g (k = 3), h (k = 4), G_i (k = K0 + i) or
+// H_i (k = K0 + N + i); every other term is a per-call point and belongs to the generic segment. enabled == 0: plain
+// (scalar, point index) arrays as for every other caller.
+struct DirectVerifySrc {
+  uint32_t enabled, K0, N, stride_T;       // stride_T in words: 0 = one challenge set for all proofs
+  const uint32_t* Tmul;                    // Montgomery form
+  const uint32_t* Tadd;                    // canonical
+  const uint32_t* xs;                      // [proof][r', s', delta', r' s'] canonical
+};
+// returns false when term k is not a generator term; s = canonical exponent, p = table index (g, h, G.., H..)
+static __device__ __noinline__ bool direct_verify_term(const DirectVerifySrc& v, uint32_t job, uint32_t k, uint32_t* s, uint32_t& p) {
+  typedef Sc<ModEll> S;
+  uint32_t sel;
+  if (k == 3) { p = 0; sel = 3; }
+  else if (k == 4) { p = 1; sel = 2; }
+  else if (k >= v.K0 && k < v.K0 + v.N) { p = 2 + (k - v.K0); sel = 0; }
+  else if (k >= v.K0 + v.N && k < v.K0 + 2 * v.N) { p = 2 + v.N + (k - v.K0 - v.N); sel = 1; }
+  else return false;
+  const uint32_t* tm = v.Tmul + (size_t)job * v.stride_T + 8 * k;
+  const uint32_t* ta = v.Tadd + (size_t)job * v.stride_T + 8 * k;
+  S val = S::raw(tm) * S::raw(v.xs + (size_t)job * 32 + 8 * sel);  // Montgomery x canonical = canonical
+  if (k != 4) val = val + S::raw(ta);                              // h carries no constant part (wip.rs:292)
+#pragma unroll
+  for (int i = 0; i < 8; i++) s[i] = val.v[i];
+  return true;
+}
+
 template <class C>
 __device__ __forceinline__ void direct_add(typename C::Ext& acc, bool& have, const uint32_t* ptr, uint32_t neg) {
   if (have) C::madd_ptr(acc, ptr, neg);
@@ -93,10 +122,12 @@ __device__ __forceinline__ void direct_load_scalar(const uint32_t* __restrict__ 
   s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
 }
 
-template <class C>
-__global__ void __launch_bounds__(128)
+// FUSED: the exponents come from DirectVerifySrc (a second instantiation, so that the plain one keeps its register allocation)
+template <class C, bool FUSED>
+__global__ void __launch_bounds__(128, 4)
 direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, uint32_t S, const uint32_t* __restrict__ scalars, const uint32_t* __restrict__ pidx,
-                         const uint32_t* __restrict__ job_start, const uint32_t* __restrict__ dtab, uint32_t* __restrict__ partial) {
+                         const uint32_t* __restrict__ job_start, const uint32_t* __restrict__ dtab, uint32_t* __restrict__ partial,
+                         DirectVerifySrc vsrc) {
   __shared__ uint32_t sh[128 * C::EXT_WORDS];
   const uint32_t tid = threadIdx.x, lane = tid & (tpj - 1);
   const uint32_t unit = blockIdx.x * (128 / tpj) + tid / tpj;  // (job, slice)
@@ -111,10 +142,14 @@ direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, uint32_t S, const uint32_t* _
     const uint32_t GL = tpj * S, gl = slice * tpj + lane, K = t1 - t0, full = K / GL;
     for (uint32_t r = 0; r < full; r++) {  // phase 1
       const uint32_t t = t0 + r * GL + gl;
-      const uint32_t p = pidx[t];
-      if (p >= n) continue;
-      uint32_t s[8];
-      direct_load_scalar(scalars, t, s);
+      uint32_t s[8], p;
+      if (FUSED) {
+        if (!direct_verify_term(vsrc, job, t - t0, s, p)) continue;
+      } else {
+        p = pidx[t];
+        if (p >= n) continue;
+        direct_load_scalar(scalars, t, s);
+      }
       const uint32_t flip = msm_fold_half(pl, s);
       // software pipeline over the windows: (cur) is added while (nxt) is recoded and its line prefetched
       uint32_t carry = 0;
@@ -142,10 +177,14 @@ direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, uint32_t S, const uint32_t* _
     const uint32_t tb = t0 + full * GL, R = K - full * GL;  // phase 2
     for (uint32_t idx = gl; idx < R * W; idx += GL) {
       const uint32_t t = tb + idx / W, w = idx % W;
-      const uint32_t p = pidx[t];
-      if (p >= n) continue;
-      uint32_t s[8];
-      direct_load_scalar(scalars, t, s);
+      uint32_t s[8], p;
+      if (FUSED) {
+        if (!direct_verify_term(vsrc, job, t - t0, s, p)) continue;
+      } else {
+        p = pidx[t];
+        if (p >= n) continue;
+        direct_load_scalar(scalars, t, s);
+      }
       const uint32_t flip = msm_fold_half(pl, s);
       uint32_t carry = 0;
       for (uint32_t v = 0; v < w; v++) carry = (msm_bits(s, v * c, c) + carry) > half;  // windows below w are all signed

@@ -135,8 +135,10 @@ __device__ Sc<M> block_sum(Sc<M> v, uint32_t* sh) {  // sh: blockDim.x * 8 words
 // one block per proof; blockDim.x must be a power of two. a, b: this proof's vectors (Montgomery, N each,
 // overwritten). Emits the MSM terms of every job of the proof and the three final scalars.
 // job order per proof: [A], L_0..L_{L-1}, R_0..R_{L-1}, wipA, wipB   (= wire order of include/bpp.h)
+// 256 threads, two blocks per SM (<= 128 registers): at 153 registers one block fitted per SM and a batch of 256 proofs ran as
+// two waves, the second 27 % full.
 template <class M>
-__global__ void wip_prove_kernel(ProveShape ps, ProveTables T, const uint32_t* __restrict__ params, uint32_t* __restrict__ a_all,
+__global__ void __launch_bounds__(256, 2) wip_prove_kernel(ProveShape ps, ProveTables T, const uint32_t* __restrict__ params, uint32_t* __restrict__ a_all,
                                  uint32_t* __restrict__ b_all, const uint32_t* __restrict__ alpha_all,
                                  uint32_t* __restrict__ out_scalars, uint32_t* __restrict__ out_pidx, uint8_t* __restrict__ proofs,
                                  size_t proof_stride, size_t scalar_off) {

@@ -101,8 +101,10 @@ verify_inverses_kernel(uint32_t n_proofs, uint32_t L, const uint32_t* __restrict
 
 // one block of VT_THREADS threads; ext_* are canonical inputs used only when mode == 0
 constexpr int VT_THREADS = 512;
-template <class M>
-__global__ void __launch_bounds__(VT_THREADS)
+// NT = block size: 512 for the one block of a shared challenge set, 128 with six blocks per SM (<= 85 registers; at 127 only
+// four fitted and the kernel sat at 27 % issue slots, latency-bound) for one block per proof
+template <class M, int NT>
+__global__ void __launch_bounds__(NT, NT == 128 ? 6 : 1)
 verify_tables_kernel(VerifyShape vs, const uint32_t* __restrict__ params, const uint32_t* __restrict__ ext_Gc,
                      const uint32_t* __restrict__ ext_Hc, const uint32_t* __restrict__ ext_gc,
                      const uint32_t* __restrict__ ext_Vc, const uint32_t* __restrict__ ext_y, VerifyTables T) {
@@ -297,14 +299,21 @@ __global__ void verify_proof_scalars_kernel(uint32_t n_proofs, const uint8_t* __
 
 // grid: (ceil(K / blockDim), n_proofs). Writes K = 5 + 2L + 2N + nV terms per proof:
 //   [wipB, wipA, A', g, h, L.., R.., G.., H.., V..] with exponents lam * [1, e, e^2, g_exp, h_exp, ...]  (wip.rs:297-318)
+// skip_fixed: the generator terms (g, h, G_i, H_i) get their point index only — their exponents are computed where they are
+// used, inside direct_accumulate_kernel (pk_direct.cuh, DirectVerifySrc), which saves this kernel's multiplication and the
+// round trip of 2 + 2N scalars per proof through HBM.
 template <class M>
 __global__ void verify_scalars_kernel(VerifyShape vs, VerifyTables T, const uint32_t* __restrict__ xs,
-                                      uint32_t* __restrict__ out_scalars, uint32_t* __restrict__ out_pidx) {
+                                      uint32_t* __restrict__ out_scalars, uint32_t* __restrict__ out_pidx, uint32_t skip_fixed) {
   typedef Sc<M> S;
   const uint32_t N = vs.N, L = vs.L, K = 5 + 2 * L + 2 * N + vs.nV;
   const uint32_t p = blockIdx.y;
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= K) return;
+  if (skip_fixed && (k == 3 || k == 4 || (k >= 5 + 2 * L && k < 5 + 2 * L + 2 * N))) {
+    out_pidx[(size_t)p * K + k] = k == 3 ? 0u : k == 4 ? 1u : k < 5 + 2 * L + N ? vs.pk_G0 + (k - 5 - 2 * L) : vs.pk_H0 + (k - 5 - 2 * L - N);
+    return;
+  }
   const uint32_t dyn = vs.dyn0 + p * (2 * L + 3);  // this proof's decoded points: A, L.., R.., wipA, wipB
   const uint32_t* x = xs + (size_t)p * 32;
   T.Tadd += (size_t)p * T.stride_T; T.Tmul += (size_t)p * T.stride_T;
