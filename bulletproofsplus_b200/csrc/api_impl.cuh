@@ -478,7 +478,7 @@ struct Api {
       T.pre = ctx->buf[B_TAB6].as<uint32_t>(); T.stride_pre = (L + 2) * 8;
       BPP_LAUNCH(verify_inverses_kernel<M>, ceil_div(count, 32), 32, 0, count, L, ctx->buf[B_TAB5].as<uint32_t>(), T.stride_params,
                  ctx->buf[B_TAB6].as<uint32_t>(), T.stride_pre);
-      BPP_LAUNCH((verify_tables_kernel<M, 128>), count, 128, 0, vs, ctx->buf[B_TAB5].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
+      BPP_LAUNCH((verify_tables_kernel<M, 256>), count, 256, 0, vs, ctx->buf[B_TAB5].as<uint32_t>(), ext_Gc, ext_Hc, ext_gc, ext_Vc, ext_y, T);
     } else {
       const size_t cap0 = ctx->buf[B_TAB0].cap + ctx->buf[B_TAB1].cap + ctx->buf[B_TAB2].cap + ctx->buf[B_TAB3].cap;
       if (!tables_cached(ctx, 1, pk, N, n, m, mode) || cap0 != ctx->tab_caps)
@@ -487,8 +487,10 @@ struct Api {
     }
     dim3 grid(ceil_div(K, 256), count);
     // with the key's direct tables the generator terms' exponents are computed inside the accumulation kernel (DirectVerifySrc)
-    static const bool no_fuse = getenv("BPP_NO_FUSE") != nullptr;  // A/B switch
-    const bool fuse = !no_fuse && !d_weights && C::CURVE_ID == 0 && Msm<C>::uses_direct(pk->dtab, count);
+    // (measured slower — 7.08 vs 6.72 ms per 2048 proofs: the exponent arithmetic costs the accumulation kernel 6 registers and
+    // 144 B of spills, more than the 0.25 ms it saves here; off unless BPP_FUSE is set, profiles/r02h_bench_{fused,nofuse}_*.json)
+    static const bool want_fuse = getenv("BPP_FUSE") != nullptr;  // A/B switch
+    const bool fuse = want_fuse && !d_weights && C::CURVE_ID == 0 && Msm<C>::uses_direct(pk->dtab, count);
     BPP_LAUNCH(verify_scalars_kernel<M>, grid, 256, 0, vs, T, xs, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>(), fuse ? 1u : 0u);
     DirectVerifySrc vsrc;
     vsrc.enabled = 1; vsrc.K0 = 5 + 2 * L; vsrc.N = N; vsrc.stride_T = T.stride_T; vsrc.Tmul = T.Tmul; vsrc.Tadd = T.Tadd; vsrc.xs = xs;

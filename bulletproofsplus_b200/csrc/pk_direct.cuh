@@ -111,11 +111,6 @@ static __device__ __noinline__ bool direct_verify_term(const DirectVerifySrc& v,
   return true;
 }
 
-template <class C>
-__device__ __forceinline__ void direct_add(typename C::Ext& acc, bool& have, const uint32_t* ptr, uint32_t neg) {
-  if (have) C::madd_ptr(acc, ptr, neg);
-  else { C::init_from_ptr(acc, ptr, neg); have = true; }
-}
 __device__ __forceinline__ void direct_load_scalar(const uint32_t* __restrict__ scalars, uint32_t t, uint32_t* s) {
   const uint4* sp = reinterpret_cast<const uint4*>(scalars + 8ull * t);
   const uint4 a = __ldg(sp), b = __ldg(sp + 1);
@@ -135,11 +130,18 @@ direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, uint32_t S, const uint32_t* _
   const bool live = job < pl.n_jobs;
   const uint32_t c = pl.cA, W = pl.WA, half = 1u << (c - 1), n = pl.n_fixed;
   typename C::Ext acc;
-  bool have = false;
+  C::set_identity(acc);  // complete formulas: adding to the identity is an ordinary addition
   if (live) {
     const uint32_t t0 = pl.uniform ? job * pl.uniform : job_start[job];
     const uint32_t t1 = pl.uniform ? t0 + pl.uniform : job_start[job + 1];
     const uint32_t GL = tpj * S, gl = slice * tpj + lane, K = t1 - t0, full = K / GL;
+    // The digit loop costs instructions beside the ~1064 of an addition, and on sm_100a every issued instruction counts (the ALU
+    // work does not overlap the wide multiplies). So: the scalar is SHIFTED down by c bits per window (eight funnel
+    // shifts on registers; indexing s[] by a runtime window number put it in local memory), the table region of (window, point)
+    // is a running pointer advanced by one window stride, and the accumulator starts as the identity so that the loop holds one
+    // addition and no first-entry case (first version: 1342 instructions per iteration, profiles/r02_sass_direct_loop.txt).
+    const size_t wstride = ((size_t)n << (c - 1)) * C::AFF_WORDS;  // words from window w to w + 1 (signed windows)
+    const uint32_t cmask = (1u << c) - 1u;
     for (uint32_t r = 0; r < full; r++) {  // phase 1
       const uint32_t t = t0 + r * GL + gl;
       uint32_t s[8], p;
@@ -151,27 +153,32 @@ direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, uint32_t S, const uint32_t* _
         direct_load_scalar(scalars, t, s);
       }
       const uint32_t flip = msm_fold_half(pl, s);
-      // software pipeline over the windows: (cur) is added while (nxt) is recoded and its line prefetched
-      uint32_t carry = 0;
-      const uint32_t* cur = nullptr;
-      uint32_t cur_neg = 0;
-      for (uint32_t w = 0; w <= W; w++) {
-        const uint32_t* nxt = nullptr;
-        uint32_t nxt_neg = 0;
-        if (w < W) {
-          const uint32_t raw = msm_bits(s, w * c, c) + carry;
-          const uint32_t neg = (w + 1 < W) && raw > half;  // the last window is taken unsigned: no carry out of it
-          const uint32_t mag = neg ? (1u << c) - raw : raw;
-          carry = neg;
-          if (mag) {
-            nxt = dtab + (dtab_offset(w, p, n, c, W) + (mag - 1)) * C::AFF_WORDS;
-            nxt_neg = neg ^ flip;
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
-          }
-        }
-        if (cur) direct_add<C>(acc, have, cur, cur_neg);
+      const uint32_t* wp = dtab + ((size_t)p << (c - 1)) * C::AFF_WORDS;  // region of (window 0, point p)
+      uint32_t carry = 0, cur_neg = 0;
+      const uint32_t* cur = nullptr;  // the addition in flight: (cur) is added while the next digit is recoded and prefetched
+      for (uint32_t w = 0; w + 1 < W; w++) {  // signed windows
+        const uint32_t raw = (s[0] & cmask) + carry;
+#pragma unroll
+        for (int q = 0; q < 7; q++) s[q] = __funnelshift_r(s[q], s[q + 1], c);
+        s[7] >>= c;
+        const uint32_t neg = raw > half;
+        const uint32_t mag = neg ? (1u << c) - raw : raw;
+        carry = neg;
+        const uint32_t* nxt = mag ? wp + (size_t)(mag - 1) * C::AFF_WORDS : nullptr;
+        if (mag) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
+        wp += wstride;
+        if (cur) C::madd_ptr(acc, cur, cur_neg);
         cur = nxt;
-        cur_neg = nxt_neg;
+        cur_neg = neg ^ flip;
+      }
+      {  // last window, unsigned: what is left of the scalar (< 2^c) + carry <= 2^c; its regions hold 2^c entries
+        // (a non-canonical scalar — rejected with FORMAT by the callers, but still run — is not folded and may have more bits left:
+        // clamped so that the read stays inside the region)
+        const uint32_t left = s[0] + carry, mag = left < (1u << c) ? left : (1u << c);
+        const uint32_t* nxt = mag ? dtab + (dtab_offset(W - 1, p, n, c, W) + (mag - 1)) * C::AFF_WORDS : nullptr;
+        if (mag) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
+        if (cur) C::madd_ptr(acc, cur, cur_neg);
+        if (nxt) C::madd_ptr(acc, nxt, flip);
       }
     }
     const uint32_t tb = t0 + full * GL, R = K - full * GL;  // phase 2
@@ -191,10 +198,9 @@ direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, uint32_t S, const uint32_t* _
       const uint32_t raw = msm_bits(s, w * c, c) + carry;
       const uint32_t neg = (w + 1 < W) && raw > half;
       const uint32_t mag = neg ? (1u << c) - raw : raw;
-      if (mag) direct_add<C>(acc, have, dtab + (dtab_offset(w, p, n, c, W) + (mag - 1)) * C::AFF_WORDS, neg ^ flip);
+      if (mag) C::madd_ptr(acc, dtab + (dtab_offset(w, p, n, c, W) + (mag - 1)) * C::AFF_WORDS, neg ^ flip);
     }
   }
-  if (!have) C::set_identity(acc);
   typename C::Ext* mine = reinterpret_cast<typename C::Ext*>(sh + tid * C::EXT_WORDS);
   *mine = acc;
   __syncthreads();

@@ -101,10 +101,11 @@ verify_inverses_kernel(uint32_t n_proofs, uint32_t L, const uint32_t* __restrict
 
 // one block of VT_THREADS threads; ext_* are canonical inputs used only when mode == 0
 constexpr int VT_THREADS = 512;
-// NT = block size: 512 for the one block of a shared challenge set, 128 with six blocks per SM (<= 85 registers; at 127 only
-// four fitted and the kernel sat at 27 % issue slots, latency-bound) for one block per proof
+// NT = block size: 512 for the one block of a shared challenge set, 256 for one block per proof. (Holding the per-proof instance
+// to 80 registers for six 128-thread blocks per SM instead of four was measured slower — 1.20 vs 1.05 ms per 2048 proofs: 384 B of
+// spills on the scalar arithmetic.)
 template <class M, int NT>
-__global__ void __launch_bounds__(NT, NT == 128 ? 6 : 1)
+__global__ void __launch_bounds__(NT)
 verify_tables_kernel(VerifyShape vs, const uint32_t* __restrict__ params, const uint32_t* __restrict__ ext_Gc,
                      const uint32_t* __restrict__ ext_Hc, const uint32_t* __restrict__ ext_gc,
                      const uint32_t* __restrict__ ext_Vc, const uint32_t* __restrict__ ext_y, VerifyTables T) {
