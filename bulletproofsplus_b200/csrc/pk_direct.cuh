@@ -135,11 +135,12 @@ direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, uint32_t S, const uint32_t* _
     const uint32_t t0 = pl.uniform ? job * pl.uniform : job_start[job];
     const uint32_t t1 = pl.uniform ? t0 + pl.uniform : job_start[job + 1];
     const uint32_t GL = tpj * S, gl = slice * tpj + lane, K = t1 - t0, full = K / GL;
-    // The digit loop costs instructions beside the ~1064 of an addition, and on sm_100a every issued instruction counts (the ALU
-    // work does not overlap the wide multiplies). So: the scalar is SHIFTED down by c bits per window (eight funnel
-    // shifts on registers; indexing s[] by a runtime window number put it in local memory), the table region of (window, point)
-    // is a running pointer advanced by one window stride, and the accumulator starts as the identity so that the loop holds one
-    // addition and no first-entry case (first version: 1342 instructions per iteration, profiles/r02_sass_direct_loop.txt).
+    // Digit loop: the scalar is SHIFTED down by c bits per window (eight funnel shifts on registers; indexing s[] by a runtime
+    // window number put it in local memory), the table region of (window, point) is a running pointer advanced by one window
+    // stride, and the accumulator starts as the identity so that the loop holds one addition and no first-entry case. Measured
+    // (profiles/r02_sass_direct_loop.txt): 1342 -> 1109 instructions per addition bought under 1 % — the loop is bound by the
+    // IMAD.WIDE issue rate, not by instruction count — while a variant with three inlined additions lost 13 % to the
+    // instruction cache. Keep ONE madd_ptr per phase.
     const size_t wstride = ((size_t)n << (c - 1)) * C::AFF_WORDS;  // words from window w to w + 1 (signed windows)
     const uint32_t cmask = (1u << c) - 1u;
     for (uint32_t r = 0; r < full; r++) {  // phase 1
@@ -153,32 +154,34 @@ direct_accumulate_kernel(MsmPlan pl, uint32_t tpj, uint32_t S, const uint32_t* _
         direct_load_scalar(scalars, t, s);
       }
       const uint32_t flip = msm_fold_half(pl, s);
-      const uint32_t* wp = dtab + ((size_t)p << (c - 1)) * C::AFF_WORDS;  // region of (window 0, point p)
+      const uint32_t* wp = dtab + ((size_t)p << (c - 1)) * C::AFF_WORDS;                    // region of (window 0, point p)
+      const uint32_t* wlast = dtab + dtab_offset(W - 1, p, n, c, W) * C::AFF_WORDS;         // region of the last window (2^c entries)
       uint32_t carry = 0, cur_neg = 0;
       const uint32_t* cur = nullptr;  // the addition in flight: (cur) is added while the next digit is recoded and prefetched
-      for (uint32_t w = 0; w + 1 < W; w++) {  // signed windows
-        const uint32_t raw = (s[0] & cmask) + carry;
+      // ONE call site of madd_ptr for the whole term: a version with the last window peeled out of the loop had three inlined
+      // copies (51 KB of hot code) and ran 13 % slower although its loop was 260 instructions shorter — instruction cache.
+      for (uint32_t w = 0; w <= W; w++) {
+        const uint32_t* nxt = nullptr;
+        uint32_t nxt_neg = 0;
+        if (w < W) {
+          const bool last = w + 1 == W;  // taken unsigned: what is left of the scalar (< 2^c; masked: a non-canonical scalar stays in range)
+          const uint32_t raw = (s[0] & cmask) + carry;
 #pragma unroll
-        for (int q = 0; q < 7; q++) s[q] = __funnelshift_r(s[q], s[q + 1], c);
-        s[7] >>= c;
-        const uint32_t neg = raw > half;
-        const uint32_t mag = neg ? (1u << c) - raw : raw;
-        carry = neg;
-        const uint32_t* nxt = mag ? wp + (size_t)(mag - 1) * C::AFF_WORDS : nullptr;
-        if (mag) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
-        wp += wstride;
+          for (int q = 0; q < 7; q++) s[q] = __funnelshift_r(s[q], s[q + 1], c);
+          s[7] >>= c;
+          const uint32_t neg = !last && raw > half;
+          const uint32_t mag = neg ? (1u << c) - raw : raw;
+          carry = neg;
+          if (mag) {
+            nxt = (last ? wlast : wp) + (size_t)(mag - 1) * C::AFF_WORDS;
+            nxt_neg = neg ^ flip;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
+          }
+          wp += wstride;
+        }
         if (cur) C::madd_ptr(acc, cur, cur_neg);
         cur = nxt;
-        cur_neg = neg ^ flip;
-      }
-      {  // last window, unsigned: what is left of the scalar (< 2^c) + carry <= 2^c; its regions hold 2^c entries
-        // (a non-canonical scalar — rejected with FORMAT by the callers, but still run — is not folded and may have more bits left:
-        // clamped so that the read stays inside the region)
-        const uint32_t left = s[0] + carry, mag = left < (1u << c) ? left : (1u << c);
-        const uint32_t* nxt = mag ? dtab + (dtab_offset(W - 1, p, n, c, W) + (mag - 1)) * C::AFF_WORDS : nullptr;
-        if (mag) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
-        if (cur) C::madd_ptr(acc, cur, cur_neg);
-        if (nxt) C::madd_ptr(acc, nxt, flip);
+        cur_neg = nxt_neg;
       }
     }
     const uint32_t tb = t0 + full * GL, R = K - full * GL;  // phase 2
