@@ -852,13 +852,14 @@ def run_msm_split(bn, int_peak):
 
 def run_msm_sweep(bn, int_peak):
     """MSM points/s vs size, every power of two 2^10 .. 2^msm_max_log, three curves, device-resident, CUDA-event timed.
-    SURVEY §8(d): field multiply = 72 IMAD for 2^255-19, 300 for BLS12-381; the secp256k1 field here is generic Montgomery
-    (8 x 8 + 8 x 8 = 128 IMAD executed), so its fraction is given for both the algorithmic 72 and the executed 128.
+    SURVEY §8(d): field multiply = 72 IMAD for 2^255-19, 300 for BLS12-381; the secp256k1 field uses the special form of
+    p = 2^256 - 2^32 - 977 (64 + 8 + 1 = 73 wide products executed; it was generic Montgomery, 128, until r02m), so its fraction
+    is given for both the algorithmic 72 and the executed 73.
     Edwards mixed/full/double = 7/8/8 field multiplies, short Weierstrass 11/16/7."""
     torch, api, ctx, lib, _lib, args = bn.torch, bn.api, bn.ctx, bn.lib, bn._lib, bn.args
     out = {}
     curves = (("", _lib.RISTRETTO255, 253, 72, None, (7, 8, 8), 20),
-              ("_secp256k1", _lib.SECP256K1, 256, 72, 128, (11, 16, 7), 16),
+              ("_secp256k1", _lib.SECP256K1, 256, 72, 73, (11, 16, 7), 16),
               ("_bls12_381_g1", _lib.BLS12_381_G1, 255, 300, None, (11, 16, 7), 16))
     for suffix, curve, bits, imad, imad_exec, costs, tables_max in curves:
         sweep = []
