@@ -747,6 +747,9 @@ def run_configs_2_3(bn):
     return out
 
 
+C4_TABLE_BYTES = 6 << 30  # config 4's key: c = 15 fits (4.9 GB), c = 16 (9.3 GB) does not
+
+
 def run_config4(bn):
     """BASELINE.json config 4: a FIXED batch of 8192 independent n=64, m=1 proofs (146-term MSM each, 128 of them tampered)
     sharded over the ranks by parallel.shard_range: strong scaling. Rank 0 holds the host batch; e2e includes the scatter
@@ -756,6 +759,9 @@ def run_config4(bn):
     torch, dist, api, ctx, lib = bn.torch, bn.dist, bn.api, bn.ctx, bn.lib
     n, m, TOTAL = 64, 1, 8192
     pk = api.PublicKey.new(n * m, 0, ctx)
+    c4_tables = None
+    if bn.args.table_gb > 0:  # direct tables for the 130 generators of this key: 4.9 GB at c = 15 (setup, untimed)
+        c4_tables = pk.precompute(min(int(bn.args.table_gb * 2**30), C4_TABLE_BYTES))
     plen = lib.bpp_range_proof_len(0, n, m)
     lo, hi = parallel.shard_range(TOTAL, bn.rank, bn.world)
     cnt = hi - lo
@@ -797,6 +803,7 @@ def run_config4(bn):
         "tampered": TOTAL // 64, "verdicts_match_tamper_pattern": True,
         "e2e": {"value": TOTAL / (ms_h * 1e-3), "unit": "proofs/s", "ms": ms_h, "h2d_bytes_per_step": cnt * (plen + 32), "d2h_bytes_per_step": cnt},
         "exchange": "all-gather of the verdict bytes (NCCL)" if bn.world > 1 else "none",
+        "fixed_base_tables_window_bits": c4_tables,
         "algorithmic_field_muls_per_proof": algorithmic_field_muls(146)[0]}}
 
 

@@ -105,17 +105,30 @@ struct Sc {
     for (int i = 0; i < 8; i++) r.v[i] = t[8 + i];
     return r;
   }
-  // Montgomery product: 8x8 schoolbook (IMAD.WIDE carry chains, shared with the base field) + reduction
-  BPP_DEV friend Sc operator*(const Sc& a, const Sc& b) {
+  // Montgomery product: 8x8 schoolbook (IMAD.WIDE carry chains, shared with the base field) + reduction.
+  // The product and the square are real FUNCTIONS (operands and result in registers by the ABI), not inlined: the kernels that
+  // use scalars are long straight-line protocol code with 50-150 multiplications each, and inlined they were 0.3-0.5 MB of
+  // instructions that every warp executed about once - bound by instruction fetch, not by any pipe.
+#ifdef BPP_SC_INLINE_MUL
+  BPP_DEV static Sc mul_core(const Sc& a, const Sc& b) {
+#else
+  __device__ __noinline__ static Sc mul_core(Sc a, Sc b) {
+#endif
     uint32_t t[16];
     mul_wide_n<8>(t, a.v, b.v);
     return mont_reduce(t);
   }
-  BPP_DEV Sc sqr() const {  // 36 wide products instead of 64 (the inversion chains are ~250 squarings)
+#ifdef BPP_SC_INLINE_MUL
+  BPP_DEV static Sc sqr_core(const Sc& a) {
+#else
+  __device__ __noinline__ static Sc sqr_core(Sc a) {
+#endif
     uint32_t t[16];
-    sqr_wide_n<8>(t, v);
+    sqr_wide_n<8>(t, a.v);
     return mont_reduce(t);
   }
+  BPP_DEV friend Sc operator*(const Sc& a, const Sc& b) { return mul_core(a, b); }
+  BPP_DEV Sc sqr() const { return sqr_core(*this); }  // 36 wide products instead of 64 (the inversion chains are ~250 squarings)
   BPP_DEV bool is_zero() const { uint32_t o = 0; for (int i = 0; i < 8; i++) o |= v[i]; return o == 0; }
 
   // canonical little-endian limbs <-> Montgomery

@@ -1,5 +1,5 @@
 """One workload of the hot path, timed with the wall clock around a stream sync (development aid; bench.py is the
-measurement of record).  usage: run_case.py verify|prove|msm|commit SIZE [reps] [curve]"""
+measurement of record).  usage: run_case.py verify|prove|msm|commit SIZE [reps] [curve]   env: BPP_TABLE_GB (direct tables), BPP_NM="n,m" (default 64,16)"""
 import ctypes as C, os, sys, time, random
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from bulletproofsplus_b200 import api, _lib
@@ -11,7 +11,7 @@ ctx = api.Context(0)
 lib = ctx.lib
 ELL = api.ORDERS[0]
 rng = random.Random(7)
-n, m = 64, 16
+n, m = (int(x) for x in os.environ.get("BPP_NM", "64,16").split(","))  # aggregation shape of the range-proof cases
 
 def timeit(f, label):
     f(); ctx.sync()

@@ -7,7 +7,7 @@ from bulletproofsplus_b200 import api
 case, size = sys.argv[1], int(sys.argv[2])
 ctx = api.Context(0)
 rng = random.Random(7)
-n, m = 64, 16
+n, m = (int(x) for x in os.environ.get("BPP_NM", "64,16").split(","))  # aggregation shape; default the headline config
 ELL = api.ORDERS[0]
 if case == "msm":
     curve = int(sys.argv[4]) if len(sys.argv) > 4 else 0
