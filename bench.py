@@ -739,8 +739,23 @@ def run_configs_2_3(bn):
     ms = bn.timed(lambda: ctx.check(lib.bpp_range_verify_batch_dev(ctx.h, pk.handle, n, m, CB, d_V.data_ptr(), d_p.data_ptr(), None, d_vd.data_ptr()),
                                     "verify 64x64"), reps=5, warm=2, flush=True)
     assert bool((d_vd == 0).all())
+    # the same batch with direct tables for this key's 8194 generators, if HBM allows beside the headline key's (c = 12: 47 GB)
+    ms_bucket, c3_tables = ms, None
+    free_b = bn.torch.cuda.mem_get_info(bn.dev)[0]
+    budget = min(int(bn.args.table_gb * 2**30), free_b - (12 << 30))
+    if bn.args.table_gb > 0 and budget > (8 << 30):
+        try:
+            c3_tables = pk.precompute(budget)
+        except Exception as e:  # out of HBM beside the other keys' tables: keep the bucket-path figure
+            c3_tables = "unavailable: " + str(e)[:120]
+        else:
+            d_vd.fill_(255)
+            ms = bn.timed(lambda: ctx.check(lib.bpp_range_verify_batch_dev(ctx.h, pk.handle, n, m, CB, d_V.data_ptr(), d_p.data_ptr(), None,
+                                                                           d_vd.data_ptr()), "verify 64x64 tables"), reps=5, warm=2, flush=True)
+            assert bool((d_vd == 0).all())
     out["config3_n64_m64"] = {
         "single_proof_prove_ms": t_p, "single_proof_verify_ms": t_v, "batch": CB, "batch_verify_ms": ms, "batch_verifies_per_sec": CB / (ms * 1e-3),
+        "batch_verify_ms_bucket_path": ms_bucket, "fixed_base_tables_window_bits": c3_tables,
         "note": "one aggregated proof of 64 values (N = 4096): verifier MSM of 8285 terms; single-proof numbers are host-ABI latencies "
                 "(python packing included), the batch is device-resident",
         "algorithmic_field_muls_verify": algorithmic_field_muls(8285)[0]}
