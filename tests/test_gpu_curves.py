@@ -40,6 +40,10 @@ def test_field_ops(ctx, R):
     p, fb = FP[R], FB[R]
     rng = random.Random(R)
     edge = [0, 1, 2, 3, p - 1, p - 2, 2**32, 2**(8 * fb - 8) % p, (p + 1) // 2]
+    # operands that push the reductions' carries: just below p and 2^k, all-ones halves (secp256k1 folds the high half of the
+    # product with 2^256 = 2^32 + 977: fp_mont.cuh k1_reduce)
+    edge += [p - 977, p - 2**32, p - 2**32 - 977, (2**(8 * fb) - 1) % p, 2**(8 * fb - 1) % p, 2**(4 * fb) - 1, ((2**(4 * fb) - 1) << (4 * fb - 1)) % p,
+             2**(8 * fb - 32) % p, (p - 1) // 2, (p - 1) // 3]
     xs = edge + [rng.randrange(p) for _ in range(200)]
     ys = list(reversed(edge)) + [rng.randrange(p) for _ in range(200)]
     a, b = b"".join(x.to_bytes(fb, "little") for x in xs), b"".join(y.to_bytes(fb, "little") for y in ys)
