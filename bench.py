@@ -599,6 +599,44 @@ def run_fs_verify(bn, pk, B):
         "value": bn.world * B / (ms * 1e-3), "unit": "proofs/s", "batch_per_gpu": B, "ms_per_step": ms, "entry": "bpp_range_verify_batch_fs_dev",
         "e2e": {"value": bn.world * B / (ms_h * 1e-3), "unit": "proofs/s", "entry": "bpp_range_verify_batch_fs (host buffers)",
                 "h2d_bytes_per_step": B * (len(pb) // B + M_AGG * 32 + len(block)), "d2h_bytes_per_step": B}}}
+    # Two contexts in flight on one GPU (how a serving process with two worker threads uses the library: a bpp_ctx per thread,
+    # the key shared): the second context's challenge-table kernels (latency-bound) overlap the first one's accumulation
+    # (pipe-bound). Two different resident batches, calls issued alternately, no synchronisation between them; CUDA events on
+    # the first stream, which waits for the second before the closing event.
+    try:
+        stream2 = torch.cuda.Stream(bn.dev)
+        ctx2 = bn.api.Context(bn.local_rank, stream2.cuda_stream)
+        pb2, vb2, _, _ = bn.make_proofs(pk, N_BITS, M_AGG, B, seed=bn.rank * 1000 + 8)
+        d_pr2, d_V2 = bn.to_dev(pb2), bn.to_dev(vb2)
+        d_vd2 = torch.full((B,), 255, dtype=torch.uint8, device=bn.dev)
+
+        def dev_call2():
+            ctx2.check(lib.bpp_range_verify_batch_fs_dev(ctx2.h, pk.handle, N_BITS, M_AGG, B, d_V2.data_ptr(), d_pr2.data_ptr(), d_ch.data_ptr(),
+                                                         d_vd2.data_ptr()), "verify_fs_dev ctx2")
+
+        for _ in range(2):
+            dev_call(); dev_call2()
+        torch.cuda.synchronize()
+        reps2 = 5
+        e0, e1, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event()
+        e0.record(bn.stream)
+        stream2.wait_event(e0)
+        for _ in range(reps2):
+            bn.flush.zero_()
+            dev_call(); dev_call2()
+        e2.record(stream2)
+        bn.stream.wait_event(e2)
+        e1.record(bn.stream)
+        torch.cuda.synchronize()
+        assert bool((d_vd == 0).all()) and bool((d_vd2 == 0).all())
+        (ms2,) = bn.max_over_ranks(e0.elapsed_time(e1) / reps2)
+        out["verify_per_proof_challenges"]["two_contexts"] = {
+            "value": bn.world * 2 * B / (ms2 * 1e-3), "unit": "proofs/s", "ms_per_pair_of_batches": ms2, "batch_per_context": B,
+            "note": "two bpp_ctx (one stream pair each) sharing the key, calls issued alternately by one host thread: the second batch's "
+                    "challenge tables are built while the first batch accumulates"}
+        del ctx2
+    except Exception as e:  # keep the single-context figures
+        out["verify_per_proof_challenges"]["two_contexts"] = {"error": repr(e)[:200]}
     # random-linear-combination batch verification of the same proofs: one combined MSM per rank (per-proof fallback on failure)
     import secrets
     d_w = bn.to_dev(b"".join((secrets.randbits(128) | 1).to_bytes(32, "little") for _ in range(B)))
