@@ -222,12 +222,12 @@ NCU_BUCKET = {"capture": "profiles/r02d_verify_fs_kernels_ncu_full_details.txt (
               "gpu_time_ms": 5.61, "sm_busy_pct": 88.4, "smsp__issue_active_pct": 43.6, "registers_per_thread": 106, "dram_pct_of_peak": 3.8,
               "note": "the pipe that executes IMAD.WIDE is busy 88 % of the kernel's cycles: the kernel sits at the integer-multiply roofline of "
                       "sm_100a although only 0.4 of the 32-bit IMAD issue rate is reached (every wide multiply-add holds the pipe ~3.5-4.6 clk)"}
-NCU_DIRECT = {"capture": "profiles/r02g_direct_accumulate_ncu_full_details.txt + r02g_direct_raw_metrics.txt (direct_accumulate_kernel<Ed25519>, B = 2048, "
-                         "72 GB tables, c = 15; captured alone: in the step it shares the SMs with the auxiliary stream's generic segment)",
-              "gpu_time_ms": 5.41, "dram_bytes": 9.07e9 + 0.12e9, "dram_read_GBps": 1676, "sm_throughput_pct": 83.6, "smsp__issue_active_pct": 42.5,
-              "registers_per_thread": 120, "l2_hit_pct": 38.1, "active_lanes_per_warp_inst": 30.98,
+NCU_DIRECT = {"capture": "profiles/r02q_direct_accumulate_ncu_full_details.txt + r02q_direct_raw_metrics.txt (direct_accumulate_kernel<Ed25519>, B = 2048, "
+                         "72 GB tables, c = 15, final build; captured alone: in the step it shares the SMs with the auxiliary stream's generic segment)",
+              "gpu_time_ms": 5.34, "dram_bytes": 9.089e9 + 0.035e9, "dram_read_GBps": 1702, "sm_throughput_pct": 85.9, "smsp__issue_active_pct": 42.8,
+              "registers_per_thread": 128, "l2_hit_pct": 37.2, "active_lanes_per_warp_inst": 30.90,
               "note": "one random 128-byte table line per addition: ~9.1 GB of DRAM reads per launch (the algorithmic figure: every line is read once), a quarter "
-                      "of the measured HBM copy bandwidth, hidden behind the integer pipe (SM throughput 84 %)"}
+                      "of the measured HBM copy bandwidth, hidden behind the integer pipe (SM throughput 86 %)"}
 
 _REAL_STDOUT = None
 
@@ -500,6 +500,7 @@ def main():
                                      "no faster than the 72-IMAD.WIDE form, and running both kinds of warp on one SM adds nothing "
                                      "(profiles/r01e_dfma_fe.txt) - DFMA and IMAD.WIDE contend for the same issue capacity on sm_100a"},
         "executed": {"achieved": exec_kernel / 1e12 if exec_kernel else None, "frac": (exec_kernel / int_peak) if exec_kernel else None,
+                     "frac_of_pipe_ceiling": (exec_kernel / probe["wide_chain_per_s"]) if exec_kernel else None,
                      "note": "multiply-adds the kernel really issues (upper bound: zero digits skipped): the window tables of the public key "
                              "beat the algorithmic count, so `frac` above overstates pipe utilisation by algorithmic/executed"},
         "launches_timed": hot_n, "avg_launch_ms": hot_avg_ms, "kernel_share_of_step": hot_ms / elapsed_ms if elapsed_ms else None,
