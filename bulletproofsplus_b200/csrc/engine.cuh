@@ -451,7 +451,10 @@ struct Msm {
     }
     const uint32_t ss_tiles = ceil_div(n_keys, SS_TILE);
     BPP_LAUNCH(sizesort_hist_kernel, ss_tiles, SS_THREADS, 0, counts, n_keys, bins);
-    BPP_LAUNCH(sizesort_bins_scan_kernel, 1, 256, 0, bins, bins + 256, ACC_CAP);
+    // few buckets in all (one small MSM): spread buckets over lanes much earlier — the longest one-thread chain is the kernel
+    const bool lat = n_keys <= LAT_MAX_KEYS;
+    const uint32_t acc_cap = lat ? ACC_CAP_LAT : ACC_CAP, warp_cap = lat ? WARP_CAP_LAT : WARP_CAP;
+    BPP_LAUNCH(sizesort_bins_scan_kernel, 1, 256, 0, bins, bins + 256, acc_cap, warp_cap);
     BPP_LAUNCH(sizesort_scatter_kernel, ss_tiles, SS_THREADS, 0, counts, n_keys, bins, perm);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->hot_timing) {
@@ -459,7 +462,7 @@ struct Msm {
       BPP_CK(cudaEventCreate(&e1));
       BPP_CK(cudaEventRecord(e0, ctx->stream));
     }
-    {  // the long buckets first: a warp each for count >= 255, four lanes each for ACC_CAP < count < 255
+    {  // the long buckets first: a warp each for count > warp_cap, four lanes each for acc_cap < count <= warp_cap
       const uint32_t g32 = ceil_div(n_keys, 4) < 1184 ? ceil_div(n_keys, 4) : 1184, g4 = ceil_div(n_keys, 32) < 1184 ? ceil_div(n_keys, 32) : 1184;
       auto k32 = msm_accumulate_group_kernel<C, 32>;
       auto k4 = msm_accumulate_group_kernel<C, 4>;
@@ -473,10 +476,10 @@ struct Msm {
     }
     if (pattern)
       BPP_LAUNCH((msm_accumulate_kernel<C, true>), ceil_div(n_keys, 128), 128, 0, n_keys, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets,
-                 wtab_f, dyn_f, pattern);
+                 wtab_f, dyn_f, pattern, acc_cap);
     else
       BPP_LAUNCH((msm_accumulate_kernel<C, false>), ceil_div(n_keys, 128), 128, 0, n_keys, perm, offsets, counts, sorted, wtab, pl.wtab_points, dyn, buckets,
-                 nullptr, nullptr, 0u);
+                 nullptr, nullptr, 0u, acc_cap);
     if (ctx->hot_timing) {
       BPP_CK(cudaEventRecord(e1, ctx->stream));
       ctx->hot_pending.push_back({e0, e1});

@@ -414,13 +414,15 @@ static __global__ void __launch_bounds__(SS_THREADS) sizesort_hist_kernel(const 
   __syncthreads();
   if (h[threadIdx.x]) atomicAdd(&bins[threadIdx.x], h[threadIdx.x]);
 }
-// one block: bin totals -> exclusive starts; tiers[0..2] = first perm index of the buckets with count <= 254 / <= ACC_CAP
-static __global__ void __launch_bounds__(256) sizesort_bins_scan_kernel(uint32_t* __restrict__ bins, uint32_t* __restrict__ tiers, uint32_t acc_cap) {
+// one block: bin totals -> exclusive starts; tiers[0..2] = first perm index of the buckets with count <= warp_cap / <= acc_cap
+// (32 <= warp_cap <= 254, 4 <= acc_cap < warp_cap: the group kernels give every lane an entry)
+static __global__ void __launch_bounds__(256) sizesort_bins_scan_kernel(uint32_t* __restrict__ bins, uint32_t* __restrict__ tiers, uint32_t acc_cap,
+                                                                        uint32_t warp_cap) {
   uint32_t tot;
   uint32_t ex = block_exclusive_scan(bins[threadIdx.x], &tot);
   bins[threadIdx.x] = ex;
   if (threadIdx.x == 0) tiers[0] = 0;
-  if (threadIdx.x == 1) tiers[1] = ex;
+  if (threadIdx.x == 255 - warp_cap) tiers[1] = ex;
   if (threadIdx.x == 255 - acc_cap) tiers[2] = ex;
 }
 static __global__ void __launch_bounds__(SS_THREADS) sizesort_scatter_kernel(const uint32_t* __restrict__ counts, uint32_t n, uint32_t* __restrict__ bins,
@@ -450,9 +452,13 @@ static __global__ void __launch_bounds__(SS_THREADS) sizesort_scatter_kernel(con
 // One thread per bucket, buckets taken in descending-size order. wtab: window tables of the public key
 // (wtab_points entries), dyn: per-call points; both AoS affine, C::AFF_WORDS words per point, read with
 // 128-bit loads. Empty buckets are not written (the reduce kernels test the counts). Buckets longer than
-// ACC_CAP (the partial top window always produces some; adversarial scalars produce more) are left to
-// msm_accumulate_group_kernel, which spreads each of them over 4 or 32 lanes.
-constexpr uint32_t ACC_CAP = 96;
+// acc_cap (the partial top window always produces some; adversarial scalars produce more) are left to
+// msm_accumulate_group_kernel, which spreads each of them over 4 or 32 lanes. Throughput setting (many buckets: the chip is
+// full of one-thread chains anyway): one thread up to ACC_CAP entries, four lanes up to 254, a warp beyond. Latency setting
+// (few buckets — one small MSM, where a 96-entry chain IS the kernel's duration): ACC_CAP_LAT / WARP_CAP_LAT.
+constexpr uint32_t ACC_CAP = 96, WARP_CAP = 254;
+constexpr uint32_t ACC_CAP_LAT = 8, WARP_CAP_LAT = 64;
+constexpr uint32_t LAT_MAX_KEYS = 65536;  // at most this many buckets in all: latency setting (one thread per bucket would leave most of the chip idle)
 // Buckets longer than GIANT_SEG entries are cut into segments of GIANT_SEG, one warp per segment, and merged afterwards:
 // skewed scalar sets (all equal, P/-P pairs, a top window of one or two bits) put a large share of ALL terms into a few
 // buckets, which would otherwise serialise on one warp each.
@@ -473,12 +479,12 @@ __global__ void __launch_bounds__(128)
 msm_accumulate_kernel(uint32_t n_keys, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ offsets,
                       const uint32_t* __restrict__ counts, const uint32_t* __restrict__ sorted, const uint32_t* __restrict__ wtab, uint32_t wtab_points,
                       const uint32_t* __restrict__ dyn, uint32_t* __restrict__ buckets, const uint32_t* __restrict__ wtab_f,
-                      const uint32_t* __restrict__ dyn_f, uint32_t pattern) {
+                      const uint32_t* __restrict__ dyn_f, uint32_t pattern, uint32_t acc_cap) {
   uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_keys) return;
   const uint32_t key = perm[t];
   const uint32_t beg = offsets[key], cnt = counts[key], end = beg + cnt;
-  if (cnt == 0 || cnt > ACC_CAP) return;
+  if (cnt == 0 || cnt > acc_cap) return;
   typename C::Ext out;
   uint32_t ref = __ldg(sorted + beg);
   if (HYB && ((pattern >> (blockIdx.x & 3)) & 1u)) {
@@ -499,8 +505,8 @@ msm_accumulate_kernel(uint32_t n_keys, const uint32_t* __restrict__ perm, const 
   store_words<C::EXT_WORDS>(buckets + (size_t)key * C::EXT_WORDS, out);
 }
 
-// Buckets longer than ACC_CAP (the first entries of `perm`): G lanes per bucket — lane-strided walk, then a log2(G)-level
-// tree through shared memory. Tier 0 (count >= 255) runs with G = 32, tier 1 (ACC_CAP < count < 255) with G = 4.
+// Buckets longer than acc_cap (the first entries of `perm`): G lanes per bucket — lane-strided walk, then a log2(G)-level
+// tree through shared memory. Tier 0 (count > warp_cap) runs with G = 32, tier 1 (acc_cap < count <= warp_cap) with G = 4.
 template <class C, int G>
 __global__ void __launch_bounds__(128)
 msm_accumulate_group_kernel(const uint32_t* __restrict__ tiers, uint32_t tier, const uint32_t* __restrict__ perm,
@@ -515,7 +521,7 @@ msm_accumulate_group_kernel(const uint32_t* __restrict__ tiers, uint32_t tier, c
   for (uint32_t t = lo + blockIdx.x * (128 / G) + tid / G; t < hi; t += n_groups) {
     const uint32_t key = perm[t];
     if (counts[key] > GIANT_SEG) continue;  // split over several warps by the msm_giant_* kernels (warp-uniform test)
-    const uint32_t beg = offsets[key], end = beg + counts[key];  // count > ACC_CAP >= G: every lane has an entry
+    const uint32_t beg = offsets[key], end = beg + counts[key];  // count > cap >= G: every lane has an entry
     typename C::Ext acc;
     uint32_t e = beg + lane;
     uint32_t ref = __ldg(sorted + e);
