@@ -10,6 +10,7 @@
 #include "../../include/bpp.h"
 #include "msm.cuh"
 #include "pk_direct.cuh"
+#include "msm_straus.cuh"
 #include "proto_prove.cuh"
 #include "proto_session.cuh"
 
@@ -320,6 +321,26 @@ struct Msm {
     return BPP_OK;
   }
 
+  // Generic segment of jobs with at most STRAUS_MAX_D per-call points each (msm_straus.cuh): window sums, then the Horner kernel
+  // of the bucket path. Result in B_RESULTS like run_seg(seg = 2).
+  static int run_straus(bpp_ctx* ctx, MsmPlan pl, const uint32_t* d_job_start, const uint32_t* dyn, uint32_t dyn_per_job) {
+    if constexpr (C::HAS_COOP4) {
+      pl.cA = pl.WA = pl.NBA = 0;
+      pl.cB = 4; pl.WB = STRAUS_WINDOWS; pl.NBB = 8;
+      BPP_CK(ctx->buf[B_WINDOWS].ensure((size_t)pl.n_jobs * STRAUS_WINDOWS * C::EXT_WORDS * 4));
+      BPP_CK(ctx->buf[B_RESULTS].ensure((size_t)pl.n_jobs * C::EXT_WORDS * 4));
+      uint32_t* windows = ctx->buf[B_WINDOWS].as<uint32_t>();
+      auto k = msm_straus_kernel<C>;
+      const size_t smem = straus_smem_bytes(dyn_per_job);
+      if (smem > 40 * 1024) BPP_CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      BPP_LAUNCH(k, pl.n_jobs, 64, smem, pl, dyn_per_job, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_PIDX].as<uint32_t>(), d_job_start, dyn, windows);
+      BPP_LAUNCH(msm_combine4_kernel<C>, ceil_div(pl.n_jobs, 32), 128, 0, pl, windows, ctx->buf[B_FIXEDRES].as<uint32_t>(), ctx->buf[B_RESULTS].as<uint32_t>());
+      return BPP_OK;
+    } else {
+      ctx->err = "straus: unsupported curve"; return BPP_ERR_UNSUPPORTED;
+    }
+  }
+
   // seg: bit 0 = fixed-base segment, bit 1 = generic segment; terms of a segment that is left out are skipped by the sort
   // (their window count is zero).
   static int run_seg(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start,
@@ -334,6 +355,12 @@ struct Msm {
       pl.qA = pl.NBA < 16 ? pl.NBA : 16;
     }
     if (!(seg & 2)) dyn_per_job = 0;
+    // the generic segment alone, a few per-call points per job: Straus window sums in one kernel instead of the bucket pipeline
+    if constexpr (C::HAS_COOP4) {
+      static const bool no_straus = getenv("BPP_NO_STRAUS") != nullptr;
+      if (seg == 2 && pl.n_fixed && dyn && dyn_per_job && dyn_per_job <= STRAUS_MAX_D && !no_straus)
+        return run_straus(ctx, pl, d_job_start, dyn, dyn_per_job);
+    }
     if (dyn_per_job) {
       pl.cB = choose_window_generic(dyn_per_job, C::SCALAR_BITS, n_jobs);
       pl.WB = (C::SCALAR_BITS + 1 + pl.cB - 1) / pl.cB;
