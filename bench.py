@@ -222,9 +222,10 @@ NCU_BUCKET = {"capture": "profiles/r02d_verify_fs_kernels_ncu_full_details.txt (
               "gpu_time_ms": 5.61, "sm_busy_pct": 88.4, "smsp__issue_active_pct": 43.6, "registers_per_thread": 106, "dram_pct_of_peak": 3.8,
               "note": "the pipe that executes IMAD.WIDE is busy 88 % of the kernel's cycles: the kernel sits at the integer-multiply roofline of "
                       "sm_100a although only 0.4 of the 32-bit IMAD issue rate is reached (every wide multiply-add holds the pipe ~3.5-4.6 clk)"}
-NCU_DIRECT = {"capture": "profiles/r02q_direct_accumulate_ncu_full_details.txt + r02q_direct_raw_metrics.txt (direct_accumulate_kernel<Ed25519>, B = 2048, "
-                         "72 GB tables, c = 15, final build; captured alone: in the step it shares the SMs with the auxiliary stream's generic segment)",
-              "gpu_time_ms": 5.34, "dram_bytes": 9.089e9 + 0.035e9, "dram_read_GBps": 1702, "sm_throughput_pct": 85.9, "smsp__issue_active_pct": 42.8,
+NCU_DIRECT = {"capture": "profiles/r02x_verify_kernels_ncu_full_details.txt + r02x_verify_kernels_raw_metrics.txt (direct_accumulate_kernel<Ed25519>, "
+                         "B = 2048, 72 GB tables, c = 15, final build; captured alone: in the step it shares the SMs with the auxiliary stream's "
+                         "Straus + Horner kernels, which are in the same capture)",
+              "gpu_time_ms": 5.34, "dram_bytes": 9.091e9 + 0.034e9, "dram_read_GBps": 1702, "sm_throughput_pct": 85.8, "smsp__issue_active_pct": 42.8,
               "registers_per_thread": 128, "l2_hit_pct": 37.2, "active_lanes_per_warp_inst": 30.90,
               "note": "one random 128-byte table line per addition: ~9.1 GB of DRAM reads per launch (the algorithmic figure: every line is read once), a quarter "
                       "of the measured HBM copy bandwidth, hidden behind the integer pipe (SM throughput 86 %)"}
