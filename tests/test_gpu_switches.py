@@ -1,7 +1,9 @@
 """The engine's A/B switches must not change a single byte: the same small workload (commitments, an aggregated proof,
 a 40-proof batch with tampered members, window-table and generic MSMs over 4096 points, short split-digit jobs) runs in a
 fresh process per setting — default, BPP_HYBRID=5 / f (half / all accumulation blocks on the FP64 pipe, csrc/fe25519_f64.cuh),
-BPP_NO_OVERLAP=1 (generic segment on the caller's stream), BPP_NO_SPLIT=1 — and every output is compared with the CPU oracle."""
+BPP_NO_OVERLAP=1 (generic segment on the caller's stream), BPP_NO_SPLIT=1, BPP_NO_STRAUS=1 (per-proof points through the
+bucket pipeline instead of msm_straus_kernel), BPP_FUSE=1 (exponents inside the direct kernel; the workload's second batch runs
+against direct tables) — and every output is compared with the CPU oracle."""
 import os
 import subprocess
 import sys
@@ -43,6 +45,9 @@ got = api.verify_batch(pk, n, m, batch, Vl)
 want = [o.range_verify(0, n, m, b"".join(Vl[i]), batch[i]) for i in range(count)]
 assert got == want, (got, want)
 assert [i for i, v in enumerate(got) if v] == sorted(bad), got
+assert pk.precompute(1 << 30) >= 8  # direct tables: the same batch again (>= 32 jobs take them)
+assert api.verify_batch(pk, n, m, batch, Vl) == want, "verify with direct tables"
+assert api.prove_batch(pk, n, m, vs, gs) == proofs, "prove with direct tables"
 N = 4096
 mult = [rng.randrange(q) for _ in range(N)]
 sc = [rng.randrange(q) for _ in range(N)]
@@ -59,11 +64,12 @@ print("switch workload ok", ctx.kernel_launches())
 '''
 
 
-@pytest.mark.parametrize("env", [{}, {"BPP_HYBRID": "5"}, {"BPP_HYBRID": "f"}, {"BPP_NO_OVERLAP": "1"}, {"BPP_NO_SPLIT": "1"}],
-                         ids=["default", "hybrid5", "hybridf", "no_overlap", "no_split"])
+@pytest.mark.parametrize("env", [{}, {"BPP_HYBRID": "5"}, {"BPP_HYBRID": "f"}, {"BPP_NO_OVERLAP": "1"}, {"BPP_NO_SPLIT": "1"}, {"BPP_NO_STRAUS": "1"},
+                                 {"BPP_FUSE": "1"}],
+                         ids=["default", "hybrid5", "hybridf", "no_overlap", "no_split", "no_straus", "fuse"])
 def test_switch_does_not_change_results(env):
     e = dict(os.environ)
-    for k in ("BPP_HYBRID", "BPP_NO_OVERLAP", "BPP_NO_SPLIT"):
+    for k in ("BPP_HYBRID", "BPP_NO_OVERLAP", "BPP_NO_SPLIT", "BPP_NO_STRAUS", "BPP_FUSE"):
         e.pop(k, None)
     e.update(env)
     r = subprocess.run([sys.executable, "-c", WORKLOAD % {"root": ROOT}], env=e, capture_output=True, text=True, timeout=600)
