@@ -371,7 +371,18 @@ def main():
     pk = api.PublicKey.new(NM, _lib.RISTRETTO255, ctx)
     # one-time key set-up, not in any timed region: every signed-digit multiple of every window point of every generator in HBM
     t_tab = time.perf_counter()
-    table_c = pk.precompute(int(args.table_gb * 2**30)) if args.table_gb > 0 else 0
+    table_c, table_note = 0, None
+    if args.table_gb > 0:
+        # never ask for more than the device has free (minus working room); if even the narrowest table cannot be had the step
+        # runs on the bucket path and the line says so
+        free_b = torch.cuda.mem_get_info(dev)[0]
+        budget = min(int(args.table_gb * 2**30), free_b - (16 << 30))
+        while budget > (1 << 30) and not table_c:
+            try:
+                table_c = pk.precompute(budget)
+            except Exception as e:  # cudaMalloc refused: halve and retry
+                table_note = f"precompute({budget >> 30} GiB) failed: {str(e)[:80]}"
+                budget //= 2
     t_tab = time.perf_counter() - t_tab
     table_W = -(-252 // table_c) if table_c else 0
     table_bytes = (table_W + 1) * (1 << (table_c - 1)) * (2 + 2 * NM) * 128 if table_c else 0
@@ -555,7 +566,7 @@ def main():
             "dtype": "u32 limbs (integer, GF(2^255-19) / mod ell)", "data": "synthetic",
             "config": {"workload": WORKLOAD, "batch_per_gpu": B, "parallelism": f"proofs sharded x{world}",
                        "fixed_base_tables": ({"window_bits": table_c, "windows": table_W, "bytes": table_bytes, "build_s": t_tab,
-                                              "note": "bpp_pk_precompute: one-time key set-up, outside every timed region"} if table_c else None),
+                                              "note": "bpp_pk_precompute: one-time key set-up, outside every timed region" + (("; " + table_note) if table_note else "")} if table_c else None),
                        "challenge_mode": "the reference's constants (parity mode; challenge tables reused across calls). The same batch with "
                                          "per-proof Fiat-Shamir challenges is `verify_per_proof_challenges` in this line",
                        "l2": "256 MB memset between steps (inside the timed region); intermediates per step > L2"},

@@ -122,7 +122,12 @@ struct Api {
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
       }
       if (base) cudaFree(base);
-      if (e != cudaSuccess) { if (dtab) cudaFree(dtab); ctx->err = cudaGetErrorString(e); return BPP_ERR_CUDA; }
+      if (e != cudaSuccess) {
+        if (dtab) cudaFree(dtab);
+        cudaGetLastError();  // an allocation failure is not sticky, but it would surface at the next launch check of this context
+        ctx->err = cudaGetErrorString(e);
+        return BPP_ERR_CUDA;
+      }
       pk->dtab = dtab; pk->cD = c; pk->WD = W;
       if (c_out) *c_out = (int)c;
       return BPP_OK;
