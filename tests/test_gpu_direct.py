@@ -105,3 +105,23 @@ def test_precompute_errors(env):
     with pytest.raises(api.BppError) as ei:
         api.PublicKey.new(8, 1, ctx).precompute(1 << 30)  # secp256k1: not implemented
     assert ei.value.rc == 8
+
+
+def test_precompute_that_cannot_be_allocated_fails_cleanly(env, oracle):
+    """A table budget above what the device can give (c = 16 for 8194 generators: 583 GB) must fail with BPP_ERR_CUDA, leave the
+    key usable on the bucket path, leave no pending CUDA error in the context, and a later request that fits must succeed."""
+    api, ctx = env
+    n, m = 64, 64
+    pk = api.PublicKey.new(n * m, R, ctx)
+    with pytest.raises(api.BppError):
+        pk.precompute(10**12)
+    rng = random.Random(9)
+    vs = [rng.randrange(2**31) for _ in range(m)]
+    gs = [rng.randrange(ELL) for _ in range(m)]
+    proof = api.prove_batch(pk, n, m, vs, gs)[0]
+    V = pk.commit_batch(vs, gs)
+    assert api.verify_batch(pk, n, m, [proof], [V]) == [0]
+    assert proof == oracle.range_prove(R, n, m, vs, gs)
+    c = pk.precompute(_table_bytes(2 + 2 * n * m, 9))
+    assert c == 9
+    assert api.verify_batch(pk, n, m, [proof] * 33, [V] * 33) == [0] * 33  # >= 32 jobs: through the tables
