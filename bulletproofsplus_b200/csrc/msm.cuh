@@ -458,7 +458,7 @@ static __global__ void __launch_bounds__(SS_THREADS) sizesort_scatter_kernel(con
 // (few buckets — one small MSM, where a 96-entry chain IS the kernel's duration): ACC_CAP_LAT / WARP_CAP_LAT.
 constexpr uint32_t ACC_CAP = 96, WARP_CAP = 254;
 constexpr uint32_t ACC_CAP_LAT = 8, WARP_CAP_LAT = 64;
-constexpr uint32_t LAT_MAX_KEYS = 65536;  // at most this many buckets in all: latency setting (one thread per bucket would leave most of the chip idle)
+constexpr uint32_t LAT_MAX_KEYS = 262144;  // at most this many buckets in all: latency setting (one thread per bucket would leave most of the chip idle)
 // Buckets longer than GIANT_SEG entries are cut into segments of GIANT_SEG, one warp per segment, and merged afterwards:
 // skewed scalar sets (all equal, P/-P pairs, a top window of one or two bits) put a large share of ALL terms into a few
 // buckets, which would otherwise serialise on one warp each.
