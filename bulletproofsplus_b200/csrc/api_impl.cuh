@@ -691,8 +691,18 @@ struct Api {
       BPP_LAUNCH(range_bits_sum_kernel<C>, count, 128, 0, ps, d_v, pk->table, ctx->buf[B_EXT].as<uint32_t>());
     }
     const size_t scalar_off = (size_t)J * PB;
-    BPP_LAUNCH(wip_prove_kernel<M>, count, 256, 256 * 32, ps, T, params, a, b, alpha, ctx->buf[B_SCALARS].as<uint32_t>(),
-               ctx->buf[B_PIDX].as<uint32_t>(), d_proofs, proof_len, scalar_off);
+    {
+      // few proofs: a thread-block cluster per proof (proto_prove.cuh) - as many blocks as leave every block >= 128 vector
+      // elements and the whole launch within one wave of two blocks per SM
+      static const bool no_cluster = getenv("BPP_NO_CLUSTER") != nullptr;
+      uint32_t cs = 1;
+      while (!no_cluster && cs < 8 && N / (2 * cs) >= 128 && (uint64_t)count * 2 * cs <= 2 * 148) cs <<= 1;
+      uint32_t* o_sc = ctx->buf[B_SCALARS].as<uint32_t>();
+      uint32_t* o_pi = ctx->buf[B_PIDX].as<uint32_t>();
+      const uint32_t* c_params = params;
+      const uint32_t* c_alpha = alpha;
+      BPP_LAUNCH_CLUSTER(wip_prove_kernel<M>, count * cs, 256, 256 * 32, cs, ps, T, c_params, a, b, c_alpha, o_sc, o_pi, d_proofs, (size_t)proof_len, (size_t)scalar_off);
+    }
     BPP_LAUNCH(prove_jobstart_kernel, ceil_div(count * J + 1, 256), 256, 0, count, L, N, ps.has_A, ps.terms_per_proof,
                ctx->buf[B_JOBSTART].as<uint32_t>());
     BPP_TRY(Msm<C>::run(ctx, T_all, count * J, 0, ctx->buf[B_JOBSTART].as<uint32_t>(), pk->wtab, pk->n_points(), pk->cA, pk->WA, nullptr, 0, pk->wtab_f, nullptr, pk->dtab, pk->cD, pk->WD));

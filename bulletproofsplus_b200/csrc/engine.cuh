@@ -148,6 +148,26 @@ namespace bpp {
     }                                                                      \
   } while (0)
 
+// The same for a kernel that takes a thread-block cluster of `cs` blocks (1, 2, 4 or 8; grid must be a multiple of it).
+#define BPP_LAUNCH_CLUSTER(kernel, grid, block, smem, cs, ...)                 \
+  do {                                                                     \
+    cudaEvent_t _t0 = nullptr, _t1 = nullptr;                              \
+    if (ctx->trace_on) { cudaEventCreate(&_t0); cudaEventCreate(&_t1); cudaEventRecord(_t0, ctx->stream); } \
+    cudaLaunchConfig_t _cfg = {};                                          \
+    _cfg.gridDim = dim3(grid); _cfg.blockDim = dim3(block); _cfg.dynamicSmemBytes = (smem); _cfg.stream = ctx->stream; \
+    cudaLaunchAttribute _at[1];                                            \
+    _at[0].id = cudaLaunchAttributeClusterDimension;                       \
+    _at[0].val.clusterDim.x = (cs); _at[0].val.clusterDim.y = 1; _at[0].val.clusterDim.z = 1; \
+    _cfg.attrs = _at; _cfg.numAttrs = 1;                                   \
+    BPP_CK(cudaLaunchKernelEx(&_cfg, kernel, __VA_ARGS__));                \
+    ctx->launches++;                                                       \
+    BPP_CK(cudaGetLastError());                                            \
+    if (ctx->trace_on) {                                                   \
+      cudaEventRecord(_t1, ctx->stream);                                   \
+      ctx->trace.push_back({#kernel, _t0, _t1, ctx->aux_swapped ? 1 : 0}); \
+    }                                                                      \
+  } while (0)
+
 // block roles of the hybrid accumulation kernel: bit i set = blocks with (index % 4) == i run on the FP64 pipe. 0 (the
 // default: measured, mixing the two multiplies gains nothing on sm_100a — DESIGN.md §3.2) = integer pipe only.
 inline uint32_t hybrid_pattern() {
