@@ -153,9 +153,10 @@ def test_msm(api, ctx, oracle, R):
 
 
 @pytest.mark.parametrize("R", CURVES)
-@pytest.mark.parametrize("n,m", [(8, 1), (8, 4), (64, 2)])
+@pytest.mark.parametrize("n,m", [(8, 1), (8, 4), (64, 2), (32, 8), (64, 8)])
 def test_range_prove_and_verify(api, ctx, oracle, R, n, m):
-    """Byte-identical proofs and identical verdicts (valid + one tamper per proof field) on the reference's own group."""
+    """Byte-identical proofs and identical verdicts (valid + one tamper per proof field) on the reference's own group.
+    N = 256 and 512 take the WIP prover's thread-block clusters (2 and 4 blocks per proof) on every curve's scalar field."""
     q, pb = ORD[R], 2 * FB[R]
     rng = random.Random(100 * R + n + m)
     vs = [rng.randrange(2**min(n, 31)) for _ in range(m)]
