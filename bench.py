@@ -792,6 +792,7 @@ def run_configs_2_3(bn):
     assert bool((d_vd == 0).all())
     # the same batch with direct tables for this key's 8194 generators, if HBM allows beside the headline key's (c = 12: 47 GB)
     ms_bucket, c3_tables = ms, None
+    t_p_tab = t_v_tab = None
     free_b = bn.torch.cuda.mem_get_info(bn.dev)[0]
     budget = min(int(bn.args.table_gb * 2**30), free_b - (12 << 30))
     if bn.args.table_gb > 0 and budget > (8 << 30):
@@ -804,9 +805,17 @@ def run_configs_2_3(bn):
             ms = bn.timed(lambda: ctx.check(lib.bpp_range_verify_batch_dev(ctx.h, pk.handle, n, m, CB, d_V.data_ptr(), d_p.data_ptr(), None,
                                                                            d_vd.data_ptr()), "verify 64x64 tables"), reps=5, warm=2, flush=True)
             assert bool((d_vd == 0).all())
+            # the single-call latencies again, against the key with tables (every call takes them, one job or many)
+            out["config2_wip_4096"]["prove_ms_with_tables"] = bn.timed_host(wip_prove, reps=5, warm=2)
+            out["config2_wip_4096"]["verify_ms_with_tables"] = bn.timed_host(wip_verify, reps=5, warm=2)
+            out["config2_wip_4096"]["fixed_base_tables_window_bits"] = c3_tables
+            assert api.verify_batch(pk, n, m, pr, [Vs]) == [0] and api.prove_batch(pk, n, m, vs, gs) == pr
+            t_p_tab = bn.timed_host(lambda: api.prove_batch(pk, n, m, vs, gs), reps=5, warm=1)
+            t_v_tab = bn.timed_host(lambda: api.verify_batch(pk, n, m, pr, [Vs]), reps=5, warm=1)
     out["config3_n64_m64"] = {
         "single_proof_prove_ms": t_p, "single_proof_verify_ms": t_v, "batch": CB, "batch_verify_ms": ms, "batch_verifies_per_sec": CB / (ms * 1e-3),
         "batch_verify_ms_bucket_path": ms_bucket, "fixed_base_tables_window_bits": c3_tables,
+        "single_proof_prove_ms_with_tables": t_p_tab, "single_proof_verify_ms_with_tables": t_v_tab,
         "note": "one aggregated proof of 64 values (N = 4096): verifier MSM of 8285 terms; single-proof numbers are host-ABI latencies "
                 "(python packing included), the batch is device-resident",
         "algorithmic_field_muls_verify": algorithmic_field_muls(8285)[0]}

@@ -243,11 +243,13 @@ struct Msm {
                  const uint32_t* wtab_f = nullptr, const uint32_t* dyn_f = nullptr, const uint32_t* dtab = nullptr, uint32_t cD = 0,
                  uint32_t WD = 0, const DirectVerifySrc* vsrc = nullptr) {
     if (n_jobs == 0) return BPP_OK;
-    // direct tables exist for the Ed25519 policy only; a job is one block's work there, so a handful of jobs (one proof, one RLC
-    // combination) is better served by the bucket path, which spreads a job over the whole chip
+    // direct tables exist for the Ed25519 policy only. Any number of jobs takes them: run_direct cuts a job into up to 64 slices,
+    // so that one proof's generator terms are 8192 threads' work for a few dozen additions each (one n = 64, m = 16
+    // verification 886 -> 682 us, one proof 1022 -> 702 us: profiles/r02ar_ab.txt; BPP_DIRECT_MIN_JOBS=32 restores the old rule)
     const bool direct = uses_direct(dtab, n_jobs) && n_fixed && wtab;
     if (vsrc && !direct) { ctx->err = "msm: fused exponents need the direct tables"; return BPP_ERR_UNSUPPORTED; }
-    const bool two = n_fixed && wtab && dyn_per_job && overlaps(n_jobs);
+    // with direct tables the two segments are different kernels anyway: run them side by side for any number of jobs
+    const bool two = n_fixed && wtab && dyn_per_job && (overlaps(n_jobs) || (direct && overlaps(16)));
     if (!two) {
       if (!direct) return run_seg(ctx, n_terms, n_jobs, uniform, d_job_start, wtab, n_fixed, cA, WA, dyn, dyn_per_job, 3, wtab_f, dyn_f);
       BPP_CK(ctx->buf[B_RESULTS].ensure((size_t)n_jobs * C::EXT_WORDS * 4));
@@ -294,7 +296,10 @@ struct Msm {
   // The fixed-base terms (point index < n_fixed) of every job straight from the key's direct tables: ONE kernel, no sort, no
   // buckets, no reduction (pk_direct.cuh). Terms with other indices are skipped (the generic segment takes them).
   // whether a launch sequence over n_jobs jobs takes the direct tables (callers that fuse work into that kernel ask beforehand)
-  static bool uses_direct(const uint32_t* dtab, uint32_t n_jobs) { return dtab && C::HAS_COOP4 && n_jobs >= 32; }
+  static bool uses_direct(const uint32_t* dtab, uint32_t n_jobs) {
+    static const uint32_t min_jobs = getenv("BPP_DIRECT_MIN_JOBS") ? (uint32_t)atoi(getenv("BPP_DIRECT_MIN_JOBS")) : 1u;
+    return dtab && C::HAS_COOP4 && n_jobs >= min_jobs;
+  }
   static int run_direct(bpp_ctx* ctx, uint32_t n_terms, uint32_t n_jobs, uint32_t uniform, const uint32_t* d_job_start, uint32_t n_fixed,
                         const uint32_t* dtab, uint32_t cD, uint32_t WD, uint32_t* out, const DirectVerifySrc* vsrc = nullptr) {
     DirectVerifySrc src;
@@ -311,6 +316,9 @@ struct Msm {
     while (tpj > 4 && tpj * 8 > avg) tpj >>= 1;
     uint32_t S = 1;
     while (S < 8 && (uint64_t)ceil_div(n_jobs, 128 / tpj) * S < 8 * 592 && (uint64_t)tpj * S * 2 * 2 <= avg) S <<= 1;
+    // few jobs (a single proof, a handful): keep doubling while the launch stays within one wave of the chip and every lane
+    // keeps at least one (term, window) pair - one job then runs on up to 64 x tpj threads instead of 8 x tpj
+    while (S < 64 && (uint64_t)n_jobs * tpj * S * 2 <= 592 * 128 && (uint64_t)tpj * S * 2 <= (uint64_t)avg * WD) S <<= 1;
     uint32_t* partial = out;
     if (S > 1) {
       BPP_CK(ctx->buf[B_CHUNK_S2].ensure((size_t)n_jobs * S * C::EXT_WORDS * 4));
@@ -329,7 +337,8 @@ struct Msm {
       else
         BPP_LAUNCH((direct_accumulate_kernel<C, false>), ceil_div((uint64_t)n_jobs * S, 128 / tpj), 128, 0, pl, tpj, S, ctx->buf[B_SCALARS].as<uint32_t>(),
                    ctx->buf[B_PIDX].as<uint32_t>(), d_job_start, dtab, partial, src);
-      if (S > 1) BPP_LAUNCH(direct_join_kernel<C>, ceil_div(n_jobs, 128), 128, 0, n_jobs, S, partial, out);
+      if (S > 8) BPP_LAUNCH(direct_join_tree_kernel<C>, ceil_div(n_jobs, 4), 128, 0, n_jobs, S, partial, out);
+      else if (S > 1) BPP_LAUNCH(direct_join_kernel<C>, ceil_div(n_jobs, 128), 128, 0, n_jobs, S, partial, out);
     } else {
       ctx->err = "direct tables: unsupported curve"; return BPP_ERR_UNSUPPORTED;
     }

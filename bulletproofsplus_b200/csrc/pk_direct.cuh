@@ -232,4 +232,32 @@ __global__ void __launch_bounds__(128) direct_join_kernel(uint32_t n_jobs, uint3
   store_words<C::EXT_WORDS>(results + (size_t)job * C::EXT_WORDS, a);
 }
 
+// The same for many slices per job (few jobs spread over the whole chip): a warp per job, lane-strided partial sums, then a
+// five-level tree through shared memory.
+template <class C>
+__global__ void __launch_bounds__(128) direct_join_tree_kernel(uint32_t n_jobs, uint32_t S, const uint32_t* __restrict__ partial,
+                                                               uint32_t* __restrict__ results) {
+  __shared__ uint32_t sh[128 * C::EXT_WORDS];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, job = blockIdx.x * 4 + (tid >> 5);
+  typename C::Ext acc, b;
+  C::set_identity(acc);
+  if (job < n_jobs)
+    for (uint32_t k = lane; k < S; k += 32) {
+      load_words<C::EXT_WORDS>(b, partial + ((size_t)job * S + k) * C::EXT_WORDS);
+      C::add(acc, b);
+    }
+  typename C::Ext* mine = reinterpret_cast<typename C::Ext*>(sh + tid * C::EXT_WORDS);
+  *mine = acc;
+  __syncthreads();
+  for (uint32_t sft = 16; sft > 0; sft >>= 1) {
+    if (lane < sft) {
+      typename C::Ext o = *reinterpret_cast<typename C::Ext*>(sh + (tid + sft) * C::EXT_WORDS);
+      C::add(acc, o);
+      *mine = acc;
+    }
+    __syncthreads();
+  }
+  if (job < n_jobs && lane == 0) store_words<C::EXT_WORDS>(results + (size_t)job * C::EXT_WORDS, acc);
+}
+
 }  // namespace bpp

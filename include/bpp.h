@@ -76,8 +76,8 @@ int bpp_pk_new(bpp_ctx* ctx, int curve, size_t len, bpp_pk** out);
  * BPP_RISTRETTO255 only (BPP_ERR_UNSUPPORTED otherwise). Everything else (commit, prove, verify, MSM) takes the key as usual. */
 int bpp_pk_new_hashed(bpp_ctx* ctx, int curve, size_t len, const uint8_t* domain_sep, size_t domain_sep_len, bpp_pk** out);
 /* Optional, once per key: DIRECT fixed-base tables — every signed-digit multiple of every window point of every generator, in
- * HBM (no counterpart in the reference, whose PublicKey is four vectors of points, publickey.rs:13-18). With them batches of
- * >= 32 proofs / MSM jobs evaluate their generator terms with one table addition per window and no bucket sort or reduction;
+ * HBM (no counterpart in the reference, whose PublicKey is four vectors of points, publickey.rs:13-18). With them every call
+ * against the key (one proof or thousands) evaluates its generator terms with one table addition per window and no bucket sort or reduction;
  * results are the same group elements (bit-identical encodings). max_bytes bounds the table: the widest window c in [8, 16]
  * that fits is used and returned in *window_bits ((ceil(252/c) + 1) * 2^(c-1) * 128 B per generator: 40 GB for n*m = 1024 at
  * c = 14, 8.7 GB for n*m = 64 at c = 16). BPP_RISTRETTO255 only (BPP_ERR_UNSUPPORTED otherwise); BPP_ERR_LENGTH if not even
@@ -86,7 +86,7 @@ int bpp_pk_precompute(bpp_ctx* ctx, bpp_pk* pk, size_t max_bytes, int* window_bi
 /* n_jobs multi-scalar multiplications against the key's own generators (MulVec::calculate, mulvec.rs:20-33, with the points
  * fixed to [g, h, G_0..G_{len-1}, H_0..H_{len-1}]): scalars = n_jobs x (2 + 2 len) canonical scalars in that order,
  * out_points = n_jobs encodings. Vector Pedersen commitments; fixed-base paths only (window tables, or the direct tables of
- * bpp_pk_precompute for >= 32 jobs). */
+ * bpp_pk_precompute). */
 int bpp_pk_msm(bpp_ctx* ctx, const bpp_pk* pk, const uint8_t* scalars, size_t n_jobs, uint8_t* out_points);
 int bpp_pk_export(bpp_ctx* ctx, const bpp_pk* pk, uint8_t* g, uint8_t* h, uint8_t* G, uint8_t* H);
 size_t bpp_pk_len(const bpp_pk* pk);

@@ -1,4 +1,4 @@
-"""Direct fixed-base tables (bpp_pk_precompute, csrc/pk_direct.cuh): with them batches of >= 32 jobs evaluate the generator terms
+"""Direct fixed-base tables (bpp_pk_precompute, csrc/pk_direct.cuh): with them every call (one job or thousands) evaluates the generator terms
 by one table addition per window instead of the bucket method. The results must be the SAME bytes: against the CPU oracle, against
 the exponent-domain value (sum_i s_i k_i) g, and against the bucket path of the same library on the same inputs — for adversarial
 scalars (0, 1, ell-1, the values around ell/2 where half-order folding switches, 2^252-1, all-equal), for window widths where the
@@ -35,7 +35,7 @@ def test_pk_msm_direct_equals_bucket_path_and_exponent_value(env, oracle, length
     rng = random.Random(100 * length + c)
     edge = [0, 1, 2, ELL - 1, ELL - 2, (ELL - 1) // 2, (ELL + 1) // 2, (ELL + 3) // 2, 2**252 - 1, 2**252, 2**251, 2**(c - 1), 2**(c - 1) + 1,
             2**c - 1, (1 << 252) - (1 << (252 - c)), ELL // 3]
-    jobs = 40  # >= 32: the direct path is taken once the tables exist
+    jobs = 40  # the direct path is taken once the tables exist
     scal = []
     for j in range(jobs):
         if j == 0:
@@ -57,7 +57,7 @@ def test_pk_msm_direct_equals_bucket_path_and_exponent_value(env, oracle, length
     assert got_c == c
     assert pk.precompute(1) == c  # idempotent: the tables exist
     assert pk.msm(scal, jobs) == want
-    assert pk.msm(scal[:np_ * 3], 3) == want[:3]  # fewer than 32 jobs: bucket path even with the tables
+    assert pk.msm(scal[:np_ * 3], 3) == want[:3]  # few jobs: up to 64 slices per job and the tree join
 
 
 @pytest.mark.parametrize("n,m,count", [(64, 1, 70), (32, 4, 33), (64, 16, 34)])
@@ -124,4 +124,39 @@ def test_precompute_that_cannot_be_allocated_fails_cleanly(env, oracle):
     assert proof == oracle.range_prove(R, n, m, vs, gs)
     c = pk.precompute(_table_bytes(2 + 2 * n * m, 9))
     assert c == 9
-    assert api.verify_batch(pk, n, m, [proof] * 33, [V] * 33) == [0] * 33  # >= 32 jobs: through the tables
+    assert api.verify_batch(pk, n, m, [proof] * 33, [V] * 33) == [0] * 33  # through the tables
+
+
+@pytest.mark.parametrize("n,m", [(8, 1), (32, 2), (64, 4), (64, 16)])
+def test_few_jobs_take_the_tables_too(env, oracle, n, m):
+    """One proof, a handful of proofs, 1..31 key MSMs against a key WITH tables: up to 64 slices per job, tree join, the
+    per-proof points through Straus beside them. Proof bytes and verdicts against the oracle, MSMs against (sum s_i k_i) g."""
+    api, ctx = env
+    N = n * m
+    np_ = 2 + 2 * N
+    pk = api.PublicKey.new(N, R, ctx)
+    assert pk.precompute(_table_bytes(np_, 10 if N <= 256 else 8)) >= 8
+    rng = random.Random(7000 + N)
+    dlog = [1, 2] + [3 * (i + 1) for i in range(N)] + [5 * (i + 1) for i in range(N)]
+    for jobs in (1, 2, 5, 31):
+        scal = [rng.randrange(ELL) for _ in range(jobs * np_)]
+        if jobs == 2:
+            scal[:np_] = [0] * np_                                       # the identity as a result
+            scal[np_:np_ + 3] = [ELL - 1, (ELL + 1) // 2, 2**252 - 1]
+        want = [oracle.scalar_mul(R, sum(s * k for s, k in zip(scal[j * np_:(j + 1) * np_], dlog)) % ELL) for j in range(jobs)]
+        assert pk.msm(scal, jobs) == want, jobs
+    for count in (1, 3, 15):
+        vs = [rng.randrange(2**min(n, 31)) for _ in range(count * m)]
+        gs = [rng.randrange(ELL) for _ in range(count * m)]
+        proofs = api.prove_batch(pk, n, m, vs, gs)
+        for i in range(count):
+            assert proofs[i] == oracle.range_prove(R, n, m, vs[i * m:(i + 1) * m], gs[i * m:(i + 1) * m]), (count, i)
+        Vs = pk.commit_batch(vs, gs)
+        Vl = [Vs[i * m:(i + 1) * m] for i in range(count)]
+        bad = bytearray(proofs[-1]); bad[-1] ^= 1
+        batch = proofs[:-1] + [bytes(bad)]
+        want = [0] * (count - 1) + [1]
+        assert api.verify_batch(pk, n, m, batch, Vl) == want
+        L = N.bit_length() - 1
+        y, z = (7, 7) if m == 1 else (12, 23)
+        assert api.verify_batch_fs(pk, n, m, batch, Vl, challenges=[[y, z, 99] + [7] * L] * count) == want

@@ -52,9 +52,13 @@ rows.append(("verify n=64 m=16, per-proof Fiat-Shamir challenges (device / e2e)"
 rows.append(("prove n=64 m=16 (proofs/s, device / e2e)", f"{k(pr.get('value'))} / {k((pr.get('e2e') or {}).get('value'))}", at(2, lambda d: d["proves"]["value"]),
              at(4, lambda d: d["proves"]["value"]), at(8, lambda d: d["proves"]["value"]), f"{(pr.get('roofline') or {}).get('frac', 0):.2f} whole batch (algorithmic)",
              k(prc.get("value"), 2), f"B1 all cores: {k(prc.get('all_cores'), 1)}"))
-rows.append(("WIP 2^12 prove / verify (ms, one argument, host ABI)", f"{c2.get('prove_ms', 0):.2f} / {c2.get('verify_ms', 0):.2f}", "—", "—", "—", "", "", ""))
+def _tab(d, a, b_):
+    return f" (with direct tables: {d[a]:.2f} / {d[b_]:.2f})" if d.get(a) and d.get(b_) else ""
+rows.append(("WIP 2^12 prove / verify (ms, one argument, host ABI)",
+             f"{c2.get('prove_ms', 0):.2f} / {c2.get('verify_ms', 0):.2f}" + _tab(c2, "prove_ms_with_tables", "verify_ms_with_tables"), "—", "—", "—", "", "", ""))
 rows.append(("n=64 m=64 (8 285-term MSM): single prove / verify ms; 128-proof batch verifies/s",
-             f"{c3.get('single_proof_prove_ms', 0):.2f} / {c3.get('single_proof_verify_ms', 0):.2f}; {k(c3.get('batch_verifies_per_sec'))}", "—", "—", "—", "", "", ""))
+             f"{c3.get('single_proof_prove_ms', 0):.2f} / {c3.get('single_proof_verify_ms', 0):.2f}"
+             + _tab(c3, "single_proof_prove_ms_with_tables", "single_proof_verify_ms_with_tables") + f"; {k(c3.get('batch_verifies_per_sec'))}", "—", "—", "—", "", "", ""))
 rows.append(("batch verify 8 192 × (n=64, m=1), fixed batch sharded (proofs/s, strong scaling)", at(1, c4), at(2, c4), at(4, c4), at(8, c4), "", "", ""))
 rows.append(("RLC batch verify n=64 m=16 (proofs/s)", at(1, lambda d: d["verifies_per_sec_rlc_batch"]["value"]), at(2, lambda d: d["verifies_per_sec_rlc_batch"]["value"]),
              at(4, lambda d: d["verifies_per_sec_rlc_batch"]["value"]), at(8, lambda d: d["verifies_per_sec_rlc_batch"]["value"]), "", "", ""))
