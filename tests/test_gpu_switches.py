@@ -4,7 +4,8 @@ fresh process per setting — default, BPP_HYBRID=5 / f (half / all accumulation
 BPP_NO_OVERLAP=1 (generic segment on the caller's stream), BPP_NO_SPLIT=1, BPP_NO_STRAUS=1 (per-proof points through the
 bucket pipeline instead of msm_straus_kernel), BPP_FUSE=1 (exponents inside the direct kernel; the workload's second batch runs
 against direct tables), BPP_NO_CLUSTER=1 (one block per proof in wip_prove_kernel instead of a thread-block cluster; the
-workload proves one n = 64, m = 16 proof alone for it) — and every output is compared with the CPU oracle."""
+workload proves one n = 64, m = 16 proof alone for it), BPP_DIRECT_MIN_JOBS=32 (few jobs keep the bucket path although the key
+has tables) — and every output is compared with the CPU oracle."""
 import os
 import subprocess
 import sys
@@ -48,6 +49,8 @@ assert got == want, (got, want)
 assert [i for i, v in enumerate(got) if v] == sorted(bad), got
 assert pk.precompute(1 << 30) >= 8  # direct tables: the same batch again (>= 32 jobs take them)
 assert api.verify_batch(pk, n, m, batch, Vl) == want, "verify with direct tables"
+assert api.verify_batch(pk, n, m, batch[:5], Vl[:5]) == want[:5], "five proofs with direct tables"
+assert api.verify_batch(pk, n, m, batch[3:4], Vl[3:4]) == want[3:4] == [1], "one (tampered) proof with direct tables"
 assert api.prove_batch(pk, n, m, vs, gs) == proofs, "prove with direct tables"
 pk16 = api.PublicKey.new(1024, 0, ctx)  # one large proof alone: a cluster of 8 blocks in the WIP prover
 v16 = [rng.randrange(2**31) for _ in range(16)]
@@ -70,11 +73,11 @@ print("switch workload ok", ctx.kernel_launches())
 
 
 @pytest.mark.parametrize("env", [{}, {"BPP_HYBRID": "5"}, {"BPP_HYBRID": "f"}, {"BPP_NO_OVERLAP": "1"}, {"BPP_NO_SPLIT": "1"}, {"BPP_NO_STRAUS": "1"},
-                                 {"BPP_FUSE": "1"}, {"BPP_NO_CLUSTER": "1"}],
-                         ids=["default", "hybrid5", "hybridf", "no_overlap", "no_split", "no_straus", "fuse", "no_cluster"])
+                                 {"BPP_FUSE": "1"}, {"BPP_NO_CLUSTER": "1"}, {"BPP_DIRECT_MIN_JOBS": "32"}],
+                         ids=["default", "hybrid5", "hybridf", "no_overlap", "no_split", "no_straus", "fuse", "no_cluster", "direct_min_32"])
 def test_switch_does_not_change_results(env):
     e = dict(os.environ)
-    for k in ("BPP_HYBRID", "BPP_NO_OVERLAP", "BPP_NO_SPLIT", "BPP_NO_STRAUS", "BPP_FUSE", "BPP_NO_CLUSTER"):
+    for k in ("BPP_HYBRID", "BPP_NO_OVERLAP", "BPP_NO_SPLIT", "BPP_NO_STRAUS", "BPP_FUSE", "BPP_NO_CLUSTER", "BPP_DIRECT_MIN_JOBS"):
         e.pop(k, None)
     e.update(env)
     r = subprocess.run([sys.executable, "-c", WORKLOAD % {"root": ROOT}], env=e, capture_output=True, text=True, timeout=600)
