@@ -971,9 +971,21 @@ def run_msm_sweep(bn, int_peak):
                 tables_ms = bn.timed(msm, reps=reps, warm=2)
                 assert bytes(d_out.cpu().numpy().tobytes()) == first, "window-table MSM disagrees with the generic one"
             ms, path = (tables_ms, "window tables") if tables_ms is not None and tables_ms < generic_ms else (generic_ms, "generic")
+            direct_ms = direct_c = None
+            if curve == _lib.RISTRETTO255 and lg <= 16:  # direct tables for a reused point set, as far as HBM allows beside the keys' tables
+                budget = min(48 << 30, bn.torch.cuda.mem_get_info(bn.dev)[0] - (12 << 30))
+                if budget > (1 << 30):
+                    try:
+                        direct_c = pts.precompute_direct(budget)
+                        direct_ms = bn.timed(msm, reps=reps, warm=2)
+                        assert bytes(d_out.cpu().numpy().tobytes()) == first, "direct-table MSM disagrees with the generic one"
+                        if direct_ms < ms:
+                            ms, path = direct_ms, "direct tables"
+                    except bn.api.BppError as e:
+                        direct_c = "unavailable: " + str(e)[:80]
             W, c_star, _ = algorithmic_field_muls(n, bits, *costs)
             row = {"log2_n": lg, "ms": ms, "points_per_sec": n / (ms * 1e-3), "int_roofline_frac": W * imad / (ms * 1e-3) / int_peak,
-                   "path": path, "generic_ms": generic_ms, "tables_ms": tables_ms,
+                   "path": path, "generic_ms": generic_ms, "tables_ms": tables_ms, "direct_tables_ms": direct_ms, "direct_tables_window_bits": direct_c,
                    "generic_int_roofline_frac": W * imad / (generic_ms * 1e-3) / int_peak}
             if imad_exec:
                 row["int_roofline_frac_at_executed_imad_per_mul"] = W * imad_exec / (ms * 1e-3) / int_peak

@@ -58,6 +58,7 @@ extern "C" {
     pub fn bpp_points_len(pts: *const bpp_points) -> usize;
     pub fn bpp_points_free(pts: *mut bpp_points);
     pub fn bpp_points_precompute(ctx: *mut bpp_ctx, pts: *mut bpp_points) -> c_int;
+    pub fn bpp_points_precompute_direct(ctx: *mut bpp_ctx, pts: *mut bpp_points, max_bytes: usize, window_bits: *mut c_int) -> c_int;
     pub fn bpp_msm_prepared(ctx: *mut bpp_ctx, pts: *const bpp_points, scalars: *const u8, k: usize, n_jobs: usize, out_points: *mut u8) -> c_int;
     pub fn bpp_msm_prepared_dev(ctx: *mut bpp_ctx, pts: *const bpp_points, d_scalars: *const c_void, k: usize, n_jobs: usize, d_out_points: *mut c_void) -> c_int;
     pub fn bpp_raw_point_bytes(curve: c_int) -> c_int;

@@ -17,7 +17,7 @@ ERROR_NAMES = ["OK", "VERIFICATION", "FORMAT", "LENGTH", "NOT_POW2", "GENERATORS
 SYMBOLS = [
     "bpp_init", "bpp_destroy", "bpp_last_error", "bpp_point_bytes", "bpp_range_proof_len", "bpp_wip_proof_len",
     "bpp_kernel_launches", "bpp_sync", "bpp_pk_new", "bpp_pk_new_hashed", "bpp_pk_precompute", "bpp_pk_msm", "bpp_pk_export", "bpp_pk_len", "bpp_pk_free", "bpp_commit_batch", "bpp_commit_batch_u64", "bpp_msm",
-    "bpp_points_upload", "bpp_points_from_multipliers", "bpp_points_len", "bpp_points_precompute", "bpp_points_free", "bpp_msm_prepared",
+    "bpp_points_upload", "bpp_points_from_multipliers", "bpp_points_len", "bpp_points_precompute", "bpp_points_precompute_direct", "bpp_points_free", "bpp_msm_prepared",
     "bpp_msm_prepared_dev", "bpp_raw_point_bytes", "bpp_msm_prepared_raw", "bpp_points_sum_raw", "bpp_msm_prepared_raw_dev", "bpp_points_sum_raw_dev", "bpp_points_sum_raw_noalloc_dev", "bpp_range_prove_batch",
     "bpp_range_verify_batch", "bpp_range_prove_batch_dev", "bpp_range_verify_batch_dev", "bpp_range_prove", "bpp_range_verify",
     "bpp_wip_prove", "bpp_wip_verify", "bpp_range_verify_batch_fs", "bpp_range_verify_batch_rlc", "bpp_range_verify_batch_rlc_dev", "bpp_range_verify_batch_fs_dev", "bpp_range_prove_begin", "bpp_range_prove_step",
@@ -75,6 +75,7 @@ def load() -> C.CDLL:
     L.bpp_points_from_multipliers.argtypes = [vp, i, u8p, sz, C.POINTER(vp)]
     L.bpp_points_len.argtypes = [vp]; L.bpp_points_len.restype = sz
     L.bpp_points_precompute.argtypes = [vp, vp]
+    L.bpp_points_precompute_direct.argtypes = [vp, vp, sz, C.POINTER(C.c_int)]
     L.bpp_points_free.argtypes = [vp]; L.bpp_points_free.restype = None
     L.bpp_msm_prepared.argtypes = [vp, vp, u8p, sz, sz, u8p]
     L.bpp_msm_prepared_dev.argtypes = [vp, vp, vp, sz, sz, vp]

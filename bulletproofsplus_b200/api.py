@@ -490,6 +490,12 @@ class Points:
         self.ctx.check(self.ctx.lib.bpp_points_precompute(self.ctx.h, self.h), "points_precompute")
         return self
 
+    def precompute_direct(self, max_bytes: int = 48 << 30) -> int:
+        """Direct tables for this point set within max_bytes of HBM (bpp_points_precompute_direct); returns the window width."""
+        c = C.c_int(0)
+        self.ctx.check(self.ctx.lib.bpp_points_precompute_direct(self.ctx.h, self.h, max_bytes, C.byref(c)), "points_precompute_direct")
+        return c.value
+
     def msm(self, scalars: bytes, k: int | None = None, n_jobs: int = 1) -> list:
         k = k if k is not None else len(scalars) // 32 // n_jobs
         out = C.create_string_buffer(n_jobs * self.pb)

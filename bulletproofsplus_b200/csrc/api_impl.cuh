@@ -95,27 +95,28 @@ struct Api {
   }
   // Direct fixed-base tables (pk_direct.cuh): the widest window c in [8, 16] whose table fits in max_bytes. One-time cost: a
   // few tens of milliseconds and (W + 1) * 2^(c-1) * 128 B per generator (40 GB for a 1024-generator key at c = 14).
-  static int pk_precompute(bpp_ctx* ctx, bpp_pk* pk, size_t max_bytes, int* c_out) {
+  // the tables of `np` affine points at `table` (the public key's generators, or a caller's point set)
+  static int build_direct(bpp_ctx* ctx, const uint32_t* table, uint32_t np, size_t max_bytes, const char* what, uint32_t** dtab_out,
+                          uint32_t* c_out, uint32_t* W_out) {
     if constexpr (!C::HAS_COOP4) {
-      ctx->err = "pk_precompute: direct tables are implemented for Ristretto255 only";
+      ctx->err = std::string(what) + ": direct tables are implemented for Ristretto255 only";
       return BPP_ERR_UNSUPPORTED;
     } else {
-      if (pk->dtab) { if (c_out) *c_out = (int)pk->cD; return BPP_OK; }
-      const uint32_t np = pk->n_points();
       uint32_t c = 0, W = 0;
       for (uint32_t cc = 16; cc >= 8; cc--) {
         const uint32_t WW = dtab_windows(C::SCALAR_BITS, cc);
         if (dtab_entries(np, cc, WW) * C::AFF_WORDS * 4 <= max_bytes) { c = cc; W = WW; break; }
       }
-      if (!c) { ctx->err = "pk_precompute: max_bytes is too small for any window width >= 8"; return BPP_ERR_LENGTH; }
+      if (!c) { ctx->err = std::string(what) + ": max_bytes is too small for any window width >= 8"; return BPP_ERR_LENGTH; }
       const size_t entries = dtab_entries(np, c, W);
+      if ((uint64_t)np * W >= (1ull << 31)) { ctx->err = std::string(what) + ": too many points"; return BPP_ERR_LENGTH; }
       uint32_t *dtab = nullptr, *base = nullptr;
       cudaError_t e = cudaMalloc(&dtab, entries * C::AFF_WORDS * 4);
       if (e == cudaSuccess) e = cudaMalloc(&base, (size_t)np * W * C::AFF_WORDS * 4);
       if (e == cudaSuccess) e = ctx->buf[B_EXT].ensure((size_t)np * W * C::EXT_WORDS * 4);
       if (e == cudaSuccess) {
-        wtab_build_kernel<C><<<ceil_div(np, 32), 32, 0, ctx->stream>>>(np, 0u, np, c, W, pk->table, base, ctx->buf[B_EXT].as<uint32_t>());
-        dtab_fill_kernel<C><<<ceil_div(np * W, 64), 64, 0, ctx->stream>>>(np, c, W, base, dtab);
+        wtab_build_kernel<C><<<ceil_div(np, 32), 32, 0, ctx->stream>>>(np, 0u, np, c, W, table, base, ctx->buf[B_EXT].as<uint32_t>());
+        dtab_fill_kernel<C><<<ceil_div((uint64_t)np * W, 64), 64, 0, ctx->stream>>>(np, c, W, base, dtab);
         dtab_normalise_kernel<C><<<(unsigned)((entries / DTAB_NORM + 128) / 128), 128, 0, ctx->stream>>>(entries, dtab);
         ctx->launches += 3;
         e = cudaGetLastError();
@@ -128,7 +129,32 @@ struct Api {
         ctx->err = cudaGetErrorString(e);
         return BPP_ERR_CUDA;
       }
-      pk->dtab = dtab; pk->cD = c; pk->WD = W;
+      *dtab_out = dtab; *c_out = c; *W_out = W;
+      return BPP_OK;
+    }
+  }
+  static int pk_precompute(bpp_ctx* ctx, bpp_pk* pk, size_t max_bytes, int* c_out) {
+    if (pk->dtab) { if (c_out) *c_out = (int)pk->cD; return BPP_OK; }
+    uint32_t* dtab = nullptr;
+    uint32_t c = 0, W = 0;
+    BPP_TRY(build_direct(ctx, pk->table, pk->n_points(), max_bytes, "pk_precompute", &dtab, &c, &W));
+    pk->dtab = dtab; pk->cD = c; pk->WD = W;
+    if (c_out) *c_out = (int)c;
+    return BPP_OK;
+  }
+  // the same for a caller's point set (bpp_points_precompute_direct): window tables first (the engine's plan needs them), then
+  // every signed-digit multiple. Later bpp_msm_prepared* calls against `pts` take them whatever their number of jobs.
+  static int points_precompute_direct(bpp_ctx* ctx, bpp_points* pts, size_t max_bytes, int* c_out) {
+    if (pts->dtab) { if (c_out) *c_out = (int)pts->cD; return BPP_OK; }
+    if constexpr (!C::HAS_COOP4) {
+      ctx->err = "points_precompute_direct: direct tables are implemented for Ristretto255 only";
+      return BPP_ERR_UNSUPPORTED;
+    } else {
+      BPP_TRY(points_precompute(ctx, pts));
+      uint32_t* dtab = nullptr;
+      uint32_t c = 0, W = 0;
+      BPP_TRY(build_direct(ctx, pts->table, (uint32_t)pts->len, max_bytes, "points_precompute_direct", &dtab, &c, &W));
+      pts->dtab = dtab; pts->cD = c; pts->WD = W;
       if (c_out) *c_out = (int)c;
       return BPP_OK;
     }
@@ -331,6 +357,7 @@ struct Api {
     if (pts->wtab) cudaFree(pts->wtab);
     if (pts->table_f) cudaFree(pts->table_f);
     if (pts->wtab_f) cudaFree(pts->wtab_f);
+    if (pts->dtab) cudaFree(pts->dtab);
     delete pts;
   }
   // scalars already on device (n_jobs*k); result: n_jobs extended points in B_RESULTS
@@ -343,7 +370,8 @@ struct Api {
     BPP_LAUNCH(scalars_check_kernel<M>, ceil_div(T, 256), 256, 0, T, ctx->buf[B_SCALARS].as<uint32_t>(), ctx->buf[B_FLAGS].as<uint8_t>());
     BPP_LAUNCH(iota_kernel, ceil_div(T, 256), 256, 0, T, (uint32_t)k, ctx->buf[B_PIDX].as<uint32_t>());
     if (pts->wtab)  // point index i < len: fixed-base segment only
-      return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, pts->wtab, (uint32_t)pts->len, pts->cA, pts->WA, nullptr, 0, pts->wtab_f);
+      return Msm<C>::run(ctx, T, (uint32_t)n_jobs, (uint32_t)k, nullptr, pts->wtab, (uint32_t)pts->len, pts->cA, pts->WA, nullptr, 0, pts->wtab_f, nullptr,
+                         pts->dtab, pts->cD, pts->WD);
     if (C::HAS_F64 && hybrid_pattern()) {  // the same points in the FP64 accumulators' slot format, built once per point set
       bpp_points* mp = const_cast<bpp_points*>(pts);
       if (!mp->table_f) {

@@ -209,12 +209,18 @@ void bpp_points_free(bpp_points* pts) {
   if (pts->wtab) cudaFree(pts->wtab);
   if (pts->table_f) cudaFree(pts->table_f);
   if (pts->wtab_f) cudaFree(pts->wtab_f);
+  if (pts->dtab) cudaFree(pts->dtab);
   delete pts;
 }
 int bpp_points_precompute(bpp_ctx* ctx, bpp_points* pts) {
   BPP_ENTER(ctx);
   if (!pts) return BPP_ERR_NOT_INIT;
   BPP_DISPATCH(pts->curve, points_precompute(ctx, pts));
+}
+int bpp_points_precompute_direct(bpp_ctx* ctx, bpp_points* pts, size_t max_bytes, int* window_bits) {
+  BPP_ENTER(ctx);
+  if (!pts) return BPP_ERR_NOT_INIT;
+  BPP_DISPATCH(pts->curve, points_precompute_direct(ctx, pts, max_bytes, window_bits));
 }
 int bpp_msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out_points) {
   BPP_ENTER(ctx);

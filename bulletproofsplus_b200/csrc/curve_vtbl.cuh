@@ -18,6 +18,7 @@ struct CurveVtbl {
   int (*msm)(bpp_ctx*, const uint8_t*, const uint8_t*, size_t, uint8_t*);
   int (*points_upload)(bpp_ctx*, const uint8_t*, size_t, bool, bpp_points**);
   int (*points_precompute)(bpp_ctx*, bpp_points*);
+  int (*points_precompute_direct)(bpp_ctx*, bpp_points*, size_t, int*);
   int (*msm_prepared)(bpp_ctx*, const bpp_points*, const uint8_t*, size_t, size_t, uint8_t*, bool);
   int (*msm_prepared_dev)(bpp_ctx*, const bpp_points*, const void*, size_t, size_t, void*);
   int (*msm_prepared_raw_dev)(bpp_ctx*, const bpp_points*, const void*, size_t, void*);
@@ -79,6 +80,7 @@ void fill_vtbl_core(CurveVtbl& v) {
   v.msm = A::msm;
   v.points_upload = A::points_upload;
   v.points_precompute = A::points_precompute;
+  v.points_precompute_direct = A::points_precompute_direct;
   v.msm_prepared = A::msm_prepared;
   v.msm_prepared_dev = A::msm_prepared_dev;
   v.msm_prepared_raw_dev = A::msm_prepared_raw_dev;

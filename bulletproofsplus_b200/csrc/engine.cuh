@@ -105,6 +105,8 @@ struct bpp_points {
   uint32_t* wtab = nullptr;   // optional window tables (bpp_points_precompute): wtab[w * len + i] = 2^(cA * w) * table[i]
   uint32_t* table_f = nullptr, *wtab_f = nullptr;  // `table` / `wtab` in the FP64 accumulators' slot format (HAS_F64; built on first use)
   uint32_t cA = 0, WA = 0;
+  uint32_t* dtab = nullptr;   // optional direct tables (bpp_points_precompute_direct), laid out like bpp_pk::dtab
+  uint32_t cD = 0, WD = 0;
 };
 
 // interactive proving (bpp_range_prove_begin / _step / _finish): device state of a batch between the host's challenges

@@ -114,6 +114,14 @@ void bpp_points_free(bpp_points* pts);
  * above 48 GB); later bpp_msm_prepared* calls against `pts` run without doublings, per-window bucket sets or Horner pass.
  * Results are identical with and without it. */
 int bpp_points_precompute(bpp_ctx* ctx, bpp_points* pts);
+/* The same step further, as bpp_pk_precompute does for a key's generators: DIRECT tables — every signed-digit multiple of every
+ * window point of every point of the set, (ceil(252/c) + 1) * 2^(c-1) * 128 B per point for the widest window c in [8, 16] that
+ * fits max_bytes (returned in *window_bits; 38 GB for 2^10 points at c = 15, 62 GB for 2^16 points at c = 9). Builds the window
+ * tables of bpp_points_precompute first if they are missing. Later bpp_msm_prepared* calls against `pts` then cost one table
+ * addition per window and term, with no bucket sort or reduction, whatever the number of jobs. No counterpart in the reference
+ * (mulvec.rs:35-53 clones its points per MulVec). BPP_RISTRETTO255 only (BPP_ERR_UNSUPPORTED otherwise); BPP_ERR_LENGTH if not
+ * even c = 8 fits; results are identical with and without it. */
+int bpp_points_precompute_direct(bpp_ctx* ctx, bpp_points* pts, size_t max_bytes, int* window_bits);
 /* n_jobs independent MSMs over consecutive slices of `scalars`, all against pts[0..k): out = n_jobs points */
 int bpp_msm_prepared(bpp_ctx* ctx, const bpp_points* pts, const uint8_t* scalars, size_t k, size_t n_jobs, uint8_t* out_points);
 /* same with device pointers (no host copies, no synchronisation): d_scalars = n_jobs*k*32 B, d_out = n_jobs encodings */

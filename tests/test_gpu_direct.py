@@ -160,3 +160,36 @@ def test_few_jobs_take_the_tables_too(env, oracle, n, m):
         L = N.bit_length() - 1
         y, z = (7, 7) if m == 1 else (12, 23)
         assert api.verify_batch_fs(pk, n, m, batch, Vl, challenges=[[y, z, 99] + [7] * L] * count) == want
+
+
+@pytest.mark.parametrize("log2n,jobs_k", [(6, [(1, 64), (3, 20)]), (10, [(1, 1024), (5, 200), (40, 25)]), (13, [(1, 8192), (2, 4096)])])
+def test_point_set_direct_tables(env, oracle, log2n, jobs_k):
+    """bpp_points_precompute_direct: a caller's point set with direct tables. Every MSM against it (one job or many, all points
+    or a prefix) must give the bytes of the generic path and of the exponent-domain value (sum s_i k_i) g."""
+    api, ctx = env
+    N = 1 << log2n
+    rng = random.Random(500 + log2n)
+    mult = [rng.randrange(ELL) for _ in range(N)]
+    mult[0], mult[1] = 0, ELL - 1  # the identity and -g among the points
+    le32 = lambda x: int(x).to_bytes(32, "little")
+    pts = api.Points.from_multipliers(b"".join(le32(x) for x in mult), R, ctx)
+    cases = []
+    for jobs, k in jobs_k:
+        sc = [rng.randrange(ELL) for _ in range(jobs * k)]
+        sc[:4] = [0, 1, ELL - 1, (ELL + 1) // 2][:min(4, len(sc))]
+        blob = b"".join(le32(x) for x in sc)
+        want = [oracle.scalar_mul(R, sum(s * m for s, m in zip(sc[j * k:(j + 1) * k], mult[:k])) % ELL) for j in range(jobs)]
+        assert pts.msm(blob, k=k, n_jobs=jobs) == want  # generic path
+        cases.append((blob, k, jobs, want))
+    budget = (252 // 9 + 2) * (1 << 8) * N * 128  # room for c = 9 at least
+    c = pts.precompute_direct(min(budget, 8 << 30))
+    assert 8 <= c <= 16 and pts.precompute_direct(1) == c  # idempotent
+    for blob, k, jobs, want in cases:
+        assert pts.msm(blob, k=k, n_jobs=jobs) == want, (k, jobs)
+
+
+def test_point_set_direct_tables_unsupported_curve(env):
+    api, ctx = env
+    pts = api.Points.from_multipliers((7).to_bytes(32, "little") * 4, 1, ctx)
+    with pytest.raises(api.BppError):
+        pts.precompute_direct(1 << 30)

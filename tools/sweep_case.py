@@ -10,4 +10,4 @@ bn = bench.Bench(args, torch, None, 0, 1, 0)
 probe = bn.ctx.int_peak_probe()
 out = bench.run_msm_sweep(bn, probe["imad32_per_s"])
 for k, rows in out.items():
-    print(k, json.dumps([(r["log2_n"], round(r["ms"], 3)) for r in rows]))
+    print(k, json.dumps([(r["log2_n"], round(r["ms"], 3), r["path"]) for r in rows]))
