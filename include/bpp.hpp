@@ -159,6 +159,13 @@ class PublicKey {
     detail::check(ctx_, bpp_commit_batch_u64(ctx_, pk_.get(), &v, gamma.e.data(), 1, p.bytes.data()), "commitment_u64");
     return p;
   }
+  // optional, once per key (bpp_pk_precompute): direct fixed-base tables within max_bytes of HBM; every later prove / verify /
+  // commitment MSM against the key takes them. Returns the window width. No counterpart in the reference.
+  int precompute(size_t max_bytes) {
+    int c = 0;
+    detail::check(ctx_, bpp_pk_precompute(ctx_, pk_.get(), max_bytes, &c), "PublicKey::precompute");
+    return c;
+  }
   size_t len() const { return len_; }
   Curve curve() const { return curve_; }
   size_t point_bytes() const { return pb_; }

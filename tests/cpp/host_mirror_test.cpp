@@ -165,6 +165,14 @@ int main(int argc, char** argv) {
     RangeProof proof64 = prove_with_transcript(hk64, 64, p64, merlin::Transcript("hashed"));
     report("hashed key: n = 64 transcript proof of v >= 2^31 == Ok(())", verify_with_transcript(proof64, hk64, 64, p64.commitment_vec, merlin::Transcript("hashed")) == Result::Ok());
     report("hashed key: fixed-constant prove/verify == Ok(())", RangeProof::prove(hk64, 64, p64).verify(hk64, 64, p64.commitment_vec) == Result::Ok());
+    // the same key with direct tables (bpp_pk_precompute): a single proof / verification takes them too; bytes unchanged
+    RangeProof before = RangeProof::prove(hk64, 64, p64);
+    const int c = hk64.precompute((size_t)1 << 30);
+    report("hashed key: direct tables built (8 <= c <= 16)", c >= 8 && c <= 16);
+    RangeProof after = RangeProof::prove(hk64, 64, p64);
+    report("hashed key: proof bytes unchanged by the tables", after.to_bytes() == before.to_bytes());
+    report("hashed key: verify with tables == Ok(())", after.verify(hk64, 64, p64.commitment_vec) == Result::Ok());
+    report("hashed key: transcript proof verifies with tables", verify_with_transcript(proof64, hk64, 64, p64.commitment_vec, merlin::Transcript("hashed")) == Result::Ok());
   }
   printf("%s\n", failures ? "SOME FAILED" : "ALL PASSED");
   return failures ? 1 : 0;
