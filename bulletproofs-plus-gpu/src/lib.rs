@@ -120,6 +120,13 @@ impl PublicKey {
         PublicKey { h, len }
     }
     pub fn len(&self) -> usize { self.len }
+    /// Optional, once per key (`bpp_pk_precompute`): direct fixed-base tables within `max_bytes` of HBM; every later prove /
+    /// verify against the key, one proof or a batch, takes them. Returns the window width. No counterpart in the reference.
+    pub fn precompute(&mut self, max_bytes: usize) -> i32 {
+        let mut c: std::os::raw::c_int = 0;
+        check(unsafe { bpp_pk_precompute(ctx(), self.h, max_bytes, &mut c) }, "PublicKey::precompute");
+        c as i32
+    }
     /// (g, h, G_vec, H_vec) — the pub fields of the reference struct
     pub fn generators(&self) -> (Point, Point, Vec<Point>, Vec<Point>) {
         let (mut g, mut h) = ([0u8; 32], [0u8; 32]);
