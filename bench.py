@@ -647,7 +647,7 @@ def run_fs_verify(bn, pk, B):
             "value": bn.world * 2 * B / (ms2 * 1e-3), "unit": "proofs/s", "ms_per_pair_of_batches": ms2, "batch_per_context": B,
             "note": "two bpp_ctx (one stream pair each) sharing the key, calls issued alternately by one host thread: the second batch's "
                     "challenge tables are built while the first batch accumulates"}
-        del ctx2
+        ctx2.close()
     except Exception as e:  # keep the single-context figures
         out["verify_per_proof_challenges"]["two_contexts"] = {"error": repr(e)[:200]}
     # random-linear-combination batch verification of the same proofs: one combined MSM per rank (per-proof fallback on failure)

@@ -83,6 +83,13 @@ class Context:
         if rc != _lib.OK:
             raise BppError(rc, f"{what}: {self.lib.bpp_last_error(self.h).decode()}")
 
+    def close(self):
+        """bpp_destroy: waits for the context's streams and frees its device scratch. Keys and point sets created through the
+        context stay valid (they own their memory); nothing else may use the context afterwards."""
+        if self.h:
+            self.lib.bpp_destroy(self.h)
+            self.h = None
+
     def kernel_launches(self) -> int:
         return int(self.lib.bpp_kernel_launches(self.h))
 
